@@ -1,0 +1,216 @@
+/*
+ * sbo.h -- C-ABI of the B200-native safe-BO step library (libsbo.so).
+ *
+ * Drop-in boundary for the per-step hot path of
+ * matthewyjiang/safe_bayesian_optimization's `safe_bayesian_optimization_node`
+ * (file references below are into that repository,
+ * src/safe_bayesian_optimization_node.cpp unless stated).  The reference has
+ * no FFI/plugin interface of its own -- everything on the path is a private
+ * member of `OptimizerNode` (:128) -- so each entry point names the member
+ * function or the lines of the node it replaces.  INTEGRATION.md shows the
+ * edit a maintainer makes in the node.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes, no C++/torch types.
+ *   - every function returns an sbo_status (0 = OK, < 0 = error); nothing
+ *     throws across the boundary.  sbo_last_error(ctx) gives the text; the
+ *     caller logs and skips the step, as the node does today (:569-572,
+ *     :618-621, :503-506).
+ *   - one caller thread per context (the node runs a SingleThreadedExecutor,
+ *     :1503).  Calls are synchronous unless the name ends in _async.
+ *   - host pointers are borrowed for the duration of the call; outputs go to
+ *     caller-owned buffers (pinned memory recommended, not required).
+ *   - there is no CPU fallback: sbo_create fails without an sm_100 GPU.
+ *
+ * Grid convention: cell = iy * W + ix, x = x0 + ix * rx, y = y0 + iy * ry
+ * (row-major, y outer -- the layout of `safety_image.at<uchar>(y, x)`, :454).
+ */
+#ifndef SBO_H
+#define SBO_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SBO_ABI_VERSION 1
+
+typedef enum {
+  SBO_OK = 0,
+  SBO_ERR_INVALID_ARG = -1,   /* null pointer, bad size, NaN/Inf input          */
+  SBO_ERR_NO_DEVICE = -2,     /* no CUDA device of compute capability 10.x      */
+  SBO_ERR_CUDA = -3,          /* CUDA runtime/driver failure (text in last_error) */
+  SBO_ERR_NOT_POSDEF = -4,    /* Cholesky met a non-positive pivot              */
+  SBO_ERR_CAPACITY = -5,      /* n > max_obs or m > max_cells                   */
+  SBO_ERR_STATE = -6,         /* grid / observations / posterior not set yet    */
+  SBO_ERR_COMM = -7           /* NCCL failure                                   */
+} sbo_status;
+
+typedef enum {
+  SBO_FP32 = 0,   /* mu, sigma^2 stored fp32; contraction on tcgen05 (3xTF32, fp32 accum in TMEM) */
+  SBO_FP64 = 1    /* mu, sigma^2 stored fp64; contraction in fp64 FMA                             */
+} sbo_precision;
+
+typedef enum {
+  SBO_KERNEL_AUTO = 0,     /* tcgen05 path for SBO_FP32, SIMT fp64 for SBO_FP64 */
+  SBO_KERNEL_SIMT = 1,     /* force the SIMT kernel (any precision)             */
+  SBO_KERNEL_TCGEN05 = 2   /* force the tcgen05 kernel (SBO_FP32 only)          */
+} sbo_kernel_choice;
+
+/* GP hyper-parameters of the external mapping node the library replaces
+ * (config/lpsc.yaml:35-37) plus capacity limits.  The GP is zero-mean on
+ * (y - prior_mean); sigma^2 is the latent variance unless
+ * include_noise_in_sigma != 0 (then + noise_var). */
+typedef struct {
+  double sigma_f;                 /* lpsc.yaml:37 sigma_f                     */
+  double length_scale;            /* lpsc.yaml:36 length_scale                */
+  double noise_var;               /* lpsc.yaml:35 noise_level, as a variance  */
+  double prior_mean;              /* constant mean                            */
+  int32_t include_noise_in_sigma; /* 0 = latent variance                      */
+  int32_t precision;              /* sbo_precision                            */
+  int32_t kernel;                 /* sbo_kernel_choice                        */
+  int32_t device;                 /* CUDA device ordinal                      */
+  int32_t max_obs;                /* capacity in observations (n)             */
+  int32_t reserved0;
+  int64_t max_cells;              /* capacity in LOCAL cells (this shard)     */
+} sbo_config;
+
+typedef struct sbo_ctx sbo_ctx;
+
+typedef struct {
+  int64_t idx;    /* global cell index, -1 when the safe set is empty */
+  double value;
+} sbo_argmax;
+
+/* Result of one BO step (caller-allocated POD). */
+typedef struct {
+  int64_t n_cells;            /* cells of this shard                                         */
+  int64_t safe_count;         /* S_.count() (:426, :873); global when a communicator is set   */
+  sbo_argmax argmax_ucb;      /* max of mu + beta*sigma over safe cells; ties -> lowest index */
+  sbo_argmax argmax_width;    /* max of 2*beta*sigma (Q1 - Q0, :516) over safe cells          */
+  int64_t clamped_sigma2;     /* cells whose sigma^2 came out < 0 and was clamped to 0        */
+  int32_t n_obs;
+  int32_t kernel_used;        /* sbo_kernel_choice actually run                               */
+  float ms_posterior;         /* GPU time: posterior kernel(s)                                */
+  float ms_sets;              /* GPU time: CI + mask + argmax kernel                          */
+  float ms_comm;              /* GPU time: collective                                         */
+  float ms_total;             /* GPU time: whole step on the stream                           */
+} sbo_step_out;
+
+/* ---- life cycle --------------------------------------------------------- */
+
+int32_t sbo_abi_version(void);
+/* replaces: OptimizerNode ctor parameter block (:48-72) + the service client
+ * of the external GP node (:75-77). */
+int32_t sbo_create(const sbo_config* cfg, sbo_ctx** out);
+int32_t sbo_destroy(sbo_ctx* ctx);
+const char* sbo_last_error(const sbo_ctx* ctx);   /* ctx may be NULL: last create error */
+const char* sbo_status_string(int32_t status);
+
+/* Use an existing CUDA stream (cudaStream_t as void*) instead of the
+ * context's own; NULL restores the own stream. */
+int32_t sbo_set_stream(sbo_ctx* ctx, void* cuda_stream);
+int32_t sbo_synchronize(sbo_ctx* ctx);
+
+/* ---- grid --------------------------------------------------------------- */
+
+/* replaces: request->resolution (:580-581) and n_width_cells/n_height_cells/
+ * x_coords/y_coords of the response (:612-613, :639-641).  [row0,row1) is the
+ * band of grid rows this context owns (0,H for a single GPU); cells are
+ * numbered globally. */
+int32_t sbo_set_grid(sbo_ctx* ctx, double x0, double y0, double rx, double ry,
+                     int32_t W, int32_t H, int32_t row0, int32_t row1);
+
+/* ---- observations: the external GP node's fit ---------------------------- */
+
+/* Full factorisation: K = k(X,X) + noise_var I = L L^T (blocked fp64
+ * Cholesky), L^-1 (blocked triangular inverse), alpha = K^-1 (y - mean).
+ * xy is n x 2 row-major.  replaces: mapping_package/terrain_mapping_node's
+ * fit (launch/safe_bayesian_optimization.launch.py:111-117). */
+int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, int32_t n);
+/* Rank-k append: L21 = K21 L11^-T, L22 = chol(K22 - L21 L21^T), new rows of
+ * L^-1 = [-L22^-1 L21 L11^-1, L22^-1], alpha refreshed.  O(k n^2). */
+int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y, int32_t k);
+int32_t sbo_num_observations(const sbo_ctx* ctx);
+/* Read back the factor state (fp64, n x n row-major / n) for checking. */
+int32_t sbo_copy_linv(sbo_ctx* ctx, double* host_dst);
+int32_t sbo_copy_alpha(sbo_ctx* ctx, double* host_dst);
+
+/* ---- the BO step --------------------------------------------------------- */
+
+/* One BO step over this context's cells: GP posterior (mu, sigma^2), CI,
+ * safe mask, argmax.  `mask_host` (n_cells bytes, 0/255, may be NULL)
+ * receives the mask ready to wrap as cv::Mat(H, W, CV_8UC1, ptr).
+ * replaces: request_terrain_map (:568-623) + the unpack loop (:639-644) +
+ * ComputeSets (:399-416) + the rasterise loop of FindSafetyContourIndices
+ * (:444-456). */
+int32_t sbo_step(sbo_ctx* ctx, double beta, double f_min, uint8_t* mask_host, sbo_step_out* out);
+
+/* Same step after a rank-k append, in O(m n k): only the k newest rows of
+ * L^-1 are contracted (sigma^2 -= |rows_new k*|^2) and mu is recomputed with
+ * the refreshed alpha.  Requires a previous sbo_step/sbo_step_incremental on
+ * the same grid with the observations that preceded the append. */
+int32_t sbo_step_incremental(sbo_ctx* ctx, double beta, double f_min, uint8_t* mask_host,
+                             sbo_step_out* out);
+
+/* ComputeSets on caller-supplied posterior arrays (fp64 host, length m): the
+ * reference's own arithmetic and nothing else.  q0/q1 (may be NULL) receive
+ * Q_.col(0)/Q_.col(1).  Bit-exact with the reference.
+ * replaces: ComputeConfidenceIntervals (:411-416) + UpdateSafeSet (:409). */
+int32_t sbo_compute_sets(sbo_ctx* ctx, const double* mu, const double* std_dev, int64_t m,
+                         double beta, double f_min, uint8_t* mask_host, double* q0, double* q1,
+                         sbo_step_out* out);
+
+/* GetNextSubgoal's selection on a host-supplied frontier list (global cell
+ * indices, as produced by cv::findContours on the mask, :461-492), using the
+ * posterior of the last step (or the arrays of the last sbo_compute_sets):
+ * distance to goal, sort by (distance, position), closest max(1, F/4),
+ * strictly-largest CI width.  *out_cell = -1 when F == 0.
+ * replaces: :508-549. */
+int32_t sbo_select_subgoal(sbo_ctx* ctx, const int32_t* frontier, int64_t F, double goal_x,
+                           double goal_y, int32_t* out_cell);
+
+/* Bulk read-back of the last step's posterior for this shard.  fp32 or fp64
+ * according to cfg.precision (sbo_copy_*_f64 always converts to double). */
+int32_t sbo_copy_mu(sbo_ctx* ctx, void* host_dst);
+int32_t sbo_copy_sigma2(sbo_ctx* ctx, void* host_dst);
+int32_t sbo_copy_mu_f64(sbo_ctx* ctx, double* host_dst);
+int32_t sbo_copy_sigma2_f64(sbo_ctx* ctx, double* host_dst);
+int32_t sbo_copy_mask(sbo_ctx* ctx, uint8_t* host_dst);
+
+/* ---- device-resident variants (bench / pipelines that keep data in HBM) -- */
+
+/* Step with no host traffic: results stay on the device; `out` is filled
+ * after a stream synchronise.  mask_dev may be NULL (internal buffer). */
+int32_t sbo_step_device(sbo_ctx* ctx, double beta, double f_min, sbo_step_out* out);
+/* CI+mask+argmax on device-resident fp64 mu/std (length m). */
+int32_t sbo_compute_sets_device(sbo_ctx* ctx, const double* mu_dev, const double* std_dev,
+                                int64_t m, double beta, double f_min, uint8_t* mask_dev,
+                                sbo_step_out* out);
+
+/* ---- multi-GPU ------------------------------------------------------------ */
+
+/* One process per GPU.  Rank 0 calls sbo_comm_unique_id, the host transports
+ * the 128 bytes (e.g. torch.distributed broadcast), every rank calls
+ * sbo_comm_init.  Afterwards sbo_step* reduce argmax/safe_count over all ranks
+ * with one NCCL all-gather of the per-rank (value, index) records. */
+int32_t sbo_comm_unique_id(uint8_t id_out[128]);
+int32_t sbo_comm_init(sbo_ctx* ctx, const uint8_t id[128], int32_t rank, int32_t world);
+int32_t sbo_comm_destroy(sbo_ctx* ctx);
+/* Host-side merge of per-shard results with the library's total order
+ * (value desc, index asc); used when the host does its own transport. */
+int32_t sbo_merge_step_out(const sbo_step_out* parts, int32_t count, sbo_step_out* merged);
+
+/* ---- introspection -------------------------------------------------------- */
+
+/* Number of kernel launches issued by this context since creation. */
+int64_t sbo_launch_count(const sbo_ctx* ctx);
+/* Device properties the library sees: SM count, and 1 if tcgen05 path usable. */
+int32_t sbo_device_info(const sbo_ctx* ctx, int32_t* sm_count, int32_t* tcgen05_ok);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SBO_H */

@@ -1,0 +1,168 @@
+// common.cuh -- context, error plumbing and small device helpers shared by the
+// kernels of libsbo.so (C-ABI in include/sbo.h).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/sbo.h"
+
+namespace sbo {
+
+constexpr int kFactorNB = 128;   // block size of the fp64 factorisation kernels
+constexpr int kObsPad = 256;     // observation capacity is rounded up to this (tcgen05 N tile)
+constexpr int kMaxAppend = 128;  // rows per rank-k append pass
+
+// Result record of the CI/mask/argmax pass, written by the device.
+struct SetsResult {
+  double ucb_val;
+  long long ucb_idx;
+  double width_val;
+  long long width_idx;
+  long long safe_count;
+  long long clamped;
+};
+
+enum class PosteriorSource : int { kNone = 0, kStep = 1, kHostArrays = 2 };
+
+}  // namespace sbo
+
+struct sbo_ctx {
+  sbo_config cfg{};
+  int device = 0;
+  int sm_count = 0;
+  bool tc_ok = false;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[6]{};
+  std::string err;
+  int64_t launches = 0;
+
+  // grid
+  bool grid_set = false;
+  double x0 = 0, y0 = 0, rx = 0, ry = 0;
+  int W = 0, H = 0, row0 = 0, row1 = 0;
+  int64_t cell0 = 0, m_local = 0;
+
+  // observations / factor state (all fp64, leading dimension n_cap)
+  int n = 0;
+  int n_prev = 0;  // n before the last append (for the incremental step)
+  int n_cap = 0;
+  double* d_xy = nullptr;     // [n_cap][2]
+  double* d_r = nullptr;      // [n_cap] y - prior_mean
+  double* d_A = nullptr;      // [n_cap][n_cap] K, then L in the lower triangle
+  double* d_Linv = nullptr;   // [n_cap][n_cap] L^-1, zero above the diagonal and beyond n
+  double* d_Dinv = nullptr;   // [n_cap/NB][NB][NB] inverses of the diagonal blocks of L
+  double* d_alpha = nullptr;  // [n_cap]
+  double* d_w = nullptr;      // [n_cap] work vector
+  double* d_small = nullptr;  // append scratch: K21/L21/T [kMaxAppend][n_cap] x2 + S
+  int* d_info = nullptr;      // Cholesky status (0 or 1+failing row)
+  // tcgen05 operands (fp32 mode): TF32-rounded hi/lo planes of L^-1, stacked [2*n_cap][n_cap]
+  float* d_planes = nullptr;
+  float* d_alpha_f32 = nullptr;  // [n_cap]
+  float* d_obs_f32 = nullptr;    // unused by default
+  void* tmap_planes = nullptr;   // host copy of the CUtensorMap (128 B), 256-row box
+  bool planes_valid = false;
+
+  // posterior of the last step (this shard)
+  void* d_mu = nullptr;      // [max_cells] float or double
+  void* d_s2 = nullptr;      // [max_cells]
+  uint8_t* d_mask = nullptr; // [max_cells]
+  double* d_mu64 = nullptr;  // compute_sets staging (lazy) [max_cells]
+  double* d_std64 = nullptr;
+  double* d_q0 = nullptr;
+  double* d_q1 = nullptr;
+  sbo::PosteriorSource source = sbo::PosteriorSource::kNone;
+  int64_t source_m = 0;
+  double last_beta = 0.0;
+  bool posterior_valid = false;  // mu/s2 hold a full posterior for n_prev or n observations
+  int posterior_n = 0;           // number of observations that posterior was computed with
+
+  // reduction scratch
+  sbo::SetsResult* d_partials = nullptr;  // [grid]
+  sbo::SetsResult* d_result = nullptr;    // [1] (+ gathered [world])
+  unsigned int* d_ticket = nullptr;
+  sbo::SetsResult* h_result = nullptr;    // pinned
+  int32_t* d_frontier = nullptr;          // select scratch (lazy)
+  unsigned long long* d_sel_keys = nullptr;
+  double* d_sel_width = nullptr;
+  int64_t sel_cap = 0;
+  int32_t* h_sel_out = nullptr;  // pinned
+  int32_t* d_sel_out = nullptr;
+
+  // communicator
+  void* nccl_comm = nullptr;
+  int rank = 0, world = 1;
+  sbo::SetsResult* d_gather = nullptr;  // [world]
+  sbo::SetsResult* h_gather = nullptr;  // pinned [world]
+};
+
+namespace sbo {
+
+int32_t fail(sbo_ctx* ctx, int32_t status, const std::string& msg);
+int32_t cuda_fail(sbo_ctx* ctx, cudaError_t e, const char* what);
+
+#define SBO_CUDA(ctx, call)                                        \
+  do {                                                             \
+    cudaError_t e__ = (call);                                      \
+    if (e__ != cudaSuccess) return sbo::cuda_fail(ctx, e__, #call); \
+  } while (0)
+
+#define SBO_TRY(call)                  \
+  do {                                 \
+    int32_t s__ = (call);              \
+    if (s__ != SBO_OK) return s__;     \
+  } while (0)
+
+#define SBO_LAUNCH_CHECK(ctx, name)                                   \
+  do {                                                                \
+    (ctx)->launches++;                                                \
+    cudaError_t e__ = cudaGetLastError();                             \
+    if (e__ != cudaSuccess) return sbo::cuda_fail(ctx, e__, name);    \
+  } while (0)
+
+// ---- entry points of the individual translation units ----------------------
+
+// sets.cu
+int32_t launch_sets_step(sbo_ctx* ctx, double beta, double f_min);                       // mu/s2 -> mask, result
+int32_t launch_sets_arrays(sbo_ctx* ctx, const double* d_mu, const double* d_std, int64_t m, double beta,
+                           double f_min, uint8_t* d_mask, double* d_q0, double* d_q1);   // fp64 mu/std
+int sets_grid_size(const sbo_ctx* ctx);
+
+// select.cu
+int32_t launch_select(sbo_ctx* ctx, const int32_t* d_frontier, int64_t F, double gx, double gy);
+
+// factor.cu
+int32_t factor_full(sbo_ctx* ctx);                 // d_xy, d_r, n -> d_A (L), d_Linv, d_alpha, planes
+int32_t factor_append(sbo_ctx* ctx, int k);        // rows [n, n+k) already in d_xy / d_r
+int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end);
+
+// posterior_simt.cu
+int32_t launch_posterior_simt(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
+
+// posterior_tc.cu
+int32_t tc_init(sbo_ctx* ctx);                     // tensor map, attributes; sets ctx->tc_ok
+int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
+void tc_destroy(sbo_ctx* ctx);
+
+// comm.cu
+int32_t comm_gather_reduce(sbo_ctx* ctx);          // d_result -> d_result (global), over all ranks
+
+// ---- device helpers ---------------------------------------------------------
+
+#ifdef __CUDACC__
+// Cell coordinate exactly as the oracle computes it: product and sum rounded
+// separately (no FMA contraction).
+__device__ __forceinline__ double cell_coord(double origin, double pitch, int i) {
+  return __dadd_rn(origin, __dmul_rn((double)i, pitch));
+}
+
+// Total order of the argmax: larger value first, then lower index.
+__device__ __forceinline__ bool better(double v, long long i, double bv, long long bi) {
+  return i >= 0 && (bi < 0 || v > bv || (v == bv && i < bi));
+}
+#endif
+
+}  // namespace sbo

@@ -1,0 +1,279 @@
+// sets.cu -- fused confidence interval + safe mask + argmax pass.
+//
+// Replaces OptimizerNode::ComputeConfidenceIntervals / UpdateSafeSet
+// (reference src/safe_bayesian_optimization_node.cpp:409-416) and the
+// rasterise loop that turns S_ into a 0/255 image (:444-456):
+//     conf = beta * sigma ; Q0 = mu - conf ; Q1 = mu + conf ; S = Q0 > f_min
+// All interval arithmetic is fp64 with every product/sum rounded on its own
+// (__dmul_rn/__dsub_rn/__dadd_rn are never contracted into FMAs), so that on
+// fp64 inputs the result is bit-identical to the reference's Eigen code built
+// for baseline x86-64.
+//
+// HBM-bound: reads mu + sigma^2 (2*sizeof(T) per cell), writes 1 mask byte.
+// Each thread handles 4 consecutive cells per access (16 B loads in fp32,
+// 2x16 B in fp64, one 4-byte mask store => a warp stores 128 contiguous
+// bytes), several independent accesses in flight per thread; argmax is a
+// warp-shuffle -> block -> last-block-done grid reduction on (value, index)
+// records ordered (value desc, index asc).
+#include "common.cuh"
+
+namespace sbo {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kUnroll = 4;  // independent quads in flight per thread
+
+struct Best {
+  double v;
+  long long i;
+};
+
+__device__ __forceinline__ void merge(Best& a, double v, long long i) {
+  if (better(v, i, a.v, a.i)) {
+    a.v = v;
+    a.i = i;
+  }
+}
+
+__device__ __forceinline__ Best shfl_down(const Best& b, int d) {
+  Best o;
+  o.v = __shfl_down_sync(0xffffffffu, b.v, d);
+  o.i = __shfl_down_sync(0xffffffffu, b.i, d);
+  return o;
+}
+
+struct Acc {
+  Best ucb{0.0, -1};
+  Best wid{0.0, -1};
+  long long safe = 0;
+  long long clamped = 0;
+};
+
+// One cell.  kStd: `s` is already a standard deviation (reference's std_);
+// otherwise it is a variance: clamp at 0, add the noise term, take the root.
+template <bool kStd>
+__device__ __forceinline__ uint32_t eval_cell(double mu, double s, double beta, double f_min, double noise_add,
+                                              long long idx, Acc& acc, double& q0, double& q1) {
+  double sd;
+  if (kStd) {
+    sd = s;
+  } else {
+    double v = s;
+    if (v < 0.0) {
+      v = 0.0;
+      acc.clamped++;
+    }
+    v = __dadd_rn(v, noise_add);
+    sd = __dsqrt_rn(v);
+  }
+  const double conf = __dmul_rn(beta, sd);  // :412
+  q0 = __dsub_rn(mu, conf);                 // :414
+  q1 = __dadd_rn(mu, conf);                 // :415
+  const bool safe = q0 > f_min;             // :409 (strict; NaN -> false)
+  if (safe) {
+    acc.safe++;
+    // indices grow within a thread, so strict > keeps the lowest index on ties
+    if (acc.ucb.i < 0 || q1 > acc.ucb.v) {
+      acc.ucb.v = q1;
+      acc.ucb.i = idx;
+    }
+    const double w = __dsub_rn(q1, q0);  // :516
+    if (acc.wid.i < 0 || w > acc.wid.v) {
+      acc.wid.v = w;
+      acc.wid.i = idx;
+    }
+  }
+  return safe ? 0xFFu : 0u;
+}
+
+template <typename T>
+struct Quad;  // 4 consecutive values
+template <>
+struct Quad<float> {
+  float4 a;
+  __device__ __forceinline__ void load(const float* p) { a = __ldcs(reinterpret_cast<const float4*>(p)); }
+  __device__ __forceinline__ double get(int i) const { return i == 0 ? a.x : i == 1 ? a.y : i == 2 ? a.z : a.w; }
+};
+template <>
+struct Quad<double> {
+  double2 a, b;
+  __device__ __forceinline__ void load(const double* p) {
+    a = __ldcs(reinterpret_cast<const double2*>(p));
+    b = __ldcs(reinterpret_cast<const double2*>(p) + 1);
+  }
+  __device__ __forceinline__ double get(int i) const { return i == 0 ? a.x : i == 1 ? a.y : i == 2 ? b.x : b.y; }
+};
+
+__device__ __forceinline__ void store_q(double* q, long long base, double v0, double v1, double v2, double v3) {
+  __stcs(reinterpret_cast<double2*>(q + base), make_double2(v0, v1));
+  __stcs(reinterpret_cast<double2*>(q + base) + 1, make_double2(v2, v3));
+}
+
+template <typename T, bool kStd, bool kVec>
+__global__ void __launch_bounds__(kThreads)
+sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long long cell0, double beta, double f_min,
+            double noise_add, uint8_t* __restrict__ mask, double* __restrict__ q0out, double* __restrict__ q1out,
+            SetsResult* __restrict__ partials, SetsResult* __restrict__ result, unsigned int* __restrict__ ticket) {
+  Acc acc;
+  const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
+  const long long nthreads = (long long)gridDim.x * kThreads;
+
+  if (kVec) {
+    const long long nquads = m >> 2;
+    for (long long q = tid; q < nquads; q += nthreads * kUnroll) {
+      Quad<T> qm[kUnroll], qs[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long qq = q + (long long)u * nthreads;
+        if (qq < nquads) {
+          qm[u].load(mu + (qq << 2));
+          qs[u].load(s + (qq << 2));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long qq = q + (long long)u * nthreads;
+        if (qq < nquads) {
+          const long long base = qq << 2;
+          double a0[4], a1[4];
+          uint32_t bytes = 0;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            bytes |= eval_cell<kStd>(qm[u].get(e), qs[u].get(e), beta, f_min, noise_add, cell0 + base + e, acc, a0[e],
+                                     a1[e])
+                     << (8 * e);
+          }
+          __stcs(reinterpret_cast<unsigned int*>(mask + base), bytes);
+          if (q0out) store_q(q0out, base, a0[0], a0[1], a0[2], a0[3]);
+          if (q1out) store_q(q1out, base, a1[0], a1[1], a1[2], a1[3]);
+        }
+      }
+    }
+    // tail (m % 4 cells)
+    const long long tail0 = (m >> 2) << 2;
+    if (tid < m - tail0) {
+      const long long c = tail0 + tid;
+      double a0, a1;
+      const uint32_t b = eval_cell<kStd>((double)mu[c], (double)s[c], beta, f_min, noise_add, cell0 + c, acc, a0, a1);
+      mask[c] = (uint8_t)b;
+      if (q0out) q0out[c] = a0;
+      if (q1out) q1out[c] = a1;
+    }
+  } else {
+    for (long long c = tid; c < m; c += nthreads) {
+      double a0, a1;
+      const uint32_t b = eval_cell<kStd>((double)mu[c], (double)s[c], beta, f_min, noise_add, cell0 + c, acc, a0, a1);
+      mask[c] = (uint8_t)b;
+      if (q0out) q0out[c] = a0;
+      if (q1out) q1out[c] = a1;
+    }
+  }
+
+  // ---- warp -> block -> grid reduction -------------------------------------
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    Best u = shfl_down(acc.ucb, d), w = shfl_down(acc.wid, d);
+    merge(acc.ucb, u.v, u.i);
+    merge(acc.wid, w.v, w.i);
+    acc.safe += __shfl_down_sync(0xffffffffu, acc.safe, d);
+    acc.clamped += __shfl_down_sync(0xffffffffu, acc.clamped, d);
+  }
+  __shared__ SetsResult warp_res[kThreads / 32];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) warp_res[warp] = SetsResult{acc.ucb.v, acc.ucb.i, acc.wid.v, acc.wid.i, acc.safe, acc.clamped};
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    SetsResult r = warp_res[0];
+    for (int w = 1; w < kThreads / 32; ++w) {
+      const SetsResult o = warp_res[w];
+      if (better(o.ucb_val, o.ucb_idx, r.ucb_val, r.ucb_idx)) { r.ucb_val = o.ucb_val; r.ucb_idx = o.ucb_idx; }
+      if (better(o.width_val, o.width_idx, r.width_val, r.width_idx)) { r.width_val = o.width_val; r.width_idx = o.width_idx; }
+      r.safe_count += o.safe_count;
+      r.clamped += o.clamped;
+    }
+    partials[blockIdx.x] = r;
+    __threadfence();
+    const unsigned int t = atomicAdd(ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  // last block: fold all per-block records
+  Acc tot;
+  for (int b = threadIdx.x; b < (int)gridDim.x; b += kThreads) {
+    const SetsResult o = partials[b];
+    merge(tot.ucb, o.ucb_val, o.ucb_idx);
+    merge(tot.wid, o.width_val, o.width_idx);
+    tot.safe += o.safe_count;
+    tot.clamped += o.clamped;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    Best u = shfl_down(tot.ucb, d), w = shfl_down(tot.wid, d);
+    merge(tot.ucb, u.v, u.i);
+    merge(tot.wid, w.v, w.i);
+    tot.safe += __shfl_down_sync(0xffffffffu, tot.safe, d);
+    tot.clamped += __shfl_down_sync(0xffffffffu, tot.clamped, d);
+  }
+  __syncthreads();  // warp_res reuse
+  if (lane == 0) warp_res[warp] = SetsResult{tot.ucb.v, tot.ucb.i, tot.wid.v, tot.wid.i, tot.safe, tot.clamped};
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    SetsResult r = warp_res[0];
+    for (int w = 1; w < kThreads / 32; ++w) {
+      const SetsResult o = warp_res[w];
+      if (better(o.ucb_val, o.ucb_idx, r.ucb_val, r.ucb_idx)) { r.ucb_val = o.ucb_val; r.ucb_idx = o.ucb_idx; }
+      if (better(o.width_val, o.width_idx, r.width_val, r.width_idx)) { r.width_val = o.width_val; r.width_idx = o.width_idx; }
+      r.safe_count += o.safe_count;
+      r.clamped += o.clamped;
+    }
+    *result = r;
+    *ticket = 0;  // ready for the next launch
+  }
+}
+
+template <typename T, bool kStd>
+int32_t launch(sbo_ctx* ctx, const T* mu, const T* s, int64_t m, int64_t cell0, double beta, double f_min,
+               double noise_add, uint8_t* mask, double* q0, double* q1) {
+  auto aligned = [](const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
+  const bool vec = aligned(mu, 16) && aligned(s, 16) && aligned(mask, 4) && (!q0 || aligned(q0, 16)) &&
+                   (!q1 || aligned(q1, 16));
+  const int64_t work = vec ? (m + 3) / 4 : m;
+  int64_t blocks = (work + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll);
+  const int64_t cap = sets_grid_size(ctx);
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  if (vec) {
+    sets_kernel<T, kStd, true><<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(
+        mu, s, m, cell0, beta, f_min, noise_add, mask, q0, q1, ctx->d_partials, ctx->d_result, ctx->d_ticket);
+  } else {
+    sets_kernel<T, kStd, false><<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(
+        mu, s, m, cell0, beta, f_min, noise_add, mask, q0, q1, ctx->d_partials, ctx->d_result, ctx->d_ticket);
+  }
+  SBO_LAUNCH_CHECK(ctx, "sets_kernel");
+  return SBO_OK;
+}
+
+}  // namespace
+
+int sets_grid_size(const sbo_ctx* ctx) { return ctx->sm_count * 8; }  // 8 x 256 threads resident per SM
+
+int32_t launch_sets_step(sbo_ctx* ctx, double beta, double f_min) {
+  const double noise_add = ctx->cfg.include_noise_in_sigma ? ctx->cfg.noise_var : 0.0;
+  if (ctx->cfg.precision == SBO_FP64) {
+    return launch<double, false>(ctx, static_cast<const double*>(ctx->d_mu), static_cast<const double*>(ctx->d_s2),
+                                 ctx->m_local, ctx->cell0, beta, f_min, noise_add, ctx->d_mask, nullptr, nullptr);
+  }
+  return launch<float, false>(ctx, static_cast<const float*>(ctx->d_mu), static_cast<const float*>(ctx->d_s2),
+                              ctx->m_local, ctx->cell0, beta, f_min, noise_add, ctx->d_mask, nullptr, nullptr);
+}
+
+int32_t launch_sets_arrays(sbo_ctx* ctx, const double* d_mu, const double* d_std, int64_t m, double beta, double f_min,
+                           uint8_t* d_mask, double* d_q0, double* d_q1) {
+  return launch<double, true>(ctx, d_mu, d_std, m, 0, beta, f_min, 0.0, d_mask, d_q0, d_q1);
+}
+
+}  // namespace sbo
