@@ -1,0 +1,543 @@
+// api.cu -- the C-ABI of include/sbo.h: context life cycle, host<->device plumbing and the
+// sequencing of the kernels of one BO step.  No arithmetic of the path lives here.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+
+namespace sbo {
+
+static thread_local std::string g_create_error;
+
+int32_t fail(sbo_ctx* ctx, int32_t status, const std::string& msg) {
+  if (ctx) ctx->err = msg;
+  else g_create_error = msg;
+  return status;
+}
+
+int32_t cuda_fail(sbo_ctx* ctx, cudaError_t e, const char* what) {
+  return fail(ctx, SBO_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+namespace {
+
+size_t elem_size(const sbo_ctx* ctx) { return ctx->cfg.precision == SBO_FP64 ? sizeof(double) : sizeof(float); }
+
+bool all_finite(const double* p, size_t count) {
+  for (size_t i = 0; i < count; ++i)
+    if (!std::isfinite(p[i])) return false;
+  return true;
+}
+
+void free_all(sbo_ctx* c) {
+  tc_destroy(c);
+  void* dev[] = {c->d_xy, c->d_r, c->d_A, c->d_Linv, c->d_Dinv, c->d_alpha, c->d_w, c->d_small, c->d_info,
+                 c->d_planes, c->d_alpha_f32, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
+                 c->d_partials, c->d_result, c->d_ticket, c->d_frontier, c->d_sel_keys, c->d_sel_width, c->d_sel_out,
+                 c->d_gather};
+  for (void* p : dev)
+    if (p) cudaFree(p);
+  if (c->h_result) cudaFreeHost(c->h_result);
+  if (c->h_sel_out) cudaFreeHost(c->h_sel_out);
+  for (auto& e : c->ev)
+    if (e) cudaEventDestroy(e);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+}
+
+// Which posterior kernel runs for this context.
+int32_t pick_kernel(sbo_ctx* ctx, int* which) {
+  if (ctx->cfg.precision == SBO_FP64 || ctx->cfg.kernel == SBO_KERNEL_SIMT) {
+    *which = SBO_KERNEL_SIMT;
+    return SBO_OK;
+  }
+  if (!ctx->tc_ok)
+    return fail(ctx, SBO_ERR_STATE, "tcgen05 posterior kernel unavailable on this device/driver (no fallback in fp32 mode; "
+                                    "set kernel = SBO_KERNEL_SIMT explicitly to use the FMA kernel)");
+  *which = SBO_KERNEL_TCGEN05;
+  return SBO_OK;
+}
+
+void fill_out(const sbo_ctx* ctx, const SetsResult& r, int kernel_used, const float* ms, sbo_step_out* out) {
+  std::memset(out, 0, sizeof(*out));
+  out->n_cells = ctx->source == PosteriorSource::kHostArrays ? ctx->source_m : ctx->m_local;
+  out->safe_count = r.safe_count;
+  out->argmax_ucb.idx = r.ucb_idx;
+  out->argmax_ucb.value = r.ucb_idx >= 0 ? r.ucb_val : 0.0;
+  out->argmax_width.idx = r.width_idx;
+  out->argmax_width.value = r.width_idx >= 0 ? r.width_val : 0.0;
+  out->clamped_sigma2 = r.clamped;
+  out->n_obs = ctx->n;
+  out->kernel_used = kernel_used;
+  out->ms_posterior = ms[0];
+  out->ms_sets = ms[1];
+  out->ms_comm = ms[2];
+  out->ms_total = ms[3];
+}
+
+// posterior (full or incremental) + sets + collective, all on ctx->stream; events around each phase.
+int32_t run_step(sbo_ctx* ctx, double beta, double f_min, bool incremental, int* kernel_used) {
+  if (!ctx->grid_set) return fail(ctx, SBO_ERR_STATE, "sbo_step: grid not set (call sbo_set_grid)");
+  if (!(std::isfinite(beta) && std::isfinite(f_min))) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_step: beta/f_min not finite");
+  int which = 0;
+  SBO_TRY(pick_kernel(ctx, &which));
+  int j_lo = 0, j_hi = ctx->n;
+  bool accumulate = false;
+  if (incremental) {
+    if (!ctx->posterior_valid || ctx->posterior_n > ctx->n)
+      return fail(ctx, SBO_ERR_STATE, "sbo_step_incremental: no previous posterior on this grid for a prefix of the observations");
+    j_lo = ctx->posterior_n;
+    accumulate = true;
+  }
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+  if (which == SBO_KERNEL_TCGEN05) SBO_TRY(launch_posterior_tc(ctx, j_lo, j_hi, accumulate));
+  else SBO_TRY(launch_posterior_simt(ctx, j_lo, j_hi, accumulate));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  SBO_TRY(launch_sets_step(ctx, beta, f_min));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+  SBO_TRY(comm_gather_reduce(ctx));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+  ctx->source = PosteriorSource::kStep;
+  ctx->last_beta = beta;
+  ctx->posterior_valid = true;
+  ctx->posterior_n = ctx->n;
+  *kernel_used = which;
+  return SBO_OK;
+}
+
+int32_t finish_step(sbo_ctx* ctx, int kernel_used, sbo_step_out* out) {
+  SBO_CUDA(ctx, cudaMemcpyAsync(ctx->h_result, ctx->d_result, sizeof(SetsResult), cudaMemcpyDeviceToHost, ctx->stream));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream));
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (out) {
+    float ms[4] = {0, 0, 0, 0};
+    cudaEventElapsedTime(&ms[0], ctx->ev[0], ctx->ev[1]);
+    cudaEventElapsedTime(&ms[1], ctx->ev[1], ctx->ev[2]);
+    cudaEventElapsedTime(&ms[2], ctx->ev[2], ctx->ev[3]);
+    cudaEventElapsedTime(&ms[3], ctx->ev[0], ctx->ev[4]);
+    fill_out(ctx, *ctx->h_result, kernel_used, ms, out);
+  }
+  return SBO_OK;
+}
+
+}  // namespace
+}  // namespace sbo
+
+using namespace sbo;
+
+extern "C" {
+
+int32_t sbo_abi_version(void) { return SBO_ABI_VERSION; }
+
+const char* sbo_status_string(int32_t s) {
+  switch (s) {
+    case SBO_OK: return "ok";
+    case SBO_ERR_INVALID_ARG: return "invalid argument";
+    case SBO_ERR_NO_DEVICE: return "no sm_100 CUDA device";
+    case SBO_ERR_CUDA: return "CUDA error";
+    case SBO_ERR_NOT_POSDEF: return "covariance not positive definite";
+    case SBO_ERR_CAPACITY: return "capacity exceeded";
+    case SBO_ERR_STATE: return "call out of order";
+    case SBO_ERR_COMM: return "communicator error";
+    default: return "unknown status";
+  }
+}
+
+const char* sbo_last_error(const sbo_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int32_t sbo_create(const sbo_config* cfg, sbo_ctx** out) {
+  if (!cfg || !out) return fail(nullptr, SBO_ERR_INVALID_ARG, "sbo_create: null argument");
+  *out = nullptr;
+  if (!(cfg->sigma_f > 0.0 && cfg->length_scale > 0.0 && cfg->noise_var >= 0.0 && std::isfinite(cfg->prior_mean) &&
+        std::isfinite(cfg->sigma_f) && std::isfinite(cfg->length_scale) && std::isfinite(cfg->noise_var)))
+    return fail(nullptr, SBO_ERR_INVALID_ARG, "sbo_create: sigma_f, length_scale must be > 0, noise_var >= 0, all finite");
+  if (cfg->precision != SBO_FP32 && cfg->precision != SBO_FP64)
+    return fail(nullptr, SBO_ERR_INVALID_ARG, "sbo_create: precision must be SBO_FP32 or SBO_FP64");
+  if (cfg->kernel < SBO_KERNEL_AUTO || cfg->kernel > SBO_KERNEL_TCGEN05 ||
+      (cfg->kernel == SBO_KERNEL_TCGEN05 && cfg->precision != SBO_FP32))
+    return fail(nullptr, SBO_ERR_INVALID_ARG, "sbo_create: bad kernel choice (tcgen05 is fp32-mode only)");
+  if (cfg->max_obs < 1 || cfg->max_cells < 1) return fail(nullptr, SBO_ERR_INVALID_ARG, "sbo_create: max_obs and max_cells must be >= 1");
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+    return fail(nullptr, SBO_ERR_NO_DEVICE, "sbo_create: no CUDA device (this library has no CPU fallback)");
+  if (cfg->device < 0 || cfg->device >= count) return fail(nullptr, SBO_ERR_INVALID_ARG, "sbo_create: device ordinal out of range");
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, cfg->device) != cudaSuccess || prop.major != 10)
+    return fail(nullptr, SBO_ERR_NO_DEVICE, "sbo_create: device is not compute capability 10.x (built for sm_100a only)");
+
+  sbo_ctx* c = new (std::nothrow) sbo_ctx();
+  if (!c) return fail(nullptr, SBO_ERR_CUDA, "sbo_create: out of host memory");
+  c->cfg = *cfg;
+  c->device = cfg->device;
+  c->sm_count = prop.multiProcessorCount;
+  c->n_cap = (cfg->max_obs + kObsPad - 1) / kObsPad * kObsPad;
+  const size_t nc = (size_t)c->n_cap, es = elem_size(c), mc = (size_t)cfg->max_cells;
+
+#define CREATE_CUDA(call)                                               \
+  do {                                                                  \
+    cudaError_t e__ = (call);                                           \
+    if (e__ != cudaSuccess) {                                           \
+      fail(nullptr, SBO_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+      free_all(c);                                                      \
+      delete c;                                                         \
+      return SBO_ERR_CUDA;                                              \
+    }                                                                   \
+  } while (0)
+
+  CREATE_CUDA(cudaSetDevice(c->device));
+  CREATE_CUDA(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
+  for (auto& e : c->ev) CREATE_CUDA(cudaEventCreate(&e));
+  CREATE_CUDA(cudaMalloc(&c->d_xy, sizeof(double) * 2 * nc));
+  CREATE_CUDA(cudaMalloc(&c->d_r, sizeof(double) * nc));
+  CREATE_CUDA(cudaMalloc(&c->d_A, sizeof(double) * nc * nc));
+  CREATE_CUDA(cudaMalloc(&c->d_Linv, sizeof(double) * nc * nc));
+  CREATE_CUDA(cudaMalloc(&c->d_Dinv, sizeof(double) * nc * kFactorNB));
+  CREATE_CUDA(cudaMalloc(&c->d_alpha, sizeof(double) * nc));
+  CREATE_CUDA(cudaMalloc(&c->d_w, sizeof(double) * nc));
+  CREATE_CUDA(cudaMalloc(&c->d_small, sizeof(double) * (2 * (size_t)kMaxAppend * nc + 2 * (size_t)kMaxAppend * kMaxAppend)));
+  CREATE_CUDA(cudaMalloc(&c->d_info, sizeof(int)));
+  CREATE_CUDA(cudaMemset(c->d_Linv, 0, sizeof(double) * nc * nc));
+  CREATE_CUDA(cudaMemset(c->d_alpha, 0, sizeof(double) * nc));
+  CREATE_CUDA(cudaMemset(c->d_xy, 0, sizeof(double) * 2 * nc));
+  if (cfg->precision == SBO_FP32) {
+    CREATE_CUDA(cudaMalloc(&c->d_planes, sizeof(float) * 2 * nc * nc));
+    CREATE_CUDA(cudaMemset(c->d_planes, 0, sizeof(float) * 2 * nc * nc));
+    CREATE_CUDA(cudaMalloc(&c->d_alpha_f32, sizeof(float) * nc));
+    CREATE_CUDA(cudaMemset(c->d_alpha_f32, 0, sizeof(float) * nc));
+  }
+  CREATE_CUDA(cudaMalloc(&c->d_mu, es * mc));
+  CREATE_CUDA(cudaMalloc(&c->d_s2, es * mc));
+  CREATE_CUDA(cudaMalloc(&c->d_mask, mc + 16));
+  CREATE_CUDA(cudaMalloc(&c->d_partials, sizeof(SetsResult) * (size_t)sets_grid_size(c)));
+  CREATE_CUDA(cudaMalloc(&c->d_result, sizeof(SetsResult)));
+  CREATE_CUDA(cudaMalloc(&c->d_ticket, sizeof(unsigned int)));
+  CREATE_CUDA(cudaMemset(c->d_ticket, 0, sizeof(unsigned int)));
+  CREATE_CUDA(cudaMalloc(&c->d_sel_out, sizeof(int32_t)));
+  CREATE_CUDA(cudaMallocHost(&c->h_result, sizeof(SetsResult)));
+  CREATE_CUDA(cudaMallocHost(&c->h_sel_out, sizeof(int32_t)));
+#undef CREATE_CUDA
+
+  if (cfg->precision == SBO_FP32 && cfg->kernel != SBO_KERNEL_SIMT) {
+    const int32_t st = tc_init(c);
+    if (st != SBO_OK && cfg->kernel == SBO_KERNEL_TCGEN05) {
+      g_create_error = c->err;
+      free_all(c);
+      delete c;
+      return st;
+    }
+  }
+  *out = c;
+  return SBO_OK;
+}
+
+int32_t sbo_destroy(sbo_ctx* ctx) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  if (ctx->nccl_comm) sbo_comm_destroy(ctx);
+  free_all(ctx);
+  delete ctx;
+  return SBO_OK;
+}
+
+int32_t sbo_set_stream(sbo_ctx* ctx, void* cuda_stream) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  cudaStreamSynchronize(ctx->stream);
+  ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  return SBO_OK;
+}
+
+int32_t sbo_synchronize(sbo_ctx* ctx) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SBO_OK;
+}
+
+int32_t sbo_set_grid(sbo_ctx* ctx, double x0, double y0, double rx, double ry, int32_t W, int32_t H, int32_t row0,
+                     int32_t row1) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (!(std::isfinite(x0) && std::isfinite(y0) && std::isfinite(rx) && std::isfinite(ry)) || W < 1 || H < 1 || row0 < 0 ||
+      row1 < row0 || row1 > H)
+    return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_grid: need finite origin/pitch, W,H >= 1, 0 <= row0 <= row1 <= H");
+  const int64_t m_local = (int64_t)(row1 - row0) * W;
+  if (m_local > ctx->cfg.max_cells) return fail(ctx, SBO_ERR_CAPACITY, "sbo_set_grid: shard has more cells than max_cells");
+  ctx->x0 = x0; ctx->y0 = y0; ctx->rx = rx; ctx->ry = ry;
+  ctx->W = W; ctx->H = H; ctx->row0 = row0; ctx->row1 = row1;
+  ctx->cell0 = (int64_t)row0 * W;
+  ctx->m_local = m_local;
+  ctx->grid_set = true;
+  ctx->posterior_valid = false;
+  ctx->source = PosteriorSource::kNone;
+  return SBO_OK;
+}
+
+int32_t sbo_num_observations(const sbo_ctx* ctx) { return ctx ? ctx->n : SBO_ERR_INVALID_ARG; }
+
+int64_t sbo_launch_count(const sbo_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int32_t sbo_device_info(const sbo_ctx* ctx, int32_t* sm_count, int32_t* tcgen05_ok) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (sm_count) *sm_count = ctx->sm_count;
+  if (tcgen05_ok) *tcgen05_ok = ctx->tc_ok ? 1 : 0;
+  return SBO_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// observations
+// ---------------------------------------------------------------------------------------------
+extern "C" {
+
+int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, int32_t n) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (n < 0 || (n > 0 && (!xy || !y))) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_observations: null input or n < 0");
+  if (n > ctx->n_cap || n > ctx->cfg.max_obs) return fail(ctx, SBO_ERR_CAPACITY, "sbo_set_observations: n exceeds max_obs");
+  if (!all_finite(xy, 2 * (size_t)n) || !all_finite(y, (size_t)n))
+    return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_observations: NaN/Inf in the observations");
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  std::vector<double> r((size_t)n);
+  for (int i = 0; i < n; ++i) r[i] = y[i] - ctx->cfg.prior_mean;
+  if (n > 0) {
+    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_xy, xy, sizeof(double) * 2 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_r, r.data(), sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // r is a local
+  }
+  ctx->n = n;
+  ctx->posterior_valid = false;
+  const int32_t st = factor_full(ctx);
+  if (st != SBO_OK) {
+    ctx->n = 0;  // the factor buffers were overwritten: no observations until the next successful fit
+    cudaMemsetAsync(ctx->d_Linv, 0, sizeof(double) * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
+    cudaMemsetAsync(ctx->d_alpha, 0, sizeof(double) * (size_t)ctx->n_cap, ctx->stream);
+    if (ctx->d_planes) cudaMemsetAsync(ctx->d_planes, 0, sizeof(float) * 2 * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
+    if (ctx->d_alpha_f32) cudaMemsetAsync(ctx->d_alpha_f32, 0, sizeof(float) * (size_t)ctx->n_cap, ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
+    return st;
+  }
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SBO_OK;
+}
+
+int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y, int32_t k) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (k < 0 || (k > 0 && (!xy || !y))) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_append_observations: null input or k < 0");
+  if ((int64_t)ctx->n + k > ctx->cfg.max_obs) return fail(ctx, SBO_ERR_CAPACITY, "sbo_append_observations: n + k exceeds max_obs");
+  if (!all_finite(xy, 2 * (size_t)k) || !all_finite(y, (size_t)k))
+    return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_append_observations: NaN/Inf in the observations");
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  std::vector<double> r((size_t)k);
+  for (int i = 0; i < k; ++i) r[i] = y[i] - ctx->cfg.prior_mean;
+  for (int done = 0; done < k;) {
+    const int kk = std::min(k - done, (int)kMaxAppend);
+    const int n = ctx->n;
+    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_xy + 2 * (size_t)n, xy + 2 * (size_t)done, sizeof(double) * 2 * (size_t)kk,
+                                  cudaMemcpyHostToDevice, ctx->stream));
+    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_r + n, r.data() + done, sizeof(double) * (size_t)kk, cudaMemcpyHostToDevice,
+                                  ctx->stream));
+    SBO_TRY(factor_append(ctx, kk));  // on failure n is unchanged: rows >= n of L^-1 are not part of the state
+    ctx->n = n + kk;
+    done += kk;
+  }
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SBO_OK;
+}
+
+int32_t sbo_copy_linv(sbo_ctx* ctx, double* host_dst) {
+  if (!ctx || !host_dst) return SBO_ERR_INVALID_ARG;
+  const size_t n = (size_t)ctx->n;
+  if (n == 0) return SBO_OK;
+  SBO_CUDA(ctx, cudaMemcpy2DAsync(host_dst, n * sizeof(double), ctx->d_Linv, (size_t)ctx->n_cap * sizeof(double),
+                                  n * sizeof(double), n, cudaMemcpyDeviceToHost, ctx->stream));
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SBO_OK;
+}
+
+int32_t sbo_copy_alpha(sbo_ctx* ctx, double* host_dst) {
+  if (!ctx || !host_dst) return SBO_ERR_INVALID_ARG;
+  if (ctx->n == 0) return SBO_OK;
+  SBO_CUDA(ctx, cudaMemcpyAsync(host_dst, ctx->d_alpha, sizeof(double) * (size_t)ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SBO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// the BO step
+// ---------------------------------------------------------------------------------------------
+static int32_t step_common(sbo_ctx* ctx, double beta, double f_min, uint8_t* mask_host, sbo_step_out* out, bool incremental) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  int used = 0;
+  SBO_TRY(run_step(ctx, beta, f_min, incremental, &used));
+  if (mask_host && ctx->m_local > 0)
+    SBO_CUDA(ctx, cudaMemcpyAsync(mask_host, ctx->d_mask, (size_t)ctx->m_local, cudaMemcpyDeviceToHost, ctx->stream));
+  return finish_step(ctx, used, out);
+}
+
+int32_t sbo_step(sbo_ctx* ctx, double beta, double f_min, uint8_t* mask_host, sbo_step_out* out) {
+  return step_common(ctx, beta, f_min, mask_host, out, false);
+}
+
+int32_t sbo_step_incremental(sbo_ctx* ctx, double beta, double f_min, uint8_t* mask_host, sbo_step_out* out) {
+  return step_common(ctx, beta, f_min, mask_host, out, true);
+}
+
+int32_t sbo_step_device(sbo_ctx* ctx, double beta, double f_min, sbo_step_out* out) {
+  return step_common(ctx, beta, f_min, nullptr, out, false);
+}
+
+static int32_t ensure_array_staging(sbo_ctx* ctx, int64_t m) {
+  if (ctx->d_mu64 && ctx->stage_cap >= m) return SBO_OK;
+  for (double** p : {&ctx->d_mu64, &ctx->d_std64, &ctx->d_q0, &ctx->d_q1}) {
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    SBO_CUDA(ctx, cudaMalloc(p, sizeof(double) * (size_t)(m > 0 ? m : 1)));
+  }
+  ctx->stage_cap = m;
+  return SBO_OK;
+}
+
+int32_t sbo_compute_sets(sbo_ctx* ctx, const double* mu, const double* std_dev, int64_t m, double beta, double f_min,
+                         uint8_t* mask_host, double* q0, double* q1, sbo_step_out* out) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (m < 0 || (m > 0 && (!mu || !std_dev))) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_compute_sets: null input or m < 0");
+  if (m > ctx->cfg.max_cells) return fail(ctx, SBO_ERR_CAPACITY, "sbo_compute_sets: m exceeds max_cells");
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  SBO_TRY(ensure_array_staging(ctx, m));
+  ctx->source = PosteriorSource::kHostArrays;
+  ctx->source_m = m;
+  ctx->last_beta = beta;
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+  if (m > 0) {
+    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_mu64, mu, sizeof(double) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
+    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_std64, std_dev, sizeof(double) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
+  }
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  SBO_TRY(launch_sets_arrays(ctx, ctx->d_mu64, ctx->d_std64, m, beta, f_min, ctx->d_mask, q0 ? ctx->d_q0 : nullptr,
+                             q1 ? ctx->d_q1 : nullptr));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+  if (m > 0) {
+    if (mask_host) SBO_CUDA(ctx, cudaMemcpyAsync(mask_host, ctx->d_mask, (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
+    if (q0) SBO_CUDA(ctx, cudaMemcpyAsync(q0, ctx->d_q0, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
+    if (q1) SBO_CUDA(ctx, cudaMemcpyAsync(q1, ctx->d_q1, sizeof(double) * (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  return finish_step(ctx, 0, out);
+}
+
+int32_t sbo_compute_sets_device(sbo_ctx* ctx, const double* mu_dev, const double* std_dev, int64_t m, double beta,
+                                double f_min, uint8_t* mask_dev, sbo_step_out* out) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (m < 0 || (m > 0 && (!mu_dev || !std_dev))) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_compute_sets_device: null input");
+  if (!mask_dev && m > ctx->cfg.max_cells) return fail(ctx, SBO_ERR_CAPACITY, "sbo_compute_sets_device: m exceeds max_cells");
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  SBO_TRY(launch_sets_arrays(ctx, mu_dev, std_dev, m, beta, f_min, mask_dev ? mask_dev : ctx->d_mask, nullptr, nullptr));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));
+  const PosteriorSource keep = ctx->source;
+  const int64_t keep_m = ctx->source_m;
+  ctx->source = PosteriorSource::kHostArrays;  // so that n_cells reports m
+  ctx->source_m = m;
+  const int32_t st = finish_step(ctx, 0, out);
+  ctx->source = keep;
+  ctx->source_m = keep_m;
+  return st;
+}
+
+int32_t sbo_select_subgoal(sbo_ctx* ctx, const int32_t* frontier, int64_t F, double goal_x, double goal_y,
+                           int32_t* out_cell) {
+  if (!ctx || !out_cell) return SBO_ERR_INVALID_ARG;
+  *out_cell = -1;
+  if (F < 0 || (F > 0 && !frontier)) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_select_subgoal: null frontier or F < 0");
+  if (F == 0) return SBO_OK;  // "No frontier points found" (:503-506)
+  if (ctx->source == PosteriorSource::kNone)
+    return fail(ctx, SBO_ERR_STATE, "sbo_select_subgoal: no posterior yet (call sbo_step or sbo_compute_sets first)");
+  if (!ctx->grid_set) return fail(ctx, SBO_ERR_STATE, "sbo_select_subgoal: grid not set");
+  if (F > 0xFFFFFFFFll) return fail(ctx, SBO_ERR_CAPACITY, "sbo_select_subgoal: frontier longer than 2^32");
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (F > ctx->sel_cap) {
+    for (void** p : {(void**)&ctx->d_frontier, (void**)&ctx->d_sel_keys, (void**)&ctx->d_sel_width}) {
+      if (*p) cudaFree(*p);
+      *p = nullptr;
+    }
+    const int64_t cap = F + F / 2 + 1024;
+    SBO_CUDA(ctx, cudaMalloc(&ctx->d_frontier, sizeof(int32_t) * (size_t)cap));
+    SBO_CUDA(ctx, cudaMalloc(&ctx->d_sel_keys, sizeof(unsigned long long) * (size_t)cap));
+    SBO_CUDA(ctx, cudaMalloc(&ctx->d_sel_width, sizeof(double) * (size_t)cap));
+    ctx->sel_cap = cap;
+  }
+  SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_frontier, frontier, sizeof(int32_t) * (size_t)F, cudaMemcpyHostToDevice, ctx->stream));
+  SBO_TRY(launch_select(ctx, ctx->d_frontier, F, goal_x, goal_y));
+  SBO_CUDA(ctx, cudaMemcpyAsync(ctx->h_sel_out, ctx->d_sel_out, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (*ctx->h_sel_out == -2)
+    return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_select_subgoal: frontier holds a cell outside this context's cells");
+  *out_cell = *ctx->h_sel_out;
+  return SBO_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// read-back
+// ---------------------------------------------------------------------------------------------
+static int32_t copy_posterior(sbo_ctx* ctx, const void* src, void* dst, bool to_f64) {
+  if (!ctx || !dst) return SBO_ERR_INVALID_ARG;
+  if (!ctx->posterior_valid) return fail(ctx, SBO_ERR_STATE, "sbo_copy_*: no posterior yet (call sbo_step first)");
+  const size_t m = (size_t)ctx->m_local;
+  if (m == 0) return SBO_OK;
+  if (!to_f64 || ctx->cfg.precision == SBO_FP64) {
+    SBO_CUDA(ctx, cudaMemcpyAsync(dst, src, elem_size(ctx) * m, cudaMemcpyDeviceToHost, ctx->stream));
+    SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return SBO_OK;
+  }
+  std::vector<float> tmp(m);
+  SBO_CUDA(ctx, cudaMemcpyAsync(tmp.data(), src, sizeof(float) * m, cudaMemcpyDeviceToHost, ctx->stream));
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  double* d = static_cast<double*>(dst);
+  for (size_t i = 0; i < m; ++i) d[i] = (double)tmp[i];
+  return SBO_OK;
+}
+
+int32_t sbo_copy_mu(sbo_ctx* ctx, void* host_dst) { return copy_posterior(ctx, ctx ? ctx->d_mu : nullptr, host_dst, false); }
+int32_t sbo_copy_sigma2(sbo_ctx* ctx, void* host_dst) { return copy_posterior(ctx, ctx ? ctx->d_s2 : nullptr, host_dst, false); }
+int32_t sbo_copy_mu_f64(sbo_ctx* ctx, double* host_dst) { return copy_posterior(ctx, ctx ? ctx->d_mu : nullptr, host_dst, true); }
+int32_t sbo_copy_sigma2_f64(sbo_ctx* ctx, double* host_dst) { return copy_posterior(ctx, ctx ? ctx->d_s2 : nullptr, host_dst, true); }
+
+int32_t sbo_copy_mask(sbo_ctx* ctx, uint8_t* host_dst) {
+  if (!ctx || !host_dst) return SBO_ERR_INVALID_ARG;
+  if (ctx->source == PosteriorSource::kNone) return fail(ctx, SBO_ERR_STATE, "sbo_copy_mask: no step yet");
+  const size_t m = (size_t)(ctx->source == PosteriorSource::kHostArrays ? ctx->source_m : ctx->m_local);
+  if (m == 0) return SBO_OK;
+  SBO_CUDA(ctx, cudaMemcpyAsync(host_dst, ctx->d_mask, m, cudaMemcpyDeviceToHost, ctx->stream));
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SBO_OK;
+}
+
+int32_t sbo_merge_step_out(const sbo_step_out* parts, int32_t count, sbo_step_out* merged) {
+  if (!parts || !merged || count < 1) return SBO_ERR_INVALID_ARG;
+  sbo_step_out r = parts[0];
+  auto host_better = [](const sbo_argmax& a, const sbo_argmax& b) {
+    return a.idx >= 0 && (b.idx < 0 || a.value > b.value || (a.value == b.value && a.idx < b.idx));
+  };
+  for (int i = 1; i < count; ++i) {
+    const sbo_step_out& o = parts[i];
+    if (host_better(o.argmax_ucb, r.argmax_ucb)) r.argmax_ucb = o.argmax_ucb;
+    if (host_better(o.argmax_width, r.argmax_width)) r.argmax_width = o.argmax_width;
+    r.safe_count += o.safe_count;
+    r.clamped_sigma2 += o.clamped_sigma2;
+    r.n_cells += o.n_cells;
+    r.ms_posterior = std::max(r.ms_posterior, o.ms_posterior);
+    r.ms_sets = std::max(r.ms_sets, o.ms_sets);
+    r.ms_comm = std::max(r.ms_comm, o.ms_comm);
+    r.ms_total = std::max(r.ms_total, o.ms_total);
+  }
+  *merged = r;
+  return SBO_OK;
+}
+
+}  // extern "C"

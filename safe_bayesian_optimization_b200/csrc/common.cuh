@@ -74,6 +74,7 @@ struct sbo_ctx {
   double* d_std64 = nullptr;
   double* d_q0 = nullptr;
   double* d_q1 = nullptr;
+  int64_t stage_cap = 0;     // capacity (cells) of the four staging arrays above
   sbo::PosteriorSource source = sbo::PosteriorSource::kNone;
   int64_t source_m = 0;
   double last_beta = 0.0;
