@@ -1,0 +1,237 @@
+"""Host side of the safe-BO step above the C-ABI.
+
+``SboContext`` is a thin RAII wrapper of ``sbo_ctx``.  ``OptimizerCore`` mirrors
+the step interface of the reference's ``OptimizerNode``
+(/root/reference/src/safe_bayesian_optimization_node.cpp): same member names
+(``mu_``, ``std_``, ``S_``, ``Q_``, ``beta_``, ``f_min_``), same method names
+(``process_terrain_map``, ``ComputeSets``, ``FindSafetyContourIndices``,
+``GetNextSubgoal``) and the same "warn and return -1 / empty" error behaviour
+(:419-422, :503-506), so the parity tests read like tests of the node.  All
+arithmetic of the path runs in libsbo.so on the GPU; only the contour trace
+(OpenCV, reference :461-462) stays on the host, as in the reference.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import logging
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _lib as L
+
+log = logging.getLogger("safe_bayesian_optimization_b200")
+
+
+@dataclass
+class StepResult:
+    n_cells: int
+    safe_count: int
+    argmax_ucb: tuple      # (cell, value); cell == -1 when the safe set is empty
+    argmax_width: tuple
+    clamped_sigma2: int
+    n_obs: int
+    kernel_used: int
+    ms_posterior: float
+    ms_sets: float
+    ms_comm: float
+    ms_total: float
+
+    @staticmethod
+    def from_c(o: L.SboStepOut) -> "StepResult":
+        return StepResult(o.n_cells, o.safe_count, (o.argmax_ucb.idx, o.argmax_ucb.value),
+                          (o.argmax_width.idx, o.argmax_width.value), o.clamped_sigma2, o.n_obs, o.kernel_used,
+                          o.ms_posterior, o.ms_sets, o.ms_comm, o.ms_total)
+
+
+def _dptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _u8ptr(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint8))
+
+
+class SboContext:
+    """Owns one ``sbo_ctx`` (one GPU, one shard of grid rows)."""
+
+    def __init__(self, *, sigma_f=1.0, length_scale=0.4, noise_var=0.1, prior_mean=0.0, precision="fp32",
+                 kernel="auto", device=0, max_obs=1024, max_cells=1 << 20, include_noise_in_sigma=False):
+        self.lib = L.load()
+        cfg = L.SboConfig(sigma_f, length_scale, noise_var, prior_mean, int(include_noise_in_sigma),
+                          {"fp32": L.SBO_FP32, "fp64": L.SBO_FP64}[precision],
+                          {"auto": L.SBO_KERNEL_AUTO, "simt": L.SBO_KERNEL_SIMT, "tcgen05": L.SBO_KERNEL_TCGEN05}[kernel],
+                          device, max_obs, 0, max_cells)
+        self.precision = precision
+        self._h = C.c_void_p()
+        st = self.lib.sbo_create(C.byref(cfg), C.byref(self._h))
+        if st != L.SBO_OK:
+            msg = self.lib.sbo_last_error(None).decode()
+            self._h = None
+            raise L.SboError(st, msg)
+        self.m_local = 0
+        self.cell0 = 0
+
+    # -- plumbing ---------------------------------------------------------
+    def _check(self, st):
+        if st != L.SBO_OK:
+            raise L.SboError(st, self.lib.sbo_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.sbo_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def handle(self):
+        return self._h
+
+    def set_stream(self, cuda_stream_ptr: int | None):
+        self._check(self.lib.sbo_set_stream(self._h, C.c_void_p(cuda_stream_ptr or 0)))
+
+    def synchronize(self):
+        self._check(self.lib.sbo_synchronize(self._h))
+
+    def device_info(self):
+        sm, ok = C.c_int32(), C.c_int32()
+        self._check(self.lib.sbo_device_info(self._h, C.byref(sm), C.byref(ok)))
+        return sm.value, bool(ok.value)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.sbo_launch_count(self._h))
+
+    # -- grid / observations ----------------------------------------------
+    def set_grid(self, x0, y0, rx, ry, W, H, row0=0, row1=None):
+        row1 = H if row1 is None else row1
+        self._check(self.lib.sbo_set_grid(self._h, x0, y0, rx, ry, W, H, row0, row1))
+        self.W, self.H, self.row0, self.row1 = W, H, row0, row1
+        self.m_local = (row1 - row0) * W
+        self.cell0 = row0 * W
+
+    def set_observations(self, xy, y):
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1, 2)
+        y = np.ascontiguousarray(y, dtype=np.float64).reshape(-1)
+        if xy.shape[0] != y.shape[0]:
+            raise ValueError("xy and y disagree on n")
+        self._check(self.lib.sbo_set_observations(self._h, _dptr(xy), _dptr(y), xy.shape[0]))
+
+    def append_observations(self, xy, y):
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1, 2)
+        y = np.ascontiguousarray(y, dtype=np.float64).reshape(-1)
+        self._check(self.lib.sbo_append_observations(self._h, _dptr(xy), _dptr(y), xy.shape[0]))
+
+    @property
+    def n_obs(self) -> int:
+        return int(self.lib.sbo_num_observations(self._h))
+
+    def linv(self):
+        n = self.n_obs
+        out = np.zeros((n, n))
+        self._check(self.lib.sbo_copy_linv(self._h, _dptr(out)))
+        return out
+
+    def alpha(self):
+        out = np.zeros(self.n_obs)
+        self._check(self.lib.sbo_copy_alpha(self._h, _dptr(out)))
+        return out
+
+    # -- the step -----------------------------------------------------------
+    def step(self, beta, f_min, mask_out=None, incremental=False, want_mask=True):
+        """One BO step; returns (StepResult, mask uint8[m_local] or None)."""
+        if mask_out is None and want_mask:
+            mask_out = np.empty(self.m_local, dtype=np.uint8)
+        out = L.SboStepOut()
+        fn = self.lib.sbo_step_incremental if incremental else self.lib.sbo_step
+        self._check(fn(self._h, float(beta), float(f_min), _u8ptr(mask_out) if mask_out is not None else None,
+                       C.byref(out)))
+        return StepResult.from_c(out), mask_out
+
+    def step_device(self, beta, f_min):
+        out = L.SboStepOut()
+        self._check(self.lib.sbo_step_device(self._h, float(beta), float(f_min), C.byref(out)))
+        return StepResult.from_c(out)
+
+    def compute_sets(self, mu, std, beta, f_min, want_q=True):
+        mu = np.ascontiguousarray(mu, dtype=np.float64).reshape(-1)
+        std = np.ascontiguousarray(std, dtype=np.float64).reshape(-1)
+        if mu.size != std.size:
+            raise ValueError("mu and std disagree on m")
+        m = mu.size
+        mask = np.empty(m, dtype=np.uint8)
+        q0 = np.empty(m) if want_q else None
+        q1 = np.empty(m) if want_q else None
+        out = L.SboStepOut()
+        self._check(self.lib.sbo_compute_sets(self._h, _dptr(mu), _dptr(std), m, float(beta), float(f_min), _u8ptr(mask),
+                                              _dptr(q0) if want_q else None, _dptr(q1) if want_q else None, C.byref(out)))
+        return StepResult.from_c(out), mask, q0, q1
+
+    def select_subgoal(self, frontier, goal_xy) -> int:
+        fr = np.ascontiguousarray(frontier, dtype=np.int32).reshape(-1)
+        cell = C.c_int32(-1)
+        self._check(self.lib.sbo_select_subgoal(self._h, fr.ctypes.data_as(C.POINTER(C.c_int32)), fr.size,
+                                                float(goal_xy[0]), float(goal_xy[1]), C.byref(cell)))
+        return int(cell.value)
+
+    # -- read-back ----------------------------------------------------------
+    def mu(self):
+        out = np.empty(self.m_local)
+        self._check(self.lib.sbo_copy_mu_f64(self._h, _dptr(out)))
+        return out
+
+    def sigma2(self):
+        out = np.empty(self.m_local)
+        self._check(self.lib.sbo_copy_sigma2_f64(self._h, _dptr(out)))
+        return out
+
+    def mask(self, m=None):
+        out = np.empty(self.m_local if m is None else m, dtype=np.uint8)
+        self._check(self.lib.sbo_copy_mask(self._h, _u8ptr(out)))
+        return out
+
+    # -- multi-GPU ------------------------------------------------------------
+    def comm_unique_id(self) -> bytes:
+        buf = (C.c_uint8 * 128)()
+        st = self.lib.sbo_comm_unique_id(buf)
+        if st != L.SBO_OK:
+            raise L.SboError(st, "sbo_comm_unique_id failed (libnccl not loadable?)")
+        return bytes(buf)
+
+    def comm_init(self, uid: bytes, rank: int, world: int):
+        buf = (C.c_uint8 * 128).from_buffer_copy(uid)
+        self._check(self.lib.sbo_comm_init(self._h, buf, rank, world))
+
+
+def shard_rows(H: int, rank: int, world: int):
+    """Contiguous band of grid rows owned by `rank`."""
+    base, rem = divmod(H, world)
+    r0 = rank * base + min(rank, rem)
+    return r0, r0 + base + (1 if rank < rem else 0)
+
+
+def merge_results(parts):
+    """Fold per-shard StepResults with the library's order (value desc, index asc)."""
+    def better(a, b):
+        return a[0] >= 0 and (b[0] < 0 or a[1] > b[1] or (a[1] == b[1] and a[0] < b[0]))
+    ucb, wid = parts[0].argmax_ucb, parts[0].argmax_width
+    for p in parts[1:]:
+        if better(p.argmax_ucb, ucb):
+            ucb = p.argmax_ucb
+        if better(p.argmax_width, wid):
+            wid = p.argmax_width
+    return StepResult(sum(p.n_cells for p in parts), sum(p.safe_count for p in parts), ucb, wid,
+                      sum(p.clamped_sigma2 for p in parts), parts[0].n_obs, parts[0].kernel_used,
+                      max(p.ms_posterior for p in parts), max(p.ms_sets for p in parts),
+                      max(p.ms_comm for p in parts), max(p.ms_total for p in parts))

@@ -1,0 +1,201 @@
+"""GPU parity: the GP posterior (mu, sigma^2), safe mask and argmax of a whole BO step through the C-ABI
+against the fp64 oracle, for the tcgen05 kernel (fp32 mode), the SIMT kernel in both precisions, the
+incremental (rank-k) step, row-band shards, and the committed golden fixtures.
+
+Tolerances (north_star: "mu and sigma^2 within 1e-5 relative error in fp32, tighter in fp64"):
+  fp32:  |dmu| <= 1e-5 * max|mu_ref|      |dsigma^2| <= 1e-5 * sigma_f^2
+  fp64:  |dmu| <= 1e-10 * max|mu_ref|     |dsigma^2| <= 1e-10 * sigma_f^2
+i.e. relative to the scale of each field; sigma^2 = sigma_f^2 - |v|^2 cancels, so an error relative to
+sigma^2 itself is below fp32 resolution where sigma^2 << sigma_f^2 (reported, not gated).  The mask must
+be identical outside the band |LCB_ref - f_min| <= dmu_tol + beta * ds2_tol / (2 sigma_ref); the argmax
+must agree in index or differ only between candidates whose values lie within the same band."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from conftest import make_ctx
+from safe_bayesian_optimization_b200 import synthetic as S
+
+pytestmark = pytest.mark.gpu
+TOL = {"fp32": 1e-5, "fp64": 1e-10}
+GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
+
+
+def reference(oracle, coracle, p, n=None):
+    n = p.n if n is None else n
+    hp = oracle.Hyper(p.sigma_f, p.length, p.noise_var, p.prior_mean)
+    g = oracle.Grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+    if n > 0:
+        _, Linv, alpha = coracle.gp_fit(p.xy[:n], p.y[:n], hp)
+    else:
+        Linv, alpha = np.zeros((0, 0)), np.zeros(0)
+    mu, s2 = coracle.posterior(p.xy[:n], hp, Linv, alpha, g)
+    q0, q1 = coracle.confidence_intervals(mu, np.sqrt(np.maximum(s2, 0.0)), p.beta)
+    mask, cnt = coracle.safe_set(q0, p.f_min)
+    return dict(mu=mu, s2=s2, q0=q0, q1=q1, mask=mask, cnt=cnt, g=g)
+
+
+def check_step(p, ref, res, mask, mu, s2, precision, cell0=0, label=""):
+    tol = TOL[precision]
+    sl = slice(cell0, cell0 + mu.size)
+    mu_ref, s2_ref, q0, q1, mref = ref["mu"][sl], ref["s2"][sl], ref["q0"][sl], ref["q1"][sl], ref["mask"][sl]
+    mu_tol = tol * np.abs(ref["mu"]).max()
+    s2_tol = tol * p.sigma_f ** 2
+    emu, es2 = np.abs(mu - mu_ref).max(), np.abs(s2 - s2_ref).max()
+    rel_plain = (np.abs(s2 - s2_ref) / np.maximum(s2_ref, 1e-30)).max()
+    print(f"[{label} {precision}] n={p.n} m={mu.size} max|dmu|={emu:.3e} (tol {mu_tol:.1e}) max|ds2|={es2:.3e} "
+          f"(tol {s2_tol:.1e}) plain-rel ds2={rel_plain:.2e} min s2={s2_ref.min():.3e} clamped={res.clamped_sigma2}")
+    assert emu <= mu_tol and es2 <= s2_tol
+    band = mu_tol + p.beta * s2_tol / (2.0 * np.sqrt(np.maximum(s2_ref, 1e-12)))
+    diff = mask != mref
+    in_band = np.abs(q0 - p.f_min) <= band
+    print(f"    mask mismatches: {int(diff.sum())} (all inside the tolerance band: {bool((~diff | in_band).all())})")
+    assert not (diff & ~in_band).any()
+    assert set(np.unique(mask)) <= {0, 255}
+    return band
+
+
+def check_argmax(res, ref, band, mask):
+    for got, val in ((res.argmax_ucb, ref["q1"]), (res.argmax_width, ref["q1"] - ref["q0"])):
+        safe = ref["mask"] == 255
+        if not safe.any():
+            assert got[0] == -1 or band[got[0]] > 0
+            continue
+        best = np.flatnonzero(safe & (val == val[safe].max()))[0]
+        if got[0] != best:      # allowed only between candidates inside the band
+            assert got[0] >= 0 and abs(val[got[0]] - val[best]) <= 2 * band[[got[0], best]].max() + 1e-300
+        assert abs(got[1] - val[got[0]]) <= 2 * band[got[0]]
+
+
+CASES = [  # (cfg, n, W, H) -- ragged sizes on purpose: n % 32, n % 256, W % 128 != 0, single rows, tiny grids
+    ("C2", 0, 64, 8), ("C2", 1, 128, 4), ("C2", 31, 130, 9), ("C2", 32, 128, 16), ("C2", 200, 96, 48),
+    ("C2", 256, 256, 32), ("C2", 257, 200, 40), ("C2", 700, 384, 24), ("C2", 1024, 512, 64), ("C3", 1100, 1, 300),
+]
+
+
+@pytest.mark.parametrize("cfg,n,W,H", CASES)
+@pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp32", "simt"), ("fp64", "simt")])
+def test_step_matches_oracle(pkg, oracle, coracle, cfg, n, W, H, precision, kernel):
+    p = S.make_problem(cfg, n=n, W=W, H=H)
+    ref = reference(oracle, coracle, p)
+    with make_ctx(pkg, p, precision=precision, kernel=kernel) as ctx:
+        ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+        ctx.set_observations(p.xy, p.y)
+        res, mask = ctx.step(p.beta, p.f_min)
+        assert res.kernel_used == {"tcgen05": 2, "simt": 1}[kernel] and res.n_obs == n and res.n_cells == p.m
+        band = check_step(p, ref, res, mask, ctx.mu(), ctx.sigma2(), precision, label=kernel)
+        assert res.safe_count == int((mask == 255).sum())
+        check_argmax(res, ref, band, mask)
+        assert np.array_equal(ctx.mask(), mask)
+
+
+@pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp64", "simt")])
+@pytest.mark.parametrize("n0,ks", [(300, [1, 16]), (250, [6, 1, 40]), (0, [5])])
+def test_incremental_step_equals_full(pkg, oracle, coracle, precision, kernel, n0, ks):
+    total = n0 + sum(ks)
+    p = S.make_problem("C3", n=total, W=256, H=24)
+    with make_ctx(pkg, p, precision=precision, kernel=kernel, max_obs=total) as ctx:
+        ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+        ctx.set_observations(p.xy[:n0], p.y[:n0])
+        ctx.step(p.beta, p.f_min)
+        n = n0
+        for k in ks:
+            ctx.append_observations(p.xy[n:n + k], p.y[n:n + k])
+            n += k
+            res, mask = ctx.step(p.beta, p.f_min, incremental=True)
+            q = S.make_problem("C3", n=total, W=256, H=24); q.xy, q.y = p.xy[:n], p.y[:n]
+            ref = reference(oracle, coracle, q)
+            band = check_step(q, ref, res, mask, ctx.mu(), ctx.sigma2(), precision, label=f"incr+{k}")
+            check_argmax(res, ref, band, mask)
+
+
+@pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp64", "simt")])
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_row_band_shards_equal_single(pkg, oracle, coracle, precision, kernel, world):
+    """G shards emulated one after the other on one GPU: identical bytes, merged argmax."""
+    p = S.make_problem("C2", n=300, W=256, H=37)
+    ref = reference(oracle, coracle, p)
+    with make_ctx(pkg, p, precision=precision, kernel=kernel) as ctx:
+        ctx.set_observations(p.xy, p.y)
+        ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+        single, mask1 = ctx.step(p.beta, p.f_min)
+        mu1, s21 = ctx.mu(), ctx.sigma2()
+        parts, masks, mus, s2s = [], [], [], []
+        for r in range(world):
+            r0, r1 = pkg.shard_rows(p.H, r, world)
+            ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H, r0, r1)
+            res, mask = ctx.step(p.beta, p.f_min)
+            parts.append(res); masks.append(mask); mus.append(ctx.mu()); s2s.append(ctx.sigma2())
+        merged = pkg.merge_results(parts)
+        assert np.array_equal(np.concatenate(masks), mask1)
+        assert np.array_equal(np.concatenate(mus), mu1) and np.array_equal(np.concatenate(s2s), s21)   # bitwise
+        assert merged.safe_count == single.safe_count and merged.n_cells == p.m
+        assert merged.argmax_ucb == single.argmax_ucb and merged.argmax_width == single.argmax_width
+
+
+@pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(x) for x in GOLDEN])
+def test_golden_fixtures(pkg, path):
+    z = np.load(path)
+    sf, ell, nv, pm = z["hyper"]; x0, y0, rx, ry = z["grid"]; W, H, n = int(z["W"]), int(z["H"]), int(z["n"])
+    for precision, kernel in (("fp32", "tcgen05"), ("fp64", "simt")):
+        tol = TOL[precision]
+        with pkg.SboContext(sigma_f=sf, length_scale=ell, noise_var=nv, prior_mean=pm, precision=precision,
+                            kernel=kernel, max_obs=n, max_cells=W * H) as ctx:
+            ctx.set_grid(x0, y0, rx, ry, W, H)
+            ctx.set_observations(z["xy"], z["y"])
+            res, mask = ctx.step(float(z["beta"]), float(z["f_min"]))
+            assert np.abs(ctx.alpha() - z["alpha"]).max() <= 1e-9 * np.abs(z["alpha"]).max()
+            assert np.abs(ctx.mu() - z["mu"]).max() <= tol * np.abs(z["mu"]).max()
+            assert np.abs(ctx.sigma2() - z["s2"]).max() <= tol * sf ** 2
+            band = tol * np.abs(z["mu"]).max() + float(z["beta"]) * tol * sf ** 2 / (2 * np.sqrt(np.maximum(z["s2"], 1e-12)))
+            assert not ((mask != z["mask"]) & (np.abs(z["q0"] - float(z["f_min"])) > band)).any()
+            if precision == "fp64":
+                assert np.array_equal(mask, z["mask"]) and res.safe_count == int(z["safe_count"])
+                assert res.argmax_ucb[0] == int(z["ucb"][0]) and res.argmax_width[0] == int(z["width"][0])
+                fr = pkg.find_safety_contour_indices(mask.reshape(H, W), x0, y0, rx, ry)
+                assert np.array_equal(fr, z["frontier"])
+                assert ctx.select_subgoal(fr, z["goal"]) == int(z["subgoal"])
+
+
+def test_optimizer_core_end_to_end(pkg, oracle, coracle):
+    """The node-shaped host mirror: both entry forms give the oracle's subgoal."""
+    p = S.make_problem("C1", n=48, W=40, H=30)
+    ref = reference(oracle, coracle, p)
+    fr_ref = oracle.find_safety_contour_indices(ref["mask"], ref["g"])
+    want = coracle.get_next_subgoal(fr_ref, ref["g"], ref["q0"], ref["q1"], p.goal)
+    # (a) the reference's own boundary: posterior arrays in (service response), sets + subgoal out
+    core = pkg.OptimizerCore(beta=p.beta, f_min=p.f_min, precision="fp64", max_obs=p.n, max_cells=p.m,
+                             sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean)
+    cx, cy = ref["g"].cell_xy()
+    core.goal_point_callback(*p.goal)
+    assert core.process_terrain_map(cx, cy, ref["mu"], np.sqrt(np.maximum(ref["s2"], 0)), p.W, p.H)
+    assert np.array_equal(core.S_, ref["mask"]) and np.array_equal(core.Q_[:, 0], ref["q0"])
+    assert np.array_equal(core.FindSafetyContourIndices(), fr_ref) and core.GetNextSubgoal() == want
+    # (b) the integrated path: observations in
+    core.process_observations(p.xy, p.y, (p.x0, p.y0, p.rx, p.ry, p.W, p.H))
+    assert np.array_equal(core.S_, ref["mask"]) and core.GetNextSubgoal() == want
+    core.ctx.close()
+
+
+def test_full_size_c2_properties(pkg):
+    """BASELINE config C2 at full size (1024 obs x 1M cells): size-independent properties."""
+    p = S.make_problem("C2")
+    with make_ctx(pkg, p) as ctx:
+        ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+        ctx.set_observations(p.xy, p.y)
+        a, mask = ctx.step(p.beta, p.f_min)
+        s2, mu = ctx.sigma2(), ctx.mu()
+        assert a.kernel_used == 2 and a.clamped_sigma2 == 0
+        assert np.isfinite(mu).all() and (s2 > 0).all() and (s2 <= p.sigma_f ** 2 * (1 + 1e-6)).all()
+        assert a.safe_count == int((mask == 255).sum()) and 0 < a.safe_count < p.m
+        b, mask_b = ctx.step(p.beta, p.f_min)                      # idempotent, bitwise
+        assert np.array_equal(mask, mask_b) and a.argmax_ucb == b.argmax_ucb and np.array_equal(ctx.sigma2(), s2)
+        # more observations never raise the latent variance (up to fp32 rounding)
+        xy2, y2 = S.extra_observations(p, 16, 0)
+        with make_ctx(pkg, p, max_obs=p.n + 16) as ctx2:
+            ctx2.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+            ctx2.set_observations(np.concatenate([p.xy, xy2]), np.concatenate([p.y, y2]))
+            ctx2.step(p.beta, p.f_min)
+            assert (ctx2.sigma2() <= s2 + 2e-5).all()
