@@ -134,7 +134,14 @@ int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, in
  * L^-1 = [-L22^-1 L21 L11^-1, L22^-1], alpha refreshed.  O(k n^2). */
 int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y, int32_t k);
 int32_t sbo_num_observations(const sbo_ctx* ctx);
-/* Read back the factor state (fp64, n x n row-major / n) for checking. */
+/* Internal ordering.  sbo_set_observations stores the observations sorted spatially (bands of 2
+ * length-scales in y, by x inside a band): the GP is invariant under the permutation, the sorted
+ * order makes the cross-covariance tiles of a cell tile block-sparse and keeps the tensor-core
+ * accumulation short.  order[pos] = index in the caller's arrays of the observation stored at
+ * `pos`; appended observations keep their arrival order behind the sorted ones. */
+int32_t sbo_copy_order(sbo_ctx* ctx, int32_t* host_dst);
+/* Read back the factor state for checking: alpha (n, in the CALLER's order) and L^-1 (n x n
+ * row-major fp64, of the covariance in the INTERNAL order, see sbo_copy_order). */
 int32_t sbo_copy_linv(sbo_ctx* ctx, double* host_dst);
 int32_t sbo_copy_alpha(sbo_ctx* ctx, double* host_dst);
 

@@ -56,6 +56,7 @@ SYMBOLS = {
     "sbo_set_observations": (C.c_int32, [_P, _D, _D, C.c_int32]),
     "sbo_append_observations": (C.c_int32, [_P, _D, _D, C.c_int32]),
     "sbo_num_observations": (C.c_int32, [_P]),
+    "sbo_copy_order": (C.c_int32, [_P, C.POINTER(C.c_int32)]),
     "sbo_copy_linv": (C.c_int32, [_P, _D]),
     "sbo_copy_alpha": (C.c_int32, [_P, _D]),
     "sbo_step": (C.c_int32, [_P, C.c_double, C.c_double, _U8, C.POINTER(SboStepOut)]),

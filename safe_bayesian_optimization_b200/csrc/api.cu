@@ -301,18 +301,38 @@ int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, in
   if (!all_finite(xy, 2 * (size_t)n) || !all_finite(y, (size_t)n))
     return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_observations: NaN/Inf in the observations");
   SBO_CUDA(ctx, cudaSetDevice(ctx->device));
-  std::vector<double> r((size_t)n);
-  for (int i = 0; i < n; ++i) r[i] = y[i] - ctx->cfg.prior_mean;
-  if (n > 0) {
-    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_xy, xy, sizeof(double) * 2 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
-    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_r, r.data(), sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
-    SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // r is a local
+  // spatial order: bands of two length-scales in y, by x inside a band (see sbo_copy_order)
+  std::vector<int32_t> order((size_t)n);
+  for (int i = 0; i < n; ++i) order[i] = i;
+  if (n > 1) {
+    double ymin = xy[1];
+    for (int i = 1; i < n; ++i) ymin = std::min(ymin, xy[2 * i + 1]);
+    const double inv_band = 1.0 / (2.0 * ctx->cfg.length_scale);
+    std::vector<long long> band((size_t)n);
+    for (int i = 0; i < n; ++i) band[i] = (long long)std::floor((xy[2 * i + 1] - ymin) * inv_band);
+    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
+      if (band[a] != band[b]) return band[a] < band[b];
+      return xy[2 * a] < xy[2 * b];
+    });
   }
+  std::vector<double> sxy(2 * (size_t)n), r((size_t)n);
+  for (int i = 0; i < n; ++i) {
+    sxy[2 * i] = xy[2 * (size_t)order[i]];
+    sxy[2 * i + 1] = xy[2 * (size_t)order[i] + 1];
+    r[i] = y[order[i]] - ctx->cfg.prior_mean;
+  }
+  if (n > 0) {
+    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_xy, sxy.data(), sizeof(double) * 2 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_r, r.data(), sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // sxy, r are locals
+  }
+  ctx->order.swap(order);
   ctx->n = n;
   ctx->posterior_valid = false;
   const int32_t st = factor_full(ctx);
   if (st != SBO_OK) {
     ctx->n = 0;  // the factor buffers were overwritten: no observations until the next successful fit
+    ctx->order.clear();
     cudaMemsetAsync(ctx->d_Linv, 0, sizeof(double) * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
     cudaMemsetAsync(ctx->d_alpha, 0, sizeof(double) * (size_t)ctx->n_cap, ctx->stream);
     if (ctx->d_planes) cudaMemsetAsync(ctx->d_planes, 0, sizeof(float) * 2 * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
@@ -341,6 +361,7 @@ int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y,
     SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_r + n, r.data() + done, sizeof(double) * (size_t)kk, cudaMemcpyHostToDevice,
                                   ctx->stream));
     SBO_TRY(factor_append(ctx, kk));  // on failure n is unchanged: rows >= n of L^-1 are not part of the state
+    for (int i = 0; i < kk; ++i) ctx->order.push_back(n + i);
     ctx->n = n + kk;
     done += kk;
   }
@@ -361,8 +382,16 @@ int32_t sbo_copy_linv(sbo_ctx* ctx, double* host_dst) {
 int32_t sbo_copy_alpha(sbo_ctx* ctx, double* host_dst) {
   if (!ctx || !host_dst) return SBO_ERR_INVALID_ARG;
   if (ctx->n == 0) return SBO_OK;
-  SBO_CUDA(ctx, cudaMemcpyAsync(host_dst, ctx->d_alpha, sizeof(double) * (size_t)ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
+  std::vector<double> tmp((size_t)ctx->n);
+  SBO_CUDA(ctx, cudaMemcpyAsync(tmp.data(), ctx->d_alpha, sizeof(double) * (size_t)ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int i = 0; i < ctx->n; ++i) host_dst[ctx->order[i]] = tmp[i];  // back to the caller's order
+  return SBO_OK;
+}
+
+int32_t sbo_copy_order(sbo_ctx* ctx, int32_t* host_dst) {
+  if (!ctx || !host_dst) return SBO_ERR_INVALID_ARG;
+  for (int i = 0; i < ctx->n; ++i) host_dst[i] = ctx->order[i];
   return SBO_OK;
 }
 

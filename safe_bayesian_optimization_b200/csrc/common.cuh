@@ -6,6 +6,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/sbo.h"
 
@@ -50,6 +51,7 @@ struct sbo_ctx {
   int n = 0;
   int n_prev = 0;  // n before the last append (for the incremental step)
   int n_cap = 0;
+  std::vector<int32_t> order;  // order[pos] = caller index of the observation stored at pos
   double* d_xy = nullptr;     // [n_cap][2]
   double* d_r = nullptr;      // [n_cap] y - prior_mean
   double* d_A = nullptr;      // [n_cap][n_cap] K, then L in the lower triangle

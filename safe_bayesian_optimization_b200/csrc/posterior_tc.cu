@@ -66,6 +66,7 @@ struct TcParams {
   float neg_c2;            // -log2(e) / (2 l^2)
   float log2_sf2;          // log2(sigma_f^2)
   float sf2, prior_mean;
+  float* dbg_v;            // debug: V of tile 0 ([128][n_cap]) when non-null
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -162,6 +163,10 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+#ifndef SBO_TC_TERMS
+#define SBO_TC_TERMS 3 // 3: lo.hi + hi.lo + hi.hi   4: + lo.lo   1: hi.hi only (diagnostics)
+#endif
+
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -245,9 +250,18 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
 #pragma unroll
             for (int k8 = 0; k8 < BK / UK; ++k8) {
               const uint64_t adv = (uint64_t)((k8 * UK * 4) >> 4);  // +32 bytes along K inside the swizzle row
+#if SBO_TC_TERMS == 1
+              umma_tf32(d_tmem, dah + adv, dbh + adv, kIdesc, (kc | k8) != 0);
+#else
+#if SBO_TC_TERMS == 4
+              umma_tf32(d_tmem, dal + adv, dbl + adv, kIdesc, (kc | k8) != 0);
+              umma_tf32(d_tmem, dal + adv, dbh + adv, kIdesc, 1u);
+#else
               umma_tf32(d_tmem, dal + adv, dbh + adv, kIdesc, (kc | k8) != 0);
+#endif
               umma_tf32(d_tmem, dah + adv, dbl + adv, kIdesc, 1u);
               umma_tf32(d_tmem, dah + adv, dbh + adv, kIdesc, 1u);
+#endif
             }
             umma_commit(&sh->empty[s]);  // stage reusable once these MMAs have read it
           }
@@ -275,6 +289,10 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           uint32_t v[32];
           tmem_ld32(taddr + c * 32, v);
           tmem_ld_wait();
+          if (p.dbg_v && tile == 0) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) p.dbg_v[(size_t)r * p.n_cap + jc + i] = __uint_as_float(v[i]);
+          }
           const bool whole = (jc >= p.j_lo) && (jc + 32 <= p.j_hi);
           double s0 = 0.0, s1 = 0.0;
 #pragma unroll
@@ -314,7 +332,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       const int lrow = (int)(tile / tiles_per_row), col0 = (int)(tile % tiles_per_row) * BM;
       const double ox = cell_coord(p.x0, p.rx, col0), oy = cell_coord(p.y0, p.ry, p.row0 + lrow);
       const float cxr = (float)r * p.frx;  // offset of this thread's cell from the tile origin
-      float mu_acc = 0.f;
+      double mu_acc = 0.0;  // fp32 inside a 32-observation chunk, fp64 across chunks
       for (int jb = jb_lo; jb < jb_hi; ++jb) {
         const bool last = (jb == jb_hi - 1);
         const int nch = chunks_of(jb, n_pad32);
@@ -338,6 +356,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             __syncwarp();
           }
           mbar_wait(&sh->empty[s], ph ^ 1u);  // MMAs that read this stage have completed
+          float mu_chunk = 0.f;
           uint8_t* pa_hi = a_hi(s) + row_off;
           uint8_t* pa_lo = a_lo(s) + row_off;
 #pragma unroll
@@ -347,8 +366,10 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             for (int e = 0; e < 4; ++e) {
               const float4 t = scratch[qd * 4 + e];  // broadcast
               const float dx = t.x - cxr;
+              // MUFU ex2 is accurate enough here: swapping it for a 1-ulp polynomial changed neither mu nor
+              // sigma^2 errors (profiles/accuracy_r01.md); the error budget is set by the accumulator.
               const float kv = ex2_approx(fmaf(dx * dx, p.neg_c2, t.y));
-              if (last) mu_acc = fmaf(kv, t.z, mu_acc);
+              mu_chunk = fmaf(kv, t.z, mu_chunk);
               hi[e] = tf32_rna_bits(kv);
               lo[e] = tf32_rna_bits(kv - hi[e]);
             }
@@ -356,17 +377,18 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             *reinterpret_cast<float4*>(pa_hi + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
             *reinterpret_cast<float4*>(pa_lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
           }
+          if (last) mu_acc += (double)mu_chunk;
           fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
           __syncwarp();
           if (lane == 0) mbar_arrive(&sh->full[s]);
         }
       }
       // combine the two groups' partial mu and write it out
-      if (grp == 1) sh->mu_part[tile_par][r] = mu_acc;
+      if (grp == 1) sh->mu_part[tile_par][r] = (float)mu_acc;
       named_bar_sync(1, 256);
       if (grp == 0) {
         const int col = col0 + r;
-        if (col < p.W) p.mu[(long long)lrow * p.W + col] = p.prior_mean + mu_acc + sh->mu_part[tile_par][r];
+        if (col < p.W) p.mu[(long long)lrow * p.W + col] = (float)((double)p.prior_mean + mu_acc + (double)sh->mu_part[tile_par][r]);
       }
     }
   }
@@ -426,6 +448,8 @@ void tc_destroy(sbo_ctx* ctx) {
   ctx->tc_ok = false;
 }
 
+static float* g_dbg_v = nullptr;
+
 int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   if (!ctx->tc_ok) return fail(ctx, SBO_ERR_STATE, "tcgen05 kernel not initialised");
   if (ctx->m_local == 0) return SBO_OK;
@@ -449,6 +473,7 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.log2_sf2 = (float)std::log2(sf2);
   p.sf2 = (float)sf2;
   p.prior_mean = (float)ctx->cfg.prior_mean;
+  p.dbg_v = g_dbg_v;
   const long long ntiles = (long long)p.rows_local * ((p.W + BM - 1) / BM);
   const unsigned grid = (unsigned)std::min<long long>(ntiles, ctx->sm_count);  // persistent: one CTA per SM
   posterior_tc_kernel<<<grid, kThreadsTc, kSmemBytes, ctx->stream>>>(*static_cast<CUtensorMap*>(ctx->tmap_planes), p);
@@ -457,3 +482,20 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
 }
 
 }  // namespace sbo
+
+// Undocumented debug hook (not part of include/sbo.h): V = K* L^-T of cell tile 0 as the tensor core
+// produced it, [128][n_cap] floats, for accuracy forensics in scripts/.
+extern "C" int32_t sbo_debug_tc_v(sbo_ctx* ctx, float* host_dst) {
+  if (!ctx || !host_dst || !ctx->tc_ok || !ctx->grid_set) return SBO_ERR_INVALID_ARG;
+  const size_t count = (size_t)128 * ctx->n_cap;
+  float* d = nullptr;
+  if (cudaMalloc(&d, count * sizeof(float)) != cudaSuccess) return SBO_ERR_CUDA;
+  cudaMemsetAsync(d, 0, count * sizeof(float), ctx->stream);
+  sbo::g_dbg_v = d;
+  const int32_t st = sbo::launch_posterior_tc(ctx, 0, ctx->n, false);
+  sbo::g_dbg_v = nullptr;
+  cudaMemcpyAsync(host_dst, d, count * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream);
+  cudaStreamSynchronize(ctx->stream);
+  cudaFree(d);
+  return st;
+}

@@ -137,6 +137,12 @@ class SboContext:
     def n_obs(self) -> int:
         return int(self.lib.sbo_num_observations(self._h))
 
+    def order(self):
+        """order[pos] = caller index of the observation stored at internal position pos."""
+        out = np.zeros(self.n_obs, dtype=np.int32)
+        self._check(self.lib.sbo_copy_order(self._h, out.ctypes.data_as(C.POINTER(C.c_int32))))
+        return out
+
     def linv(self):
         n = self.n_obs
         out = np.zeros((n, n))

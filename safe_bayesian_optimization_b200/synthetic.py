@@ -106,7 +106,7 @@ def make_problem(name: str = "C2", n: int | None = None, W: int | None = None, H
     gx, gy = np.meshgrid(np.linspace(0, Lx, 96), np.linspace(0, Ly, 96))
     f_min = float(np.percentile(terrain(gx, gy), 40.0))
     return Problem(name=name, xy=xy, y=y, x0=0.0, y0=0.0, rx=rx, ry=ry, W=W, H=H, beta=BETA, f_min=f_min,
-                   goal=(0.9 * Lx, 0.9 * Ly), prior_mean=float(np.mean(y)),
+                   goal=(0.9 * Lx, 0.9 * Ly), prior_mean=float(np.mean(y)) if n > 0 else 5.0,
                    precision=cfg["precision"] if precision is None else precision, terrain=terrain)
 
 

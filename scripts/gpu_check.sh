@@ -1,10 +1,7 @@
 #!/bin/bash
-# One gpurun call: staged GPU checks with per-stage timeouts; logs under gpurun_out/.
+# One gpurun call: the whole GPU suite, accuracy probe, smoke, short bench; logs under gpurun_out/.
 mkdir -p gpurun_out
-nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
-echo "== sets/select/factor"; timeout 600 python -m pytest tests/test_gpu_sets.py tests/test_gpu_factor.py -q -m gpu -x 2>&1 | tail -25 | tee gpurun_out/t1.log
-echo "== posterior simt"; timeout 900 python -m pytest tests/test_gpu_posterior.py -q -m gpu -k "simt and not tcgen05 and test_step_matches" -s 2>&1 | grep -E "^\[|passed|failed|Error|error|assert" | tail -40 | tee gpurun_out/t2.log
-echo "== posterior tcgen05"; timeout 600 python -m pytest tests/test_gpu_posterior.py -q -m gpu -k "tcgen05 and test_step_matches" -s 2>&1 | grep -E "^\[|    mask|passed|failed|Error|error|assert|Timeout" | tail -60 | tee gpurun_out/t3.log
-echo "== rest"; timeout 900 python -m pytest tests/test_gpu_posterior.py -q -m gpu -k "not test_step_matches" 2>&1 | tail -30 | tee gpurun_out/t4.log
-echo "== smoke"; timeout 300 python __graft_entry__.py smoke 2>&1 | tail -12 | tee gpurun_out/smoke.log
-echo "== bench"; timeout 600 python bench.py --steps 5 --warmup 3 2>&1 | tail -5 | tee gpurun_out/bench.log
+echo "== pytest -m gpu"; timeout 1500 python -m pytest tests -q -m gpu 2>&1 | tail -25 | tee gpurun_out/pytest_gpu.log
+echo "== accuracy"; timeout 300 python scripts/acc_probe.py "[lib]" 256,1024,2048,4096 tcgen05,simt 2>&1 | tail -8 | tee gpurun_out/accuracy.log
+echo "== smoke"; timeout 300 python __graft_entry__.py smoke 2>&1 | tail -6 | tee gpurun_out/smoke.log
+echo "== bench"; timeout 600 python bench.py --steps 10 --warmup 3 2>&1 | tail -3 | tee gpurun_out/bench.log

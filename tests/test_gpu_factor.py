@@ -22,7 +22,10 @@ def test_factor_matches_oracle(pkg, oracle, coracle, n):
     with make_ctx(pkg, p, precision="fp64") as ctx:
         ctx.set_observations(p.xy, p.y)
         assert ctx.n_obs == n
-        assert _rel(ctx.linv(), Linv) < TOL and _rel(ctx.alpha(), alpha) < TOL
+        order = ctx.order()
+        assert sorted(order.tolist()) == list(range(n))
+        _, Linv_sorted, _ = coracle.gp_fit(p.xy[order], p.y[order], hp)       # L^-1 is reported in the internal order
+        assert _rel(ctx.linv(), Linv_sorted) < TOL and _rel(ctx.alpha(), alpha) < TOL
         assert np.array_equal(np.triu(ctx.linv(), 1), np.zeros((n, n)))
 
 
@@ -37,7 +40,10 @@ def test_append_equals_full_refactor(pkg, oracle, coracle, n0, ks):
         for k in ks:
             ctx.append_observations(p.xy[n:n + k], p.y[n:n + k])
             n += k
-            _, Linv, alpha = coracle.gp_fit(p.xy[:n], p.y[:n], hp)
+            order = ctx.order()
+            assert sorted(order.tolist()) == list(range(n)) and np.array_equal(order[n - k:], np.arange(n - k, n))
+            _, Linv, _ = coracle.gp_fit(p.xy[order], p.y[order], hp)
+            _, _, alpha = coracle.gp_fit(p.xy[:n], p.y[:n], hp)
             assert ctx.n_obs == n
             assert _rel(ctx.linv(), Linv) < 1e-9 and _rel(ctx.alpha(), alpha) < 1e-9
 
@@ -64,7 +70,7 @@ def test_errors_and_state(pkg):
         xy = np.array([[0.1, 0.1], [0.5, 0.5], [0.1, 0.1]])
         with pytest.raises(pkg.SboError) as e:
             ctx.set_observations(xy, np.zeros(3))
-        assert e.value.status == -4 and "row 2" in str(e.value)
+        assert e.value.status == -4 and "positive definite at row" in str(e.value)
         assert ctx.n_obs == 0
         ctx.set_observations(xy[:2], np.zeros(2))                     # context still usable
         with pytest.raises(pkg.SboError) as e:
