@@ -205,8 +205,8 @@ int32_t sbo_create(const sbo_config* cfg, sbo_ctx** out) {
   CREATE_CUDA(cudaMemset(c->d_alpha, 0, sizeof(double) * nc));
   CREATE_CUDA(cudaMemset(c->d_xy, 0, sizeof(double) * 2 * nc));
   if (cfg->precision == SBO_FP32) {
-    CREATE_CUDA(cudaMalloc(&c->d_planes, sizeof(float) * 2 * nc * nc));
-    CREATE_CUDA(cudaMemset(c->d_planes, 0, sizeof(float) * 2 * nc * nc));
+    CREATE_CUDA(cudaMalloc(&c->d_planes, sizeof(uint16_t) * 2 * nc * nc));
+    CREATE_CUDA(cudaMemset(c->d_planes, 0, sizeof(uint16_t) * 2 * nc * nc));
     CREATE_CUDA(cudaMalloc(&c->d_alpha_f32, sizeof(float) * nc));
     CREATE_CUDA(cudaMemset(c->d_alpha_f32, 0, sizeof(float) * nc));
   }
@@ -335,7 +335,7 @@ int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, in
     ctx->order.clear();
     cudaMemsetAsync(ctx->d_Linv, 0, sizeof(double) * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
     cudaMemsetAsync(ctx->d_alpha, 0, sizeof(double) * (size_t)ctx->n_cap, ctx->stream);
-    if (ctx->d_planes) cudaMemsetAsync(ctx->d_planes, 0, sizeof(float) * 2 * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
+    if (ctx->d_planes) cudaMemsetAsync(ctx->d_planes, 0, sizeof(uint16_t) * 2 * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
     if (ctx->d_alpha_f32) cudaMemsetAsync(ctx->d_alpha_f32, 0, sizeof(float) * (size_t)ctx->n_cap, ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     return st;

@@ -61,8 +61,10 @@ struct sbo_ctx {
   double* d_w = nullptr;      // [n_cap] work vector
   double* d_small = nullptr;  // append scratch: K21/L21/T [kMaxAppend][n_cap] x2 + S
   int* d_info = nullptr;      // Cholesky status (0 or 1+failing row)
-  // tcgen05 operands (fp32 mode): TF32-rounded hi/lo planes of L^-1, stacked [2*n_cap][n_cap]
-  float* d_planes = nullptr;
+  // tcgen05 operands (fp32 mode): fp16 hi/lo planes of 2^shift_b L^-1, stacked [2*n_cap][n_cap]
+  uint16_t* d_planes = nullptr;
+  int shift_a = 0, shift_b = 0;  // power-of-two scales of the K* and L^-1 planes (tc_plane_shifts)
+  int tc_cg = 2;                 // CTAs per tcgen05.mma group (2 = CTA pair, 1 = single CTA)
   float* d_alpha_f32 = nullptr;  // [n_cap]
   float* d_obs_f32 = nullptr;    // unused by default
   void* tmap_planes = nullptr;   // host copy of the CUtensorMap (128 B), 256-row box
@@ -146,7 +148,8 @@ int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end);
 int32_t launch_posterior_simt(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
 
 // posterior_tc.cu
-int32_t tc_init(sbo_ctx* ctx);                     // tensor map, attributes; sets ctx->tc_ok
+int32_t tc_init(sbo_ctx* ctx);                     // tensor map, attributes, plane scales; sets ctx->tc_ok
+void tc_plane_shifts(const sbo_config& cfg, int* shift_a, int* shift_b);
 int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
 void tc_destroy(sbo_ctx* ctx);
 

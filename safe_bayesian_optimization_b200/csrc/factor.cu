@@ -1,6 +1,6 @@
 // factor.cu -- fp64 factor state of the GP on the GPU: K = k(X,X) + noise I = L L^T by a
 // blocked right-looking Cholesky, L^-1 by blocked forward substitution, alpha = K^-1 r, the
-// rank-k append, and the TF32 hi/lo operand planes of L^-1 for the tcgen05 contraction.
+// rank-k append, and the fp16 hi/lo operand planes of L^-1 for the tcgen05 contraction.
 //
 // This is the "fit" half of the external GP node the library replaces (reference
 // launch/safe_bayesian_optimization.launch.py:111-117 mapping_package/terrain_mapping_node;
@@ -15,6 +15,10 @@
 //             X_kc = D_k B_kc                  c <= k      (tile NN)   -- L^-1, row block k
 //             B_ic -= L_ik X_kc         i > k, c <= k      (tile NN)
 // with B (the running right-hand side, initially I) stored in place in L^-1.
+#include <cuda_fp16.h>
+
+#include <cmath>
+
 #include "common.cuh"
 
 namespace sbo {
@@ -315,22 +319,18 @@ __global__ void fill_f32_kernel(float* p, float v, int count) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// TF32 operand planes: hi = rna_tf32(x), lo = rna_tf32(x - hi); rows [r0, r1), all n_cap columns.
+// fp16 operand planes of L^-1 for the tcgen05 contraction: xs = 2^shift x, hi = rn_f16(xs),
+// lo = rn_f16(xs - hi); rows [r0, r1), all n_cap columns.  |xs| <= 2^15 by tc_plane_shifts' bound.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ float tf32_rna(float x) {
-  // round-to-nearest (ties away) onto the 10-bit TF32 mantissa; the tensor core ignores the low 13 bits
-  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
-}
-
 __global__ void __launch_bounds__(256)
-planes_kernel(const double* __restrict__ X, int ld, int r0, int r1, int ncols, float* __restrict__ planes,
-              size_t lo_offset) {
+planes_kernel(const double* __restrict__ X, int ld, int r0, int r1, int ncols, __half* __restrict__ planes,
+              size_t lo_offset, double scale) {
   const int c = blockIdx.x * 256 + threadIdx.x;
   const int r = r0 + blockIdx.y;
   if (r >= r1 || c >= ncols) return;
-  const double x = X[(size_t)r * ld + c];
-  const float hi = tf32_rna((float)x);
-  const float lo = tf32_rna((float)(x - (double)hi));
+  const double x = X[(size_t)r * ld + c] * scale;
+  const __half hi = __float2half_rn((float)x);
+  const __half lo = __float2half_rn((float)(x - (double)__half2float(hi)));
   planes[(size_t)r * ld + c] = hi;
   planes[lo_offset + (size_t)r * ld + c] = lo;
 }
@@ -464,8 +464,9 @@ int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end) {
   if (!ctx->d_planes || row_end <= row_begin) return SBO_OK;
   const int ld = ctx->n_cap;
   dim3 grid((ld + 255) / 256, row_end - row_begin);
-  planes_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_Linv, ld, row_begin, row_end, ld, ctx->d_planes,
-                                               (size_t)ld * ld);
+  planes_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_Linv, ld, row_begin, row_end, ld,
+                                               reinterpret_cast<__half*>(ctx->d_planes), (size_t)ld * ld,
+                                               std::ldexp(1.0, ctx->shift_b));
   SBO_LAUNCH_CHECK(ctx, "planes_kernel");
   return SBO_OK;
 }

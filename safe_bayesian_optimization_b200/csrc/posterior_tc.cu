@@ -4,53 +4,68 @@
 //   mu = prior_mean + K* alpha
 //
 // K* (RBF cross-covariance between every cell and every observation) is never materialised:
-// generator warps compute 128 x 32 tiles of it on the fly, split every entry into two TF32-exact
-// planes (hi = rna_tf32(x), lo = rna_tf32(x - hi)) and store them straight into the 128B-swizzled
-// K-major shared-memory layout the UMMA descriptors expect.  The matching 256 x 32 tiles of the
-// pre-split hi/lo planes of L^-1 arrive by TMA.  One elected thread issues
-//   D += A_lo.B_hi ; D += A_hi.B_lo ; D += A_hi.B_hi        (tcgen05.mma kind::tf32, M128 N256 K8)
-// so the fp32 accumulator in TMEM carries ~2^-22 relative products ("3xTF32").  Epilogue warps
-// pull finished 128 x 256 accumulators out of TMEM with tcgen05.ld, square and row-sum them in fp64
-// and keep only one number per cell: V never reaches shared or global memory.  Two accumulator
-// stages (2 x 256 TMEM columns) let the epilogue of row block jb overlap the MMAs of jb+1.
-// L^-1 is lower triangular, so row block jb only walks k < 256 (jb+1).
+// generator warps compute 128 x 64 tiles of it on the fly, split every entry into two fp16 planes
+// (hi = rn_f16(x), lo = rn_f16(x - hi), x pre-scaled by a power of two so that neither plane leaves
+// the fp16 normal range where it matters) and store them straight into the 128B-swizzled K-major
+// shared-memory layout the UMMA descriptors expect.  The matching tiles of the pre-split, pre-scaled
+// hi/lo planes of L^-1 arrive by TMA.  One elected thread issues
+//   D += A_lo.B_hi ; D += A_hi.B_lo ; D += A_hi.B_hi        (tcgen05.mma kind::f16, N256 K16)
+// so the fp32 accumulator in TMEM carries ~2^-22 relative products ("3xFP16": the same 11+11
+// significand bits as a 3xTF32 split, at twice the tensor rate and half the operand bytes).
+// Epilogue warps pull finished 128 x 256 accumulators out of TMEM with tcgen05.ld, square and
+// row-sum them in fp64 and keep only one number per cell: V never reaches shared or global memory.
+// Two accumulator stages (2 x 256 TMEM columns) let the epilogue of row block jb overlap the MMAs
+// of jb+1.  L^-1 is lower triangular, so row block jb only walks k < 256 (jb+1).
+//
+// CG = 2 (default): the two CTAs of a cluster (one TPC) run tcgen05.mma.cta_group::2 -- each CTA
+// owns 128 cells (its own A tiles, its own accumulators) and HALF of every B tile (128 of the 256
+// rows of L^-1), which the tensor cores of both SMs read.  That halves the shared-memory operand
+// reads and the L2->SM traffic of L^-1 per SM, the two things that capped the 1-CTA kernel
+// (profiles/ncu_posterior_tc_r01.md).  CG = 1 is the single-CTA form of the same code.
 //
 // Warp roles (512 threads, 1 CTA/SM, persistent over cell tiles):
-//   0      TMA producer (one lane)          1  MMA issuer (one lane)      2  TMEM alloc/dealloc
+//   0      TMA producer (one lane)     1  MMA issuer (one lane, leader CTA)    2  TMEM alloc/dealloc
 //   4-7    epilogue (TMEM lane quarter = warp % 4)
-//   8-11   K* generators for even k-chunks  12-15  K* generators for odd k-chunks
+//   8-15   K* generators: warp w -> cells 32 (w & 3) .. +31, observations 32 ((w - 8) >> 2) .. +31 of the chunk
 #include <cuda.h>
+#include <cuda_fp16.h>
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "common.cuh"
 
 namespace sbo {
 namespace {
 
-constexpr int BM = 128;          // cells per tile (UMMA M)
+constexpr int BM = 128;          // cells per CTA tile (UMMA M per CTA)
 constexpr int BN = 256;          // rows of L^-1 per accumulator (UMMA N)
-constexpr int BK = 32;           // k per stage: 32 fp32 = one 128-byte swizzle row
-constexpr int UK = 8;            // k per tcgen05.mma kind::tf32
-constexpr int kStages = 2;
+constexpr int BK = 64;           // k per stage: 64 fp16 = one 128-byte swizzle row
+constexpr int UK = 16;           // k per tcgen05.mma kind::f16
 constexpr int kThreadsTc = 512;
-constexpr uint32_t kABytes = BM * BK * 4;   // 16 KB per plane
-constexpr uint32_t kBBytes = BN * BK * 4;   // 32 KB per plane
-constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // 96 KB
+constexpr uint32_t kABytes = BM * BK * 2;   // 16 KB per plane
 constexpr uint32_t kTmemCols = 512;
 
+template <int CG> struct TcCfg {
+  static constexpr uint32_t kBRows = BN / CG;                    // rows of a B tile held by one CTA
+  static constexpr uint32_t kBBytes = kBRows * BK * 2;           // 32 KB (CG=1) / 16 KB (CG=2) per plane
+  static constexpr uint32_t kStageBytes = 2 * kABytes + 2 * kBBytes;  // 96 KB / 64 KB
+  static constexpr int kStages = CG == 1 ? 2 : 3;
+};
+
 struct __align__(16) TcShared {
-  unsigned long long full[kStages];
-  unsigned long long empty[kStages];
-  unsigned long long tmem_full[2];
-  unsigned long long tmem_empty[2];
+  unsigned long long full[4];      // leader CTA's copy is the one in use
+  unsigned long long empty[4];     // local (tcgen05.commit multicasts to both CTAs)
+  unsigned long long tmem_full[2]; // local
+  unsigned long long tmem_empty[2];// leader CTA's copy is the one in use
   uint32_t tmem_base;
   uint32_t pad[3];
-  float4 scratch[8][32];        // per generator warp: (x_rel, y-term, alpha, -) of the 32 observations of a chunk
-  float mu_part[2][BM];         // odd-chunk group's partial mu, double-buffered by tile parity
+  float4 obs_x[8][8];              // per generator warp: scaled x - tile origin of its 32 observations
+  float4 obs_y[8][8];              //   y factor of K* (incl. sigma_f^2 and the A scale)
+  float4 obs_a[8][8];              //   alpha
+  float mu_part[2][BM];            // second k-half's partial mu, double-buffered by tile parity
 };
-constexpr size_t kSmemBytes = 1024 /*align slack*/ + (size_t)kStages * kStageBytes + sizeof(TcShared);
 
 struct TcParams {
   const double* xy;        // [n][2] fp64 observation coordinates
@@ -62,20 +77,44 @@ struct TcParams {
   int accumulate;
   int W, rows_local, row0; // this shard: grid rows [row0, row0 + rows_local)
   double x0, y0, rx, ry;
-  float frx;               // (float) rx
+  double xscale;           // sqrt(log2(e) / (2 l^2)): coordinates are pre-scaled so that K* = ex2(-dx^2) ey
   float neg_c2;            // -log2(e) / (2 l^2)
-  float log2_sf2;          // log2(sigma_f^2)
+  float a_scale;           // sigma_f^2 2^shift_a
+  float mu_unscale;        // 2^-shift_a
+  double v_unscale2;       // 2^(-2 (shift_a + shift_b))
+  float v_unscale;         // 2^-(shift_a + shift_b) (debug dump only)
   float sf2, prior_mean;
   float* dbg_v;            // debug: V of tile 0 ([128][n_cap]) when non-null
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// shared::cluster address of `local` (a shared::cta address) in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t mapa(uint32_t local, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 
 __device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
-__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+// arrive on a barrier addressed in the shared::cluster window (own or peer CTA).  Default .release.cta /
+// .acquire.cta semantics on purpose: cluster-scope acquire makes ptxas emit CCTL.IVALL (an L1 flush) after
+// every wait; the data handed over lives in shared memory and is ordered by fence.proxy.async.
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_local(unsigned long long* bar) {
   asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, uint32_t bytes) {
@@ -101,36 +140,66 @@ __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
-__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, unsigned long long* bar, void* dst, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
-          smem_u32(dst)),
-      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
-      : "memory");
+// TMA: 2-D box into this CTA's shared memory; completion bytes are signalled on `bar_cluster_addr`
+// (a shared::cluster address: the leader CTA's barrier when CG = 2).
+template <int CG>
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint32_t bar_cluster_addr, void* dst, int c0, int c1) {
+  if constexpr (CG == 1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+        : "memory");
+  } else {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1)
+        : "memory");
+  }
 }
 
-__device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t cols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+template <int CG> __device__ __forceinline__ void tmem_alloc(uint32_t* slot, uint32_t cols) {
+  if constexpr (CG == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  } else {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
 }
-__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+template <int CG> __device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+  if constexpr (CG == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+  else asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
 }
 
-// D[tmem] (+)= A[smem] . B[smem]^T, kind::tf32, issued by one thread for the CTA.
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
-      "}" ::"r"(d_tmem),
-      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-      : "memory");
+// D[tmem] (+)= A[smem] . B[smem]^T, kind::f16 (fp16 operands, fp32 accumulate), issued by one thread.
+template <int CG>
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  if constexpr (CG == 1) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
 }
-// mbarrier arrive when every tcgen05.mma issued so far by this thread has completed.
-__device__ __forceinline__ void umma_commit(unsigned long long* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+// mbarrier arrive (in every CTA of the group) when every tcgen05.mma issued so far by this thread has completed.
+template <int CG> __device__ __forceinline__ void umma_commit(unsigned long long* bar) {
+  if constexpr (CG == 1) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+  } else {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                     smem_u32(bar)),
+                 "h"((uint16_t)3)
+                 : "memory");
+  }
 }
 
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
@@ -152,62 +221,111 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
-// Instruction descriptor: D=f32, A=B=tf32, both K-major, N=256, M=128.
-constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// Instruction descriptor: D=f32, A=B=f16 (format 0), both K-major, N=256, M=128 per CTA.
+template <int CG> struct IdescF16 {
+  static constexpr uint32_t value = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * CG) >> 4) << 24);
+};
 
-__device__ __forceinline__ float tf32_rna_bits(float x) {
-  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
-}
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-#ifndef SBO_TC_TERMS
-#define SBO_TC_TERMS 3 // 3: lo.hi + hi.lo + hi.hi   4: + lo.lo   1: hi.hi only (diagnostics)
-#endif
+__device__ __forceinline__ uint32_t h2_bits(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
 // number of k-chunks of row block jb
-__device__ __forceinline__ int chunks_of(int jb, int n_pad32) { return min(n_pad32, (jb + 1) * BN) / BK; }
+__device__ __forceinline__ int chunks_of(int jb, int n_pad) { return min(n_pad, (jb + 1) * BN) / BK; }
+
+// One thread's share of a K* chunk: cell r of the tile x 32 observations (4 groups of 8 = 4 16-byte
+// swizzle units of the row), written as fp16 hi / lo planes.  Returns sum_k K*[r,k] alpha[k] (scaled).
+//   K*[r,k] 2^shift_a = ex2(-(xs_k - cxs_r)^2) ey_k,   xs, cxs = x sqrt(log2(e) / 2 l^2),
+//   ey_k = sigma_f^2 2^shift_a ex2(-(y_k - y_row)^2 log2(e) / 2 l^2)
+// (the scale multiplies instead of shifting the exponent argument: the argument keeps its small magnitude,
+// so the MUFU input carries full fp32 resolution where K* is large).
+template <bool kMu>
+__device__ __forceinline__ float gen_chunk(const float4* ox4, const float4* oy4, const float4* oa4, float cxs,
+                                           uint8_t* pa_hi, uint8_t* pa_lo, uint32_t unit0, uint32_t swz) {
+  float mu = 0.f;
+#pragma unroll
+  for (int qd = 0; qd < 4; ++qd) {
+    const float4 xa = ox4[2 * qd], xb = ox4[2 * qd + 1];  // warp-wide broadcast loads
+    const float4 ya = oy4[2 * qd], yb = oy4[2 * qd + 1];
+    const float xs[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+    const float ey[8] = {ya.x, ya.y, ya.z, ya.w, yb.x, yb.y, yb.z, yb.w};
+    float kv[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float dx = xs[e] - cxs;
+      // MUFU ex2 is accurate enough here: swapping it for a 1-ulp polynomial changed neither mu nor
+      // sigma^2 errors (profiles/accuracy_r01.md); the error budget is set by the accumulator.
+      kv[e] = ex2_approx(-dx * dx) * ey[e];
+    }
+    if (kMu) {
+      const float4 aa = oa4[2 * qd], ab = oa4[2 * qd + 1];
+      const float as[8] = {aa.x, aa.y, aa.z, aa.w, ab.x, ab.y, ab.z, ab.w};
+#pragma unroll
+      for (int e = 0; e < 8; ++e) mu = fmaf(kv[e], as[e], mu);
+    }
+    uint32_t hi[4], lo[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const __half2 h = __floats2half2_rn(kv[2 * e], kv[2 * e + 1]);
+      const float2 hf = __half22float2(h);
+      hi[e] = h2_bits(h);
+      lo[e] = h2_bits(__floats2half2_rn(kv[2 * e] - hf.x, kv[2 * e + 1] - hf.y));
+    }
+    const uint32_t off = ((unit0 + (uint32_t)qd) ^ swz) << 4;
+    *reinterpret_cast<uint4*>(pa_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+    *reinterpret_cast<uint4*>(pa_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+  }
+  return mu;
+}
 
 // ---- the kernel ----------------------------------------------------------------------------------
+template <int CG>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
+  using Cfg = TcCfg<CG>;
+  constexpr int kStages = Cfg::kStages;
   extern __shared__ uint8_t smem_raw[];
   // 128B-swizzled tiles need 1024-byte alignment; pad by pointer arithmetic so the compiler keeps
-  // the shared address space (STS/LDS, not generic stores).
+  // the shared address space (STS/LDS, not generic stores).  The pad is identical in both CTAs of a
+  // pair, which the cta_group::2 descriptors rely on (same offsets in both shared memories).
   uint8_t* tiles = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  TcShared* sh = reinterpret_cast<TcShared*>(tiles + (size_t)kStages * kStageBytes);
-  // stage s: [A_hi 16K][A_lo 16K][B_hi 32K][B_lo 32K]
-  auto a_hi = [&](int s) { return tiles + (size_t)s * kStageBytes; };
-  auto a_lo = [&](int s) { return tiles + (size_t)s * kStageBytes + kABytes; };
-  auto b_hi = [&](int s) { return tiles + (size_t)s * kStageBytes + 2 * kABytes; };
-  auto b_lo = [&](int s) { return tiles + (size_t)s * kStageBytes + 2 * kABytes + kBBytes; };
+  TcShared* sh = reinterpret_cast<TcShared*>(tiles + (size_t)kStages * Cfg::kStageBytes);
+  // stage s: [A_hi 16K][A_lo 16K][B_hi][B_lo]
+  auto a_hi = [&](int s) { return tiles + (size_t)s * Cfg::kStageBytes; };
+  auto a_lo = [&](int s) { return tiles + (size_t)s * Cfg::kStageBytes + kABytes; };
+  auto b_hi = [&](int s) { return tiles + (size_t)s * Cfg::kStageBytes + 2 * kABytes; };
+  auto b_lo = [&](int s) { return tiles + (size_t)s * Cfg::kStageBytes + 2 * kABytes + Cfg::kBBytes; };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = CG == 1 ? 0u : cluster_ctarank();
   const int tiles_per_row = (p.W + BM - 1) / BM;
   const long long ntiles = (long long)p.rows_local * tiles_per_row;
-  const int n_pad32 = (p.n + BK - 1) / BK * BK;
+  const long long group = blockIdx.x / CG, ngroups = gridDim.x / CG;
+  const long long ngtiles = (ntiles + CG - 1) / CG;  // tiles of CTA groups
+  const int n_pad = (p.n + BK - 1) / BK * BK;
   const int jb_lo = p.j_lo / BN, jb_hi = (p.j_hi + BN - 1) / BN;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(&sh->full[s], 1 + 4);  // TMA producer + one lane of each of the 4 generator warps of the group
-      mbar_init(&sh->empty[s], 1);     // tcgen05.commit
+      mbar_init(&sh->full[s], 1 + 8 * CG);  // leader's TMA producer + every generator warp of the group
+      mbar_init(&sh->empty[s], 1);          // tcgen05.commit
     }
     for (int s = 0; s < 2; ++s) {
-      mbar_init(&sh->tmem_full[s], 1);   // tcgen05.commit
-      mbar_init(&sh->tmem_empty[s], 4);  // one lane of each epilogue warp
+      mbar_init(&sh->tmem_full[s], 1);        // tcgen05.commit
+      mbar_init(&sh->tmem_empty[s], 4 * CG);  // every epilogue warp of the group
     }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(&sh->tmem_base, kTmemCols);
+  if (warp == 2) tmem_alloc<CG>(&sh->tmem_base, kTmemCols);
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = sh->tmem_base;
 
@@ -215,31 +333,34 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     // =============================== TMA producer ===============================
     if (lane == 0) {
       uint32_t it = 0;
-      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      for (long long gt = group; gt < ngtiles; gt += ngroups) {
         for (int jb = jb_lo; jb < jb_hi; ++jb) {
-          const int nch = chunks_of(jb, n_pad32);
+          const int nch = chunks_of(jb, n_pad);
+          const int row = jb * BN + (int)rank * (int)Cfg::kBRows;
           for (int kc = 0; kc < nch; ++kc, ++it) {
             const int s = it % kStages;
             const uint32_t ph = (it / kStages) & 1u;
             mbar_wait(&sh->empty[s], ph ^ 1u);
-            mbar_arrive_expect_tx(&sh->full[s], 2 * kBBytes);
-            tma_load_2d(&tmap, &sh->full[s], b_hi(s), kc * BK, jb * BN);
-            tma_load_2d(&tmap, &sh->full[s], b_lo(s), kc * BK, p.n_cap + jb * BN);
+            const uint32_t bar = CG == 1 ? smem_u32(&sh->full[s]) : mapa(smem_u32(&sh->full[s]), 0);
+            if (rank == 0) mbar_arrive_expect_tx(&sh->full[s], 2 * Cfg::kBBytes * CG);
+            tma_load_2d<CG>(&tmap, bar, b_hi(s), kc * BK, row);
+            tma_load_2d<CG>(&tmap, bar, b_lo(s), kc * BK, p.n_cap + row);
           }
         }
       }
     }
+    __syncwarp();
   } else if (warp == 1) {
-    // =============================== MMA issuer ===============================
-    if (lane == 0) {
+    // =============================== MMA issuer (leader CTA) ===============================
+    if (lane == 0 && rank == 0) {
       uint32_t it = 0, acc_it = 0;
-      for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      for (long long gt = group; gt < ngtiles; gt += ngroups) {
         for (int jb = jb_lo; jb < jb_hi; ++jb, ++acc_it) {
           const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
           mbar_wait(&sh->tmem_empty[as], aph ^ 1u);  // epilogue has drained this accumulator
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * BN;
-          const int nch = chunks_of(jb, n_pad32);
+          const int nch = chunks_of(jb, n_pad);
           for (int kc = 0; kc < nch; ++kc, ++it) {
             const int s = it % kStages;
             const uint32_t ph = (it / kStages) & 1u;
@@ -248,33 +369,26 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(s))), dal = umma_desc_sw128(smem_u32(a_lo(s)));
             const uint64_t dbh = umma_desc_sw128(smem_u32(b_hi(s))), dbl = umma_desc_sw128(smem_u32(b_lo(s)));
 #pragma unroll
-            for (int k8 = 0; k8 < BK / UK; ++k8) {
-              const uint64_t adv = (uint64_t)((k8 * UK * 4) >> 4);  // +32 bytes along K inside the swizzle row
-#if SBO_TC_TERMS == 1
-              umma_tf32(d_tmem, dah + adv, dbh + adv, kIdesc, (kc | k8) != 0);
-#else
-#if SBO_TC_TERMS == 4
-              umma_tf32(d_tmem, dal + adv, dbl + adv, kIdesc, (kc | k8) != 0);
-              umma_tf32(d_tmem, dal + adv, dbh + adv, kIdesc, 1u);
-#else
-              umma_tf32(d_tmem, dal + adv, dbh + adv, kIdesc, (kc | k8) != 0);
-#endif
-              umma_tf32(d_tmem, dah + adv, dbl + adv, kIdesc, 1u);
-              umma_tf32(d_tmem, dah + adv, dbh + adv, kIdesc, 1u);
-#endif
+            for (int ks = 0; ks < BK / UK; ++ks) {
+              const uint64_t adv = (uint64_t)((ks * UK * 2) >> 4);  // +32 bytes along K inside the swizzle row
+              umma_f16<CG>(d_tmem, dal + adv, dbh + adv, IdescF16<CG>::value, (kc | ks) != 0);
+              umma_f16<CG>(d_tmem, dah + adv, dbl + adv, IdescF16<CG>::value, 1u);
+              umma_f16<CG>(d_tmem, dah + adv, dbh + adv, IdescF16<CG>::value, 1u);
             }
-            umma_commit(&sh->empty[s]);  // stage reusable once these MMAs have read it
+            umma_commit<CG>(&sh->empty[s]);  // stage reusable once these MMAs have read it
           }
-          umma_commit(&sh->tmem_full[as]);  // accumulator complete
+          umma_commit<CG>(&sh->tmem_full[as]);  // accumulator complete
         }
       }
     }
+    __syncwarp();
   } else if (warp >= 4 && warp < 8) {
     // =============================== epilogue ===============================
     const int q = warp & 3;
     const int r = q * 32 + lane;  // TMEM lane == row of the tile == cell
     uint32_t acc_it = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    for (long long gt = group; gt < ngtiles; gt += ngroups) {
+      const long long tile = gt * CG + rank;
       double rsum = 0.0;
       for (int jb = jb_lo; jb < jb_hi; ++jb, ++acc_it) {
         const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
@@ -291,17 +405,17 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           tmem_ld_wait();
           if (p.dbg_v && tile == 0) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) p.dbg_v[(size_t)r * p.n_cap + jc + i] = __uint_as_float(v[i]);
+            for (int i = 0; i < 32; ++i) p.dbg_v[(size_t)r * p.n_cap + jc + i] = __uint_as_float(v[i]) * p.v_unscale;
           }
-          const bool whole = (jc >= p.j_lo) && (jc + 32 <= p.j_hi);
+          if (jc < p.j_lo || jc + 32 > p.j_hi) {  // partial group (incremental step): mask the columns outside
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (jc + i < p.j_lo || jc + i >= p.j_hi) v[i] = 0u;
+          }
           double s0 = 0.0, s1 = 0.0;
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
-            double x0 = (double)__uint_as_float(v[i]), x1 = (double)__uint_as_float(v[i + 1]);
-            if (!whole) {
-              if (jc + i < p.j_lo || jc + i >= p.j_hi) x0 = 0.0;
-              if (jc + i + 1 < p.j_lo || jc + i + 1 >= p.j_hi) x1 = 0.0;
-            }
+            const double x0 = (double)__uint_as_float(v[i]), x1 = (double)__uint_as_float(v[i + 1]);
             s0 = fma(x0, x0, s0);
             s1 = fma(x1, x1, s1);
           }
@@ -309,95 +423,112 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sh->tmem_empty[as]);
+        if (lane == 0) {
+          if constexpr (CG == 1) mbar_arrive_local(&sh->tmem_empty[as]);
+          else mbar_arrive_cluster(mapa(smem_u32(&sh->tmem_empty[as]), 0));
+        }
       }
-      const int lrow = (int)(tile / tiles_per_row), col = (int)(tile % tiles_per_row) * BM + r;
-      if (col < p.W) {
-        const long long lc = (long long)lrow * p.W + col;
-        const double prev = p.accumulate ? (double)p.s2[lc] : (double)p.sf2;
-        p.s2[lc] = (float)(prev - rsum);
+      if (tile < ntiles) {
+        const int lrow = (int)(tile / tiles_per_row), col = (int)(tile % tiles_per_row) * BM + r;
+        if (col < p.W) {
+          const long long lc = (long long)lrow * p.W + col;
+          const double prev = p.accumulate ? (double)p.s2[lc] : (double)p.sf2;
+          p.s2[lc] = (float)(prev - rsum * p.v_unscale2);
+        }
       }
     }
   } else if (warp >= 8) {
     // =============================== K* generators ===============================
     const int gw = warp - 8;       // 0..7
-    const int grp = gw >> 2;       // 0: even chunks, 1: odd chunks
+    const int half = gw >> 2;      // which 32 of the chunk's 64 observations
     const int r = (gw & 3) * 32 + lane;
-    float4* scratch = sh->scratch[gw];
+    float* ox = reinterpret_cast<float*>(sh->obs_x[gw]);
+    float* oy = reinterpret_cast<float*>(sh->obs_y[gw]);
+    float* oa = reinterpret_cast<float*>(sh->obs_a[gw]);
     const uint32_t row_off = (uint32_t)r * 128u;
     const uint32_t swz = (uint32_t)(r & 7);
+    const float cxs = (float)((double)r * p.rx * p.xscale);  // scaled offset of this thread's cell from the tile origin
     uint32_t it = 0;
     uint32_t tile_par = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, tile_par ^= 1u) {
+    // observation data of the NEXT chunk is fetched while the current one is generated (chunk 0 always follows
+    // the last chunk of a row block, whatever the tile)
+    double2 o_next = make_double2(0.0, 0.0);
+    float a_next = 0.f;
+    {
+      const int k = half * 32 + lane;
+      if (k < p.n) {
+        o_next = *reinterpret_cast<const double2*>(p.xy + 2 * (size_t)k);
+        a_next = p.alpha[k];
+      }
+    }
+    for (long long gt = group; gt < ngtiles; gt += ngroups, tile_par ^= 1u) {
+      const long long tile = min(gt * CG + (long long)rank, ntiles - 1);  // an odd last tile: the peer recomputes it, no store
+      const bool live = gt * CG + rank < ntiles;
       const int lrow = (int)(tile / tiles_per_row), col0 = (int)(tile % tiles_per_row) * BM;
-      const double ox = cell_coord(p.x0, p.rx, col0), oy = cell_coord(p.y0, p.ry, p.row0 + lrow);
-      const float cxr = (float)r * p.frx;  // offset of this thread's cell from the tile origin
-      double mu_acc = 0.0;  // fp32 inside a 32-observation chunk, fp64 across chunks
+      const double ox0 = cell_coord(p.x0, p.rx, col0), oy0 = cell_coord(p.y0, p.ry, p.row0 + lrow);
+      double mu_acc = 0.0;  // fp32 inside a 32-observation half-chunk, fp64 across chunks
       for (int jb = jb_lo; jb < jb_hi; ++jb) {
         const bool last = (jb == jb_hi - 1);
-        const int nch = chunks_of(jb, n_pad32);
+        const int nch = chunks_of(jb, n_pad);
         for (int kc = 0; kc < nch; ++kc, ++it) {
-          if ((it & 1u) != (uint32_t)grp) continue;
           const int s = it % kStages;
           const uint32_t ph = (it / kStages) & 1u;
-          // per-observation terms of this chunk, one observation per lane
+          // per-observation terms of this half-chunk, one observation per lane
           {
-            const int k = kc * BK + lane;
-            float4 t = make_float4(0.f, -INFINITY, 0.f, 0.f);
+            const int k = kc * BK + half * 32 + lane;
+            float tx = 0.f, te = 0.f, ta = 0.f;
             if (k < p.n) {
-              const double2 o = *reinterpret_cast<const double2*>(p.xy + 2 * (size_t)k);
-              const float xr = (float)(o.x - ox), yr = (float)(o.y - oy);
-              t.x = xr;
-              t.y = fmaf(yr * yr, p.neg_c2, p.log2_sf2);
-              t.z = p.alpha[k];
+              const float yr = (float)(o_next.y - oy0);
+              tx = (float)((o_next.x - ox0) * p.xscale);
+              te = ex2_approx(yr * yr * p.neg_c2) * p.a_scale;
+              ta = a_next;
             }
             __syncwarp();  // previous chunk's readers are done with the scratch
-            scratch[lane] = t;
+            ox[lane] = tx;
+            oy[lane] = te;
+            oa[lane] = ta;
             __syncwarp();
+            const int kn = (kc + 1 < nch ? (kc + 1) * BK : 0) + half * 32 + lane;
+            if (kn < p.n) {
+              o_next = *reinterpret_cast<const double2*>(p.xy + 2 * (size_t)kn);
+              a_next = p.alpha[kn];
+            }
           }
           mbar_wait(&sh->empty[s], ph ^ 1u);  // MMAs that read this stage have completed
-          float mu_chunk = 0.f;
           uint8_t* pa_hi = a_hi(s) + row_off;
           uint8_t* pa_lo = a_lo(s) + row_off;
-#pragma unroll
-          for (int qd = 0; qd < BK / 4; ++qd) {
-            float hi[4], lo[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float4 t = scratch[qd * 4 + e];  // broadcast
-              const float dx = t.x - cxr;
-              // MUFU ex2 is accurate enough here: swapping it for a 1-ulp polynomial changed neither mu nor
-              // sigma^2 errors (profiles/accuracy_r01.md); the error budget is set by the accumulator.
-              const float kv = ex2_approx(fmaf(dx * dx, p.neg_c2, t.y));
-              mu_chunk = fmaf(kv, t.z, mu_chunk);
-              hi[e] = tf32_rna_bits(kv);
-              lo[e] = tf32_rna_bits(kv - hi[e]);
-            }
-            const uint32_t off = ((uint32_t)qd ^ swz) << 4;
-            *reinterpret_cast<float4*>(pa_hi + off) = make_float4(hi[0], hi[1], hi[2], hi[3]);
-            *reinterpret_cast<float4*>(pa_lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+          if (last) {
+            const float mu_chunk =
+                gen_chunk<true>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, pa_hi, pa_lo, (uint32_t)half * 4u, swz);
+            mu_acc += (double)mu_chunk;
+          } else {
+            gen_chunk<false>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, pa_hi, pa_lo, (uint32_t)half * 4u, swz);
           }
-          if (last) mu_acc += (double)mu_chunk;
           fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
           __syncwarp();
-          if (lane == 0) mbar_arrive(&sh->full[s]);
+          if (lane == 0) {
+            if constexpr (CG == 1) mbar_arrive_local(&sh->full[s]);
+            else mbar_arrive_cluster(mapa(smem_u32(&sh->full[s]), 0));
+          }
         }
       }
-      // combine the two groups' partial mu and write it out
-      if (grp == 1) sh->mu_part[tile_par][r] = (float)mu_acc;
+      // combine the two k-halves' partial mu and write it out
+      if (half == 1) sh->mu_part[tile_par][r] = (float)mu_acc;
       named_bar_sync(1, 256);
-      if (grp == 0) {
+      if (half == 0 && live) {
         const int col = col0 + r;
-        if (col < p.W) p.mu[(long long)lrow * p.W + col] = (float)((double)p.prior_mean + mu_acc + (double)sh->mu_part[tile_par][r]);
+        if (col < p.W)
+          p.mu[(long long)lrow * p.W + col] =
+              (float)((double)p.prior_mean + (mu_acc + (double)sh->mu_part[tile_par][r]) * (double)p.mu_unscale);
       }
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    tmem_dealloc<CG>(tmem_base, kTmemCols);
   }
 }
 
@@ -410,29 +541,51 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+template <int CG> constexpr size_t tc_smem_bytes() {
+  return 1024 /*align slack*/ + (size_t)TcCfg<CG>::kStages * TcCfg<CG>::kStageBytes + sizeof(TcShared);
+}
+
 }  // namespace
+
+// Power-of-two scales of the fp16 operand planes.  A = K* <= sigma_f^2; every entry of L^-1 is bounded by
+// ||L^-1||_2 = lambda_min(K)^-1/2 <= noise_var^-1/2 (K = k(X,X) + noise_var I), so both bounds hold for every
+// observation set and survive appends.  Scaled maxima stay <= 2^15 < 65504.
+void tc_plane_shifts(const sbo_config& cfg, int* shift_a, int* shift_b) {
+  const double sf2 = cfg.sigma_f * cfg.sigma_f;
+  const double bmax = 1.0 / std::sqrt(std::max(cfg.noise_var, 1e-30));
+  *shift_a = std::max(-60, std::min(60, (int)std::floor(15.0 - std::log2(sf2))));
+  *shift_b = std::max(-60, std::min(60, (int)std::floor(15.0 - std::log2(bmax))));
+}
 
 int32_t tc_init(sbo_ctx* ctx) {
   ctx->tc_ok = false;
+  if (!(ctx->cfg.noise_var > 0.0))
+    return fail(ctx, SBO_ERR_INVALID_ARG, "tc_init: the tcgen05 kernel needs noise_var > 0 (it bounds the fp16 planes of L^-1)");
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult qres;
   cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
   if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
     return fail(ctx, SBO_ERR_CUDA, "tc_init: cuTensorMapEncodeTiled not available from the driver");
+  int cg = 2;
+  if (const char* s = std::getenv("SBO_TC_CTA_GROUP")) cg = (std::atoi(s) == 1) ? 1 : 2;
+  ctx->tc_cg = cg;
+  tc_plane_shifts(ctx->cfg, &ctx->shift_a, &ctx->shift_b);
   CUtensorMap* map = new CUtensorMap;
   const cuuint64_t nc = (cuuint64_t)ctx->n_cap;
   const cuuint64_t gdim[2] = {nc, 2 * nc};                 // inner: k (columns of L^-1), outer: hi rows then lo rows
-  const cuuint64_t gstride[1] = {nc * sizeof(float)};      // bytes between rows
-  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)BN};
+  const cuuint64_t gstride[1] = {nc * sizeof(__half)};     // bytes between rows
+  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)(BN / cg)};
   const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = reinterpret_cast<EncodeTiledFn>(fn)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ctx->d_planes, gdim, gstride,
+  const CUresult r = reinterpret_cast<EncodeTiledFn>(fn)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, ctx->d_planes, gdim, gstride,
                                                          box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     delete map;
     return fail(ctx, SBO_ERR_CUDA, "tc_init: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
   }
-  e = cudaFuncSetAttribute(posterior_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes);
+  e = cudaFuncSetAttribute(posterior_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<1>());
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(posterior_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
   if (e != cudaSuccess) {
     delete map;
     return cuda_fail(ctx, e, "tc_init: cudaFuncSetAttribute(max dynamic smem)");
@@ -467,16 +620,39 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.rows_local = ctx->row1 - ctx->row0;
   p.row0 = ctx->row0;
   p.x0 = ctx->x0; p.y0 = ctx->y0; p.rx = ctx->rx; p.ry = ctx->ry;
-  p.frx = (float)ctx->rx;
   const double sf2 = ctx->cfg.sigma_f * ctx->cfg.sigma_f;
   p.neg_c2 = (float)(-1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
-  p.log2_sf2 = (float)std::log2(sf2);
+  p.xscale = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
+  p.a_scale = (float)std::ldexp(sf2, ctx->shift_a);
+  p.mu_unscale = (float)std::ldexp(1.0, -ctx->shift_a);
+  p.v_unscale2 = std::ldexp(1.0, -2 * (ctx->shift_a + ctx->shift_b));
+  p.v_unscale = (float)std::ldexp(1.0, -(ctx->shift_a + ctx->shift_b));
   p.sf2 = (float)sf2;
   p.prior_mean = (float)ctx->cfg.prior_mean;
   p.dbg_v = g_dbg_v;
   const long long ntiles = (long long)p.rows_local * ((p.W + BM - 1) / BM);
-  const unsigned grid = (unsigned)std::min<long long>(ntiles, ctx->sm_count);  // persistent: one CTA per SM
-  posterior_tc_kernel<<<grid, kThreadsTc, kSmemBytes, ctx->stream>>>(*static_cast<CUtensorMap*>(ctx->tmap_planes), p);
+  const CUtensorMap& tmap = *static_cast<CUtensorMap*>(ctx->tmap_planes);
+  if (ctx->tc_cg == 1) {
+    const unsigned grid = (unsigned)std::min<long long>(ntiles, ctx->sm_count);  // persistent: one CTA per SM
+    posterior_tc_kernel<1><<<grid, kThreadsTc, tc_smem_bytes<1>(), ctx->stream>>>(tmap, p);
+  } else {
+    // persistent CTA pairs: one cluster of 2 per TPC
+    const long long pairs = std::min<long long>((ntiles + 1) / 2, ctx->sm_count / 2);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * pairs));
+    cfg.blockDim = dim3(kThreadsTc);
+    cfg.dynamicSmemBytes = tc_smem_bytes<2>();
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t e = cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2>, tmap, p);
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_kernel<2> (cluster launch)");
+  }
   SBO_LAUNCH_CHECK(ctx, "posterior_tc_kernel");
   return SBO_OK;
 }
