@@ -36,7 +36,7 @@ bool all_finite(const double* p, size_t count) {
 void free_all(sbo_ctx* c) {
   tc_destroy(c);
   void* dev[] = {c->d_xy, c->d_r, c->d_A, c->d_Linv, c->d_Dinv, c->d_alpha, c->d_w, c->d_small, c->d_info,
-                 c->d_planes, c->d_alpha_f32, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
+                 c->d_planes, c->d_alpha_f32, c->d_obs_f32, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
                  c->d_partials, c->d_result, c->d_ticket, c->d_frontier, c->d_sel_keys, c->d_sel_width, c->d_sel_out,
                  c->d_gather};
   for (void* p : dev)
@@ -207,6 +207,8 @@ int32_t sbo_create(const sbo_config* cfg, sbo_ctx** out) {
   if (cfg->precision == SBO_FP32) {
     CREATE_CUDA(cudaMalloc(&c->d_planes, sizeof(uint16_t) * 2 * nc * nc));
     CREATE_CUDA(cudaMemset(c->d_planes, 0, sizeof(uint16_t) * 2 * nc * nc));
+    CREATE_CUDA(cudaMalloc(&c->d_obs_f32, sizeof(float) * 4 * nc));
+    CREATE_CUDA(cudaMemset(c->d_obs_f32, 0, sizeof(float) * 4 * nc));
     CREATE_CUDA(cudaMalloc(&c->d_alpha_f32, sizeof(float) * nc));
     CREATE_CUDA(cudaMemset(c->d_alpha_f32, 0, sizeof(float) * nc));
   }

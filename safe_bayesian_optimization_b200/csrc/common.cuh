@@ -66,7 +66,7 @@ struct sbo_ctx {
   int shift_a = 0, shift_b = 0;  // power-of-two scales of the K* and L^-1 planes (tc_plane_shifts)
   int tc_cg = 2;                 // CTAs per tcgen05.mma group (2 = CTA pair, 1 = single CTA)
   float* d_alpha_f32 = nullptr;  // [n_cap]
-  float* d_obs_f32 = nullptr;    // unused by default
+  float* d_obs_f32 = nullptr;    // [n_cap] float4: scaled observation coordinates as fp32 (hi, lo) pairs (posterior_tc.cu)
   void* tmap_planes = nullptr;   // host copy of the CUtensorMap (128 B), 256-row box
   bool planes_valid = false;
 

@@ -23,10 +23,12 @@
 // reads and the L2->SM traffic of L^-1 per SM, the two things that capped the 1-CTA kernel
 // (profiles/ncu_posterior_tc_r01.md).  CG = 1 is the single-CTA form of the same code.
 //
-// Warp roles (512 threads, 1 CTA/SM, persistent over cell tiles):
+// Warp roles (768 threads, 1 CTA/SM, persistent over cell tiles):
 //   0      TMA producer (one lane)     1  MMA issuer (one lane, leader CTA)    2  TMEM alloc/dealloc
 //   4-7    epilogue (TMEM lane quarter = warp % 4)
-//   8-15   K* generators: warp w -> cells 32 (w & 3) .. +31, observations 32 ((w - 8) >> 2) .. +31 of the chunk
+//   8-23   K* generators: warp w -> cells 32 (w & 3) .. +31, observations 16 ((w - 8) >> 2) .. +15 of the chunk
+// (16 generator warps, 4 per scheduler: with 8 the serial latency of one warp's share of a chunk, not any
+// pipe, paced the tensor core -- profiles/ncu_posterior_tc_r01b.md)
 #include <cuda.h>
 #include <cuda_fp16.h>
 
@@ -43,7 +45,8 @@ constexpr int BM = 128;          // cells per CTA tile (UMMA M per CTA)
 constexpr int BN = 256;          // rows of L^-1 per accumulator (UMMA N)
 constexpr int BK = 64;           // k per stage: 64 fp16 = one 128-byte swizzle row
 constexpr int UK = 16;           // k per tcgen05.mma kind::f16
-constexpr int kThreadsTc = 512;
+constexpr int kThreadsTc = 768;
+constexpr int kGenWarps = 16;
 constexpr uint32_t kABytes = BM * BK * 2;   // 16 KB per plane
 constexpr uint32_t kTmemCols = 512;
 
@@ -61,14 +64,14 @@ struct __align__(16) TcShared {
   unsigned long long tmem_empty[2];// leader CTA's copy is the one in use
   uint32_t tmem_base;
   uint32_t pad[3];
-  float4 obs_x[8][8];              // per generator warp: scaled x - tile origin of its 32 observations
-  float4 obs_y[8][8];              //   y factor of K* (incl. sigma_f^2 and the A scale)
-  float4 obs_a[8][8];              //   alpha
-  float mu_part[2][BM];            // second k-half's partial mu, double-buffered by tile parity
+  float4 obs_x[kGenWarps][4];      // per generator warp: scaled x - tile origin of its 16 observations
+  float4 obs_y[kGenWarps][4];      //   y factor of K* (incl. sigma_f^2 and the A scale)
+  float4 obs_a[kGenWarps][4];      //   alpha
+  float mu_part[2][3][BM];         // partial mu of k-quarters 1..3, double-buffered by tile parity
 };
 
 struct TcParams {
-  const double* xy;        // [n][2] fp64 observation coordinates
+  const float4* obs;       // [n_cap] scaled observation coordinates (x_hi, x_lo, y_hi, y_lo), see pack_obs_kernel
   const float* alpha;      // [n_cap] fp32
   float* mu;               // [m_local]
   float* s2;               // [m_local]
@@ -78,7 +81,6 @@ struct TcParams {
   int W, rows_local, row0; // this shard: grid rows [row0, row0 + rows_local)
   double x0, y0, rx, ry;
   double xscale;           // sqrt(log2(e) / (2 l^2)): coordinates are pre-scaled so that K* = ex2(-dx^2) ey
-  float neg_c2;            // -log2(e) / (2 l^2)
   float a_scale;           // sigma_f^2 2^shift_a
   float mu_unscale;        // 2^-shift_a
   double v_unscale2;       // 2^(-2 (shift_a + shift_b))
@@ -222,9 +224,9 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
 // Instruction descriptor: D=f32, A=B=f16 (format 0), both K-major, N=256, M=128 per CTA.
-template <int CG> struct IdescF16 {
-  static constexpr uint32_t value = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((BM * CG) >> 4) << 24);
-};
+template <int CG> __device__ __forceinline__ uint32_t idesc_f16(uint32_t n_cols) {
+  return (1u << 4) | ((n_cols >> 3) << 17) | ((uint32_t)((BM * CG) >> 4) << 24);
+}
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
@@ -240,7 +242,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 // number of k-chunks of row block jb
 __device__ __forceinline__ int chunks_of(int jb, int n_pad) { return min(n_pad, (jb + 1) * BN) / BK; }
 
-// One thread's share of a K* chunk: cell r of the tile x 32 observations (4 groups of 8 = 4 16-byte
+// One thread's share of a K* chunk: cell r of the tile x 16 observations (2 groups of 8 = 2 16-byte
 // swizzle units of the row), written as fp16 hi / lo planes.  Returns sum_k K*[r,k] alpha[k] (scaled).
 //   K*[r,k] 2^shift_a = ex2(-(xs_k - cxs_r)^2) ey_k,   xs, cxs = x sqrt(log2(e) / 2 l^2),
 //   ey_k = sigma_f^2 2^shift_a ex2(-(y_k - y_row)^2 log2(e) / 2 l^2)
@@ -248,10 +250,10 @@ __device__ __forceinline__ int chunks_of(int jb, int n_pad) { return min(n_pad, 
 // so the MUFU input carries full fp32 resolution where K* is large).
 template <bool kMu>
 __device__ __forceinline__ float gen_chunk(const float4* ox4, const float4* oy4, const float4* oa4, float cxs,
-                                           uint8_t* pa_hi, uint8_t* pa_lo, uint32_t unit0, uint32_t swz) {
+                                           uint32_t (&hi)[8], uint32_t (&lo)[8]) {
   float mu = 0.f;
 #pragma unroll
-  for (int qd = 0; qd < 4; ++qd) {
+  for (int qd = 0; qd < 2; ++qd) {
     const float4 xa = ox4[2 * qd], xb = ox4[2 * qd + 1];  // warp-wide broadcast loads
     const float4 ya = oy4[2 * qd], yb = oy4[2 * qd + 1];
     const float xs[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
@@ -270,19 +272,40 @@ __device__ __forceinline__ float gen_chunk(const float4* ox4, const float4* oy4,
 #pragma unroll
       for (int e = 0; e < 8; ++e) mu = fmaf(kv[e], as[e], mu);
     }
-    uint32_t hi[4], lo[4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
       const __half2 h = __floats2half2_rn(kv[2 * e], kv[2 * e + 1]);
       const float2 hf = __half22float2(h);
-      hi[e] = h2_bits(h);
-      lo[e] = h2_bits(__floats2half2_rn(kv[2 * e] - hf.x, kv[2 * e + 1] - hf.y));
+      hi[4 * qd + e] = h2_bits(h);
+      lo[4 * qd + e] = h2_bits(__floats2half2_rn(kv[2 * e] - hf.x, kv[2 * e + 1] - hf.y));
     }
-    const uint32_t off = ((unit0 + (uint32_t)qd) ^ swz) << 4;
-    *reinterpret_cast<uint4*>(pa_hi + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-    *reinterpret_cast<uint4*>(pa_lo + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
   }
   return mu;
+}
+
+// fp32 double-word accumulation (2Sum): (hi, lo) += x without an fp64 instruction on the generators' path
+__device__ __forceinline__ void two_sum_acc(float& hi, float& lo, float x) {
+  const float t = hi + x;
+  const float z = t - hi;
+  lo += (hi - (t - z)) + (x - z);
+  hi = t;
+}
+
+// Observation coordinates for the generators: scaled by sqrt(log2(e) / 2 l^2) and split into fp32 (hi, lo)
+// pairs, so that a tile-relative coordinate is (x_hi - o_hi) + (x_lo - o_lo) in three fp32 adds -- exact to
+// ~1e-7 of its own magnitude wherever the grid sits -- instead of fp64 arithmetic once per chunk.
+__global__ void pack_obs_kernel(const double* __restrict__ xy, int n, int n_cap, double xscale, float4* __restrict__ out) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n_cap) return;
+  float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (k < n) {
+    const double x = xy[2 * (size_t)k] * xscale, y = xy[2 * (size_t)k + 1] * xscale;
+    o.x = (float)x;
+    o.y = (float)(x - (double)o.x);
+    o.z = (float)y;
+    o.w = (float)(y - (double)o.z);
+  }
+  out[k] = o;
 }
 
 // ---- the kernel ----------------------------------------------------------------------------------
@@ -314,7 +337,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(&sh->full[s], 1 + 8 * CG);  // leader's TMA producer + every generator warp of the group
+      mbar_init(&sh->full[s], 1 + kGenWarps * CG);  // leader's TMA producer + every generator warp of the group
       mbar_init(&sh->empty[s], 1);          // tcgen05.commit
     }
     for (int s = 0; s < 2; ++s) {
@@ -336,10 +359,13 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       for (long long gt = group; gt < ngtiles; gt += ngroups) {
         for (int jb = jb_lo; jb < jb_hi; ++jb) {
           const int nch = chunks_of(jb, n_pad);
-          const int row = jb * BN + (int)rank * (int)Cfg::kBRows;
           for (int kc = 0; kc < nch; ++kc, ++it) {
             const int s = it % kStages;
             const uint32_t ph = (it / kStages) & 1u;
+            // chunk c = kc - 4 jb >= 0 of the diagonal block only meets rows >= 64 c of this row block (L^-1 is
+            // lower triangular): the tile starts there and the MMA narrows to N = 256 - 64 c (see the issuer)
+            const int c = max(kc - jb * (BN / BK), 0);
+            const int row = jb * BN + c * BK + (int)rank * ((int)Cfg::kBRows - c * (BK / 2));
             mbar_wait(&sh->empty[s], ph ^ 1u);
             const uint32_t bar = CG == 1 ? smem_u32(&sh->full[s]) : mapa(smem_u32(&sh->full[s]), 0);
             if (rank == 0) mbar_arrive_expect_tx(&sh->full[s], 2 * Cfg::kBBytes * CG);
@@ -368,12 +394,15 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             tc_fence_after();
             const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(s))), dal = umma_desc_sw128(smem_u32(a_lo(s)));
             const uint64_t dbh = umma_desc_sw128(smem_u32(b_hi(s))), dbl = umma_desc_sw128(smem_u32(b_lo(s)));
+            // diagonal block, chunk c: columns < 64 c of the accumulator get no contribution (zeros of L^-1)
+            const uint32_t c = (uint32_t)max(kc - jb * (BN / BK), 0);
+            const uint32_t idesc = idesc_f16<CG>(BN - c * BK), d_col = d_tmem + c * BK;
 #pragma unroll
             for (int ks = 0; ks < BK / UK; ++ks) {
               const uint64_t adv = (uint64_t)((ks * UK * 2) >> 4);  // +32 bytes along K inside the swizzle row
-              umma_f16<CG>(d_tmem, dal + adv, dbh + adv, IdescF16<CG>::value, (kc | ks) != 0);
-              umma_f16<CG>(d_tmem, dah + adv, dbl + adv, IdescF16<CG>::value, 1u);
-              umma_f16<CG>(d_tmem, dah + adv, dbh + adv, IdescF16<CG>::value, 1u);
+              umma_f16<CG>(d_col, dal + adv, dbh + adv, idesc, (kc | ks) != 0);
+              umma_f16<CG>(d_col, dah + adv, dbl + adv, idesc, 1u);
+              umma_f16<CG>(d_col, dah + adv, dbh + adv, idesc, 1u);
             }
             umma_commit<CG>(&sh->empty[s]);  // stage reusable once these MMAs have read it
           }
@@ -412,14 +441,20 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             for (int i = 0; i < 32; ++i)
               if (jc + i < p.j_lo || jc + i >= p.j_hi) v[i] = 0u;
           }
-          double s0 = 0.0, s1 = 0.0;
+          // squares are exact inside the FMA; four 8-term fp32 partial sums (relative error <= ~1e-7 each,
+          // uncorrelated) then fp64: the fp32->fp64 conversions are XU-pipe instructions and would
+          // otherwise compete with the generators' MUFU.EX2 32 times per group instead of 4
+          float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            const double x0 = (double)__uint_as_float(v[i]), x1 = (double)__uint_as_float(v[i + 1]);
-            s0 = fma(x0, x0, s0);
-            s1 = fma(x1, x1, s1);
+          for (int i = 0; i < 32; i += 4) {
+            const float x0 = __uint_as_float(v[i]), x1 = __uint_as_float(v[i + 1]);
+            const float x2 = __uint_as_float(v[i + 2]), x3 = __uint_as_float(v[i + 3]);
+            s0 = fmaf(x0, x0, s0);
+            s1 = fmaf(x1, x1, s1);
+            s2 = fmaf(x2, x2, s2);
+            s3 = fmaf(x3, x3, s3);
           }
-          rsum += s0 + s1;
+          rsum += ((double)s0 + (double)s1) + ((double)s2 + (double)s3);
         }
         tc_fence_before();
         __syncwarp();
@@ -439,8 +474,8 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     }
   } else if (warp >= 8) {
     // =============================== K* generators ===============================
-    const int gw = warp - 8;       // 0..7
-    const int half = gw >> 2;      // which 32 of the chunk's 64 observations
+    const int gw = warp - 8;       // 0..15
+    const int kq = gw >> 2;        // which 16 of the chunk's 64 observations
     const int r = (gw & 3) * 32 + lane;
     float* ox = reinterpret_cast<float*>(sh->obs_x[gw]);
     float* oy = reinterpret_cast<float*>(sh->obs_y[gw]);
@@ -452,57 +487,51 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     uint32_t tile_par = 0;
     // observation data of the NEXT chunk is fetched while the current one is generated (chunk 0 always follows
     // the last chunk of a row block, whatever the tile)
-    double2 o_next = make_double2(0.0, 0.0);
+    float4 o_next = make_float4(0.f, 0.f, 0.f, 0.f);
     float a_next = 0.f;
-    {
-      const int k = half * 32 + lane;
-      if (k < p.n) {
-        o_next = *reinterpret_cast<const double2*>(p.xy + 2 * (size_t)k);
-        a_next = p.alpha[k];
-      }
+    if (lane < 16) {
+      o_next = p.obs[kq * 16 + lane];
+      a_next = p.alpha[kq * 16 + lane];
     }
     for (long long gt = group; gt < ngtiles; gt += ngroups, tile_par ^= 1u) {
       const long long tile = min(gt * CG + (long long)rank, ntiles - 1);  // an odd last tile: the peer recomputes it, no store
       const bool live = gt * CG + rank < ntiles;
       const int lrow = (int)(tile / tiles_per_row), col0 = (int)(tile % tiles_per_row) * BM;
-      const double ox0 = cell_coord(p.x0, p.rx, col0), oy0 = cell_coord(p.y0, p.ry, p.row0 + lrow);
-      double mu_acc = 0.0;  // fp32 inside a 32-observation half-chunk, fp64 across chunks
+      // scaled tile origin as an fp32 (hi, lo) pair
+      const double ox0 = cell_coord(p.x0, p.rx, col0) * p.xscale, oy0 = cell_coord(p.y0, p.ry, p.row0 + lrow) * p.xscale;
+      const float oxh = (float)ox0, oxl = (float)(ox0 - (double)oxh);
+      const float oyh = (float)oy0, oyl = (float)(oy0 - (double)oyh);
+      float mu_hi = 0.f, mu_lo = 0.f;  // fp32 inside a 16-observation quarter-chunk, double-word fp32 across chunks
       for (int jb = jb_lo; jb < jb_hi; ++jb) {
         const bool last = (jb == jb_hi - 1);
         const int nch = chunks_of(jb, n_pad);
         for (int kc = 0; kc < nch; ++kc, ++it) {
           const int s = it % kStages;
           const uint32_t ph = (it / kStages) & 1u;
-          // per-observation terms of this half-chunk, one observation per lane
-          {
-            const int k = kc * BK + half * 32 + lane;
-            float tx = 0.f, te = 0.f, ta = 0.f;
-            if (k < p.n) {
-              const float yr = (float)(o_next.y - oy0);
-              tx = (float)((o_next.x - ox0) * p.xscale);
-              te = ex2_approx(yr * yr * p.neg_c2) * p.a_scale;
-              ta = a_next;
-            }
-            __syncwarp();  // previous chunk's readers are done with the scratch
-            ox[lane] = tx;
-            oy[lane] = te;
-            oa[lane] = ta;
-            __syncwarp();
-            const int kn = (kc + 1 < nch ? (kc + 1) * BK : 0) + half * 32 + lane;
-            if (kn < p.n) {
-              o_next = *reinterpret_cast<const double2*>(p.xy + 2 * (size_t)kn);
-              a_next = p.alpha[kn];
-            }
+          // per-observation terms of this quarter-chunk, one observation per lane (lanes 0-15)
+          if (lane < 16) {
+            const int k = kc * BK + kq * 16 + lane;
+            const float yr = (o_next.z - oyh) + (o_next.w - oyl);
+            ox[lane] = (o_next.x - oxh) + (o_next.y - oxl);  // (the previous chunk's readers passed the __syncwarp below)
+            oy[lane] = k < p.n ? ex2_approx(-yr * yr) * p.a_scale : 0.f;
+            oa[lane] = a_next;
+            const int kn = (kc + 1 < nch ? (kc + 1) * BK : 0) + kq * 16 + lane;  // < n_cap: the buffers are padded
+            o_next = p.obs[kn];
+            a_next = p.alpha[kn];
           }
+          __syncwarp();
+          uint32_t hi[8], lo[8];
+          if (last) two_sum_acc(mu_hi, mu_lo, gen_chunk<true>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, hi, lo));
+          else gen_chunk<false>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, hi, lo);
           mbar_wait(&sh->empty[s], ph ^ 1u);  // MMAs that read this stage have completed
-          uint8_t* pa_hi = a_hi(s) + row_off;
-          uint8_t* pa_lo = a_lo(s) + row_off;
-          if (last) {
-            const float mu_chunk =
-                gen_chunk<true>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, pa_hi, pa_lo, (uint32_t)half * 4u, swz);
-            mu_acc += (double)mu_chunk;
-          } else {
-            gen_chunk<false>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, pa_hi, pa_lo, (uint32_t)half * 4u, swz);
+          {
+            uint8_t* pa_hi = a_hi(s) + row_off;
+            uint8_t* pa_lo = a_lo(s) + row_off;
+            const uint32_t off0 = (((uint32_t)kq * 2u) ^ swz) << 4, off1 = (((uint32_t)kq * 2u + 1u) ^ swz) << 4;
+            *reinterpret_cast<uint4*>(pa_hi + off0) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(pa_lo + off0) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            *reinterpret_cast<uint4*>(pa_hi + off1) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+            *reinterpret_cast<uint4*>(pa_lo + off1) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
           }
           fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
           __syncwarp();
@@ -512,14 +541,17 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           }
         }
       }
-      // combine the two k-halves' partial mu and write it out
-      if (half == 1) sh->mu_part[tile_par][r] = (float)mu_acc;
-      named_bar_sync(1, 256);
-      if (half == 0 && live) {
+      const double mu_acc = (double)mu_hi + (double)mu_lo;
+      // combine the four k-quarters' partial mu and write it out
+      if (kq > 0) sh->mu_part[tile_par][kq - 1][r] = (float)mu_acc;
+      named_bar_sync(1, kGenWarps * 32);
+      if (kq == 0 && live) {
         const int col = col0 + r;
-        if (col < p.W)
-          p.mu[(long long)lrow * p.W + col] =
-              (float)((double)p.prior_mean + (mu_acc + (double)sh->mu_part[tile_par][r]) * (double)p.mu_unscale);
+        if (col < p.W) {
+          const double part = (double)sh->mu_part[tile_par][0][r] + (double)sh->mu_part[tile_par][1][r] +
+                              (double)sh->mu_part[tile_par][2][r];
+          p.mu[(long long)lrow * p.W + col] = (float)((double)p.prior_mean + (mu_acc + part) * (double)p.mu_unscale);
+        }
       }
     }
   }
@@ -607,7 +639,7 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   if (!ctx->tc_ok) return fail(ctx, SBO_ERR_STATE, "tcgen05 kernel not initialised");
   if (ctx->m_local == 0) return SBO_OK;
   TcParams p;
-  p.xy = ctx->d_xy;
+  p.obs = reinterpret_cast<const float4*>(ctx->d_obs_f32);
   p.alpha = ctx->d_alpha_f32;
   p.mu = static_cast<float*>(ctx->d_mu);
   p.s2 = static_cast<float*>(ctx->d_s2);
@@ -621,7 +653,6 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.row0 = ctx->row0;
   p.x0 = ctx->x0; p.y0 = ctx->y0; p.rx = ctx->rx; p.ry = ctx->ry;
   const double sf2 = ctx->cfg.sigma_f * ctx->cfg.sigma_f;
-  p.neg_c2 = (float)(-1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
   p.xscale = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
   p.a_scale = (float)std::ldexp(sf2, ctx->shift_a);
   p.mu_unscale = (float)std::ldexp(1.0, -ctx->shift_a);
@@ -630,6 +661,9 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.sf2 = (float)sf2;
   p.prior_mean = (float)ctx->cfg.prior_mean;
   p.dbg_v = g_dbg_v;
+  pack_obs_kernel<<<(ctx->n_cap + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_xy, ctx->n, ctx->n_cap, p.xscale,
+                                                                     reinterpret_cast<float4*>(ctx->d_obs_f32));
+  SBO_LAUNCH_CHECK(ctx, "pack_obs_kernel");
   const long long ntiles = (long long)p.rows_local * ((p.W + BM - 1) / BM);
   const CUtensorMap& tmap = *static_cast<CUtensorMap*>(ctx->tmap_planes);
   if (ctx->tc_cg == 1) {
