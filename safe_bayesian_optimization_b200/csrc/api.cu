@@ -45,6 +45,9 @@ void free_all(sbo_ctx* c) {
   if (c->h_sel_out) cudaFreeHost(c->h_sel_out);
   for (auto& e : c->ev)
     if (e) cudaEventDestroy(e);
+  for (auto& e : c->ev_factor) cudaEventDestroy(e);
+  c->ev_factor.clear();
+  if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
 }
 

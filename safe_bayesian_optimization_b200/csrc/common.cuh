@@ -38,6 +38,8 @@ struct sbo_ctx {
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev[6]{};
+  cudaStream_t aux_stream = nullptr;      // second chain of the factorisation (rows of L^-1)
+  std::vector<cudaEvent_t> ev_factor;     // [0] fork/join, [1 + 2k] diag k done, [2 + 2k] panel k done
   std::string err;
   int64_t launches = 0;
 

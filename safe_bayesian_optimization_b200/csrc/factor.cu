@@ -29,86 +29,110 @@ constexpr int TK = 16;         // K depth per shared-memory stage
 constexpr int kGemmThreads = 256;
 
 // ---------------------------------------------------------------------------------------------
-// 128x128 fp64 tile: acc[8][8] per thread.  Thread (ty, tx) = (tid / 16, tid % 16) owns rows
-// {g*32 + ty*2 + v} and columns {g*32 + tx*2 + v}, g in 0..3, v in 0..1, so every shared-memory
-// read is a 16-byte vector and the 16 lanes of a half-warp read 256 contiguous bytes.
+// TM x TM fp64 tile (TM = 128: acc[8][8] per thread, TM = 64: acc[4][4]), 256 threads.  Thread
+// (ty, tx) = (tid / 16, tid % 16) owns rows {g*32 + ty*2 + v} and columns {g*32 + tx*2 + v},
+// g in 0..TM/32-1, v in 0..1, so every shared-memory read is a 16-byte vector and the 16 lanes of a
+// half-warp read 256 contiguous bytes.  The 64-tile is for small n, where a launch has fewer
+// 128-tiles than the GPU has SMs and the step time is one thread's serial FMA count: a quarter of
+// the work per thread, four times the CTAs.
 // ---------------------------------------------------------------------------------------------
-struct TileSmem {
-  double a[TK][NB];  // a[kk][row]
-  double b[TK][NB];  // b[kk][col]
+template <int TM> struct TileSmem {
+  double a[TK][TM];  // a[kk][row]
+  double b[TK][TM];  // b[kk][col]
 };
 
-__device__ __forceinline__ void tile_zero(double (&acc)[8][8]) {
+template <int R> __device__ __forceinline__ void tile_zero(double (&acc)[R][R]) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i)
+  for (int i = 0; i < R; ++i)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.0;
+    for (int j = 0; j < R; ++j) acc[i][j] = 0.0;
 }
 
-// Stage a 128 x TK chunk of a K-contiguous operand (rows r0.., columns k0..) transposed into
-// s[kk][row].  Thread t reads 8 consecutive doubles of row t/2.
-__device__ __forceinline__ void stage_kmajor(double (*s)[NB], const double* __restrict__ src, int ld, int r0, int k0) {
+// Stage a TM x TK chunk of a K-contiguous operand (rows r0.., columns k0..) transposed into
+// s[kk][row].  Thread t reads 2048 / 256 / (128 / TM) consecutive doubles of one row.
+template <int TM>
+__device__ __forceinline__ void stage_kmajor(double (*s)[TM], const double* __restrict__ src, int ld, int r0, int k0) {
   const int t = threadIdx.x;
-  const int row = t >> 1, kq = (t & 1) * 8;
-  const double2* p = reinterpret_cast<const double2*>(src + (size_t)(r0 + row) * ld + k0 + kq);
-  double2 v0 = p[0], v1 = p[1], v2 = p[2], v3 = p[3];
-  s[kq + 0][row] = v0.x; s[kq + 1][row] = v0.y;
-  s[kq + 2][row] = v1.x; s[kq + 3][row] = v1.y;
-  s[kq + 4][row] = v2.x; s[kq + 5][row] = v2.y;
-  s[kq + 6][row] = v3.x; s[kq + 7][row] = v3.y;
+  if (TM == 128) {
+    const int row = t >> 1, kq = (t & 1) * 8;
+    const double2* p = reinterpret_cast<const double2*>(src + (size_t)(r0 + row) * ld + k0 + kq);
+    double2 v0 = p[0], v1 = p[1], v2 = p[2], v3 = p[3];
+    s[kq + 0][row] = v0.x; s[kq + 1][row] = v0.y;
+    s[kq + 2][row] = v1.x; s[kq + 3][row] = v1.y;
+    s[kq + 4][row] = v2.x; s[kq + 5][row] = v2.y;
+    s[kq + 6][row] = v3.x; s[kq + 7][row] = v3.y;
+  } else {
+    const int row = t >> 2, kq = (t & 3) * 4;
+    const double2* p = reinterpret_cast<const double2*>(src + (size_t)(r0 + row) * ld + k0 + kq);
+    double2 v0 = p[0], v1 = p[1];
+    s[kq + 0][row] = v0.x; s[kq + 1][row] = v0.y;
+    s[kq + 2][row] = v1.x; s[kq + 3][row] = v1.y;
+  }
 }
 
-// Stage a TK x 128 chunk of a row-major operand (rows k0.., columns c0..) as is: s[kk][col].
-__device__ __forceinline__ void stage_rowmajor(double (*s)[NB], const double* __restrict__ src, int ld, int k0, int c0) {
+// Stage a TK x TM chunk of a row-major operand (rows k0.., columns c0..) as is: s[kk][col].
+template <int TM>
+__device__ __forceinline__ void stage_rowmajor(double (*s)[TM], const double* __restrict__ src, int ld, int k0, int c0) {
   const int t = threadIdx.x;
-  const int kk = t >> 4, cq = (t & 15) * 8;
-  const double2* p = reinterpret_cast<const double2*>(src + (size_t)(k0 + kk) * ld + c0 + cq);
-  double2* d = reinterpret_cast<double2*>(&s[kk][cq]);
-  d[0] = p[0]; d[1] = p[1]; d[2] = p[2]; d[3] = p[3];
+  if (TM == 128) {
+    const int kk = t >> 4, cq = (t & 15) * 8;
+    const double2* p = reinterpret_cast<const double2*>(src + (size_t)(k0 + kk) * ld + c0 + cq);
+    double2* d = reinterpret_cast<double2*>(&s[kk][cq]);
+    d[0] = p[0]; d[1] = p[1]; d[2] = p[2]; d[3] = p[3];
+  } else {
+    const int kk = t >> 4, cq = (t & 15) * 4;
+    const double2* p = reinterpret_cast<const double2*>(src + (size_t)(k0 + kk) * ld + c0 + cq);
+    double2* d = reinterpret_cast<double2*>(&s[kk][cq]);
+    d[0] = p[0]; d[1] = p[1];
+  }
 }
 
-__device__ __forceinline__ void tile_mac(const TileSmem& sm, double (&acc)[8][8]) {
+template <int TM>
+__device__ __forceinline__ void tile_mac(const TileSmem<TM>& sm, double (&acc)[TM / 16][TM / 16]) {
+  constexpr int G = TM / 32;
   const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
 #pragma unroll
   for (int kk = 0; kk < TK; ++kk) {
-    double a[8], b[8];
+    double a[2 * G], b[2 * G];
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
+    for (int g = 0; g < G; ++g) {
       const double2 av = *reinterpret_cast<const double2*>(&sm.a[kk][g * 32 + ty * 2]);
       const double2 bv = *reinterpret_cast<const double2*>(&sm.b[kk][g * 32 + tx * 2]);
       a[2 * g] = av.x; a[2 * g + 1] = av.y;
       b[2 * g] = bv.x; b[2 * g + 1] = bv.y;
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < 2 * G; ++i)
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
+      for (int j = 0; j < 2 * G; ++j) acc[i][j] = fma(a[i], b[j], acc[i][j]);
   }
 }
 
 // acc = A[r0.., 0..K) * B^T (kNT: B rows c0.., K contiguous) or A * B (B rows 0..K, columns c0..).
-template <bool kNT>
-__device__ __forceinline__ void tile_gemm(TileSmem& sm, const double* A, int lda, int r0, int ka0, const double* B,
-                                          int ldb, int c0, int kb0, int K, double (&acc)[8][8]) {
+template <bool kNT, int TM>
+__device__ __forceinline__ void tile_gemm(TileSmem<TM>& sm, const double* A, int lda, int r0, int ka0, const double* B,
+                                          int ldb, int c0, int kb0, int K, double (&acc)[TM / 16][TM / 16]) {
   for (int k = 0; k < K; k += TK) {
-    stage_kmajor(sm.a, A, lda, r0, ka0 + k);
-    if (kNT) stage_kmajor(sm.b, B, ldb, c0, kb0 + k);
-    else stage_rowmajor(sm.b, B, ldb, kb0 + k, c0);
+    stage_kmajor<TM>(sm.a, A, lda, r0, ka0 + k);
+    if (kNT) stage_kmajor<TM>(sm.b, B, ldb, c0, kb0 + k);
+    else stage_rowmajor<TM>(sm.b, B, ldb, kb0 + k, c0);
     __syncthreads();
-    tile_mac(sm, acc);
+    tile_mac<TM>(sm, acc);
     __syncthreads();
   }
 }
 
 // C[r0.., c0..] = sign * acc (+ C if kAdd)
-template <bool kAdd>
-__device__ __forceinline__ void tile_store(double* C, int ldc, int r0, int c0, const double (&acc)[8][8], double sign) {
+template <bool kAdd, int TM>
+__device__ __forceinline__ void tile_store(double* C, int ldc, int r0, int c0, const double (&acc)[TM / 16][TM / 16],
+                                           double sign) {
+  constexpr int G = TM / 32;
   const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
+  for (int i = 0; i < 2 * G; ++i) {
     const int r = r0 + (i >> 1) * 32 + ty * 2 + (i & 1);
 #pragma unroll
-    for (int g = 0; g < 4; ++g) {
+    for (int g = 0; g < G; ++g) {
       double2* p = reinterpret_cast<double2*>(C + (size_t)r * ldc + c0 + g * 32 + tx * 2);
       double2 v = kAdd ? *p : make_double2(0.0, 0.0);
       v.x = fma(sign, acc[i][2 * g], v.x);
@@ -117,6 +141,10 @@ __device__ __forceinline__ void tile_store(double* C, int ldc, int r0, int c0, c
     }
   }
 }
+
+// sub-tile offsets of a TM-tile inside its 128-block: blockIdx.z enumerates the (128 / TM)^2 sub-tiles
+template <int TM> __device__ __forceinline__ int sub_r() { return TM == 128 ? 0 : (int)(blockIdx.z >> 1) * TM; }
+template <int TM> __device__ __forceinline__ int sub_c() { return TM == 128 ? 0 : (int)(blockIdx.z & 1) * TM; }
 
 // ---------------------------------------------------------------------------------------------
 // K matrix
@@ -138,133 +166,333 @@ __global__ void build_K_kernel(const double* __restrict__ xy, int n, int np, int
 }
 
 // ---------------------------------------------------------------------------------------------
-// Diagonal block: Cholesky + inverse of an nb x nb (nb <= 128) block in shared memory.
-// Lower triangle of S holds L, strict upper triangle holds X^T (X = L^-1), diagonals apart.
+// Diagonal block: Cholesky + inverse of an nb x nb (nb <= 128) block, one CTA, blocked by 32.
+//   for each 32-column panel kb:  warp 0 factors and inverts the 32x32 diagonal sub-block in
+//   registers (lane = row, shuffles broadcast the pivot column: no barrier inside the 32 steps);
+//   all warps then form the panel below it (A_ik X_kk^T) and the trailing update.
+//   The inverse of the whole block follows from the 32x32 inverses by block forward substitution.
+// Shared layout: lower triangle of S holds L, strict upper triangle holds X^T (X = L^-1), the two
+// diagonals live in dL / dX.  Blocks smaller than 128 are padded with the identity.
 // ---------------------------------------------------------------------------------------------
-constexpr int kDiagThreads = 512;
+constexpr int kDiagThreads = 256;
 constexpr int kDiagLd = NB + 1;
-constexpr size_t kDiagSmem = sizeof(double) * ((size_t)NB * kDiagLd + 2 * NB);
+constexpr int SB = 32;            // sub-block
+constexpr int kPanelLd = NB - SB; // 96: rows below the first sub-block
+struct DiagSmem {
+  double S[NB][kDiagLd];          // lower: L, strict upper: X^T
+  double P[SB][kPanelLd];         // current panel, transposed: P[t][i - (base + 32)] = L[i][base + t]
+  double Xd[NB / SB][SB][SB + 1]; // dense 32x32 inverses of the diagonal sub-blocks (zeros above the diagonal)
+  double Lt[SB][SB + 2];          // current sub-block's L^T (row stride even: 16-byte pairs)
+  double cb[2][SB];               // pivot-column broadcast, double-buffered
+  double dX[NB], dL[NB];
+  int bad;
+};
+constexpr size_t kDiagSmem = sizeof(DiagSmem);
+
+#ifdef SBO_DIAG_TIMING
+__device__ long long g_diag_t[16];
+#define DIAG_T(i) do { if (threadIdx.x == 0) g_diag_t[i] = clock64(); } while (0)
+#else
+#define DIAG_T(i) do {} while (0)
+#endif
+
+// Warp-level 32x32 Cholesky + inverse.  Lane r holds row r in registers; the pivot column is broadcast
+// through shared memory (one STS + a few LDS.128 per column: shuffles of doubles cost 4-8 issue cycles each
+// and 1000 of them paced the first version of this kernel).  Entries right of the diagonal hold garbage that
+// is never read.  Column j:  a[c] -= a[j] cb[c] / d  (d = pivot, cb = column j before scaling), then
+// a[j] *= d^-1/2.
+__device__ __forceinline__ void warp_chol_inv32(DiagSmem& sm, int base, int row_base, int* info) {
+  const int lane = threadIdx.x & 31;
+  double a[SB], rinv[SB];
+#pragma unroll
+  for (int c = 0; c < SB; ++c) a[c] = sm.S[base + lane][base + c];
+#pragma unroll
+  for (int j = 0; j < SB; ++j) {
+    double* cb = sm.cb[j & 1];
+    cb[lane] = a[j];
+    __syncwarp();
+    double d = cb[j];
+    if (!(d > 0.0)) {  // uniform
+      if (lane == 0) { sm.bad = 1; atomicCAS(info, 0, row_base + base + j + 1); }
+      d = 1.0;
+    }
+    const double ri = rsqrt(d);
+    rinv[j] = ri;
+    const double t = a[j] * (ri * ri);
+#pragma unroll
+    for (int c = j + 1; c < SB; ++c) a[c] = fma(-t, cb[c], a[c]);
+    a[j] = lane == j ? d * ri : a[j] * ri;
+  }
+  // L to shared memory: the lower triangle of S, the diagonal, and L^T for the inverse below
+#pragma unroll
+  for (int c = 0; c < SB; ++c) {
+    if (c < lane) sm.S[base + lane][base + c] = a[c];
+    if (c == lane) sm.dL[base + lane] = a[c];
+    sm.Lt[c][lane] = a[c];  // only [c][i >= c] is read
+  }
+  __syncwarp();
+  // X = L^-1 by column sweep: lane c owns column c; after x[p] is final, s[i] -= L[i][p] x[p] for i > p
+  double x[SB];
+#pragma unroll
+  for (int i = 0; i < SB; ++i) x[i] = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+  for (int q = 0; q < SB; ++q) {
+    x[q] *= rinv[q];
+#pragma unroll
+    for (int i = q + 1; i < SB; ++i) x[i] = fma(-sm.Lt[q][i], x[q], x[i]);
+  }
+#pragma unroll
+  for (int c = 0; c < SB; ++c) {
+    if (c > lane) sm.S[base + lane][base + c] = x[c];  // X[c][lane], transposed into the upper triangle
+    if (c == lane) sm.dX[base + lane] = x[c];
+    sm.Xd[base / SB][c][lane] = x[c];
+  }
+}
 
 __global__ void __launch_bounds__(kDiagThreads)
 diag_chol_inv_kernel(double* __restrict__ Ablk, int ld, int nb, double* __restrict__ Dinv, int ldd, int row_base,
                      int* __restrict__ info) {
-  extern __shared__ double smem_d[];
-  double* S = smem_d;                       // [NB][kDiagLd]
-  double* dX = smem_d + (size_t)NB * kDiagLd;  // 1 / L_ii
-  double* dL = dX + NB;                        // L_ii
-  __shared__ int bad;
-  const int tid = threadIdx.x;
-  if (tid == 0) bad = 0;
-  for (int e = tid; e < nb * nb; e += kDiagThreads) {
-    const int i = e / nb, j = e - i * nb;
-    S[i * kDiagLd + j] = (j <= i) ? Ablk[(size_t)i * ld + j] : 0.0;
+  extern __shared__ __align__(16) unsigned char smem_diag[];
+  DiagSmem& sm = *reinterpret_cast<DiagSmem*>(smem_diag);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) sm.bad = 0;
+#pragma unroll 4
+  for (int e = tid; e < NB * NB; e += kDiagThreads) {
+    const int i = e >> 7, j = e & (NB - 1);
+    double v = (i == j) ? 1.0 : 0.0;  // identity padding of a short block
+    if (i < nb && j < nb) v = (j <= i) ? Ablk[(size_t)i * ld + j] : 0.0;
+    sm.S[i][j] = v;
   }
+  DIAG_T(0);
   __syncthreads();
-  const int row = tid & (NB - 1), cg = tid >> 7;  // 4 column groups
-  // Right-looking column Cholesky.  The pivot sqrt goes to dL; S[j][j] keeps the pre-sqrt value so
-  // that no thread overwrites what another is still reading (two barriers per column).
-  for (int j = 0; j < nb; ++j) {
-    __syncthreads();  // trailing updates of column j-1 are complete
-    const double d = S[j * kDiagLd + j];
-    if (!(d > 0.0)) {  // uniform: every thread reads the same d
-      if (tid == 0) { bad = 1; atomicCAS(info, 0, row_base + j + 1); }
-      break;
-    }
-    const double piv = sqrt(d);
-    const double rinv = 1.0 / piv;
-    if (tid == 0) dL[j] = piv;
-    if (cg == 0 && row > j && row < nb) S[row * kDiagLd + j] *= rinv;
+  DIAG_T(1);
+
+  for (int kb = 0; kb < NB / SB; ++kb) {
+    const int base = kb * SB;
+    if (kb == 1) DIAG_T(6);
+    if (warp == 0) warp_chol_inv32(sm, base, row_base, info);
+    if (kb == 0) DIAG_T(3);
     __syncthreads();
-    if (row > j && row < nb) {
-      const double lij = S[row * kDiagLd + j];
-      for (int c = j + 1 + cg; c <= row; c += 4) S[row * kDiagLd + c] -= lij * S[c * kDiagLd + j];
-    }
-  }
-  __syncthreads();
-  if (bad) return;
-  // inverse: thread c owns column c of X; loops are uniform so L reads broadcast
-  if (tid < nb) dX[tid] = 1.0 / dL[tid];
-  __syncthreads();
-  if (tid < nb) {
-    const int c = tid;
-    for (int i = 1; i < nb; ++i) {
-      double s0 = 0.0, s1 = 0.0;
-      if (i > c) {
-        s0 = S[i * kDiagLd + c] * dX[c];  // p == c term: L[i][c] * X[c][c]
-        int p = c + 1;
-        for (; p + 1 < i; p += 2) {
-          s0 = fma(S[i * kDiagLd + p], S[c * kDiagLd + p], s0);
-          s1 = fma(S[i * kDiagLd + p + 1], S[c * kDiagLd + p + 1], s1);
-        }
-        if (p < i) s0 = fma(S[i * kDiagLd + p], S[c * kDiagLd + p], s0);
-        S[c * kDiagLd + i] = -(s0 + s1) * dX[i];  // X[i][c] stored transposed in the upper triangle
+    if (kb == 0) DIAG_T(4);
+    const int below = NB - base - SB;  // rows under the sub-block
+    if (below > 0) {
+      // ---- panel: L[i][base+c] = sum_t A[i][base+t] X[c][t], rows i = base+32+warp+8q ----
+      const int nq = below / 8;
+      double out[12];
+#pragma unroll
+      for (int q = 0; q < 12; ++q) out[q] = 0.0;
+#pragma unroll 4
+      for (int t = 0; t < SB; ++t) {
+        const double xv = sm.Xd[kb][lane][t];
+#pragma unroll
+        for (int q = 0; q < 12; ++q)
+          if (q < nq) out[q] = fma(sm.S[base + SB + warp + 8 * q][base + t], xv, out[q]);
       }
-      // X[.][c] is private to this thread: no barrier needed between rows
+      __syncthreads();
+#pragma unroll
+      for (int q = 0; q < 12; ++q)
+        if (q < nq) {
+          sm.S[base + SB + warp + 8 * q][base + lane] = out[q];
+          sm.P[lane][warp + 8 * q] = out[q];
+        }
+      __syncthreads();
+      if (kb == 0) DIAG_T(5);
+      // ---- trailing update: A[i][j] -= L[i][base..] . L[j][base..], sub-blocks ib >= jb; lane = column,
+      //      warp = 4 rows of every sub-block row ib ----
+      const int nsub = below / SB;
+      for (int jb = 0; jb < nsub; ++jb) {
+        double acc[3][4];
+#pragma unroll
+        for (int u = 0; u < 3; ++u)
+#pragma unroll
+          for (int v = 0; v < 4; ++v) acc[u][v] = 0.0;
+#pragma unroll 4
+        for (int t = 0; t < SB; ++t) {
+          const double lj = sm.P[t][jb * SB + lane];
+#pragma unroll
+          for (int u = 0; u < 3; ++u) {
+            if (jb + u < nsub) {
+              const double2 r01 = *reinterpret_cast<const double2*>(&sm.P[t][(jb + u) * SB + warp * 4]);
+              const double2 r23 = *reinterpret_cast<const double2*>(&sm.P[t][(jb + u) * SB + warp * 4 + 2]);
+              acc[u][0] = fma(r01.x, lj, acc[u][0]);
+              acc[u][1] = fma(r01.y, lj, acc[u][1]);
+              acc[u][2] = fma(r23.x, lj, acc[u][2]);
+              acc[u][3] = fma(r23.y, lj, acc[u][3]);
+            }
+          }
+        }
+        const int j = base + SB + jb * SB + lane;
+#pragma unroll
+        for (int u = 0; u < 3; ++u)
+          if (jb + u < nsub) {
+#pragma unroll
+            for (int v = 0; v < 4; ++v) {
+              const int i = base + SB + (jb + u) * SB + warp * 4 + v;
+              if (j <= i) sm.S[i][j] -= acc[u][v];  // the upper triangle holds X^T and must not be touched
+            }
+          }
+      }
+      __syncthreads();
     }
   }
-  __syncthreads();
-  for (int e = tid; e < nb * nb; e += kDiagThreads) {
-    const int i = e / nb, j = e - i * nb;
-    Ablk[(size_t)i * ld + j] = (j < i) ? S[i * kDiagLd + j] : (j == i ? dL[i] : 0.0);
-    Dinv[(size_t)i * ldd + j] = (j < i) ? S[j * kDiagLd + i] : (j == i ? dX[i] : 0.0);
+  DIAG_T(7);
+  if (sm.bad) return;
+
+  // ---- inverse of the whole block: X_ij = -X_ii sum_{p=j..i-1} L_ip X_pj for block row bi, block column bj < bi.
+  //      lane = column of block bj, warp + 8q = row of block bi ----
+  for (int bi = 1; bi < NB / SB; ++bi) {
+    double t[3][4];
+#pragma unroll
+    for (int bj = 0; bj < 3; ++bj)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) t[bj][q] = 0.0;
+#pragma unroll
+    for (int bj = 0; bj < 3; ++bj) {
+      if (bj < bi) {
+        // k in the diagonal block bj: dense copy, no masks
+#pragma unroll 4
+        for (int k = 0; k < SB; ++k) {
+          const double xv = sm.Xd[bj][k][lane];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) t[bj][q] = fma(sm.S[bi * SB + warp + 8 * q][bj * SB + k], xv, t[bj][q]);
+        }
+        // k in the blocks between: X[k][col] lives transposed in the upper triangle
+#pragma unroll 4
+        for (int k = (bj + 1) * SB; k < bi * SB; ++k) {
+          const double xv = sm.S[bj * SB + lane][k];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) t[bj][q] = fma(sm.S[bi * SB + warp + 8 * q][k], xv, t[bj][q]);
+        }
+      }
+    }
+    __syncthreads();
+    // park T (as T^T) where X_ij will live: S[col][row] of the upper triangle, still unused
+#pragma unroll
+    for (int bj = 0; bj < 3; ++bj)
+      if (bj < bi) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) sm.S[bj * SB + lane][bi * SB + warp + 8 * q] = t[bj][q];
+      }
+    __syncthreads();
+    double o[3][4];
+#pragma unroll
+    for (int bj = 0; bj < 3; ++bj)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) o[bj][q] = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < SB; ++k) {
+      double xr[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) xr[q] = sm.Xd[bi][warp + 8 * q][k];  // X_ii[r][k], zero for k > r
+#pragma unroll
+      for (int bj = 0; bj < 3; ++bj)
+        if (bj < bi) {
+          const double tv = sm.S[bj * SB + lane][bi * SB + k];  // T[k][col]
+#pragma unroll
+          for (int q = 0; q < 4; ++q) o[bj][q] = fma(xr[q], tv, o[bj][q]);
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int bj = 0; bj < 3; ++bj)
+      if (bj < bi) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) sm.S[bj * SB + lane][bi * SB + warp + 8 * q] = -o[bj][q];
+      }
+    __syncthreads();
   }
+
+  DIAG_T(8);
+#pragma unroll 4
+  for (int e = tid; e < NB * NB; e += kDiagThreads) {
+    const int i = e >> 7, j = e & (NB - 1);
+    if (i < nb && j < nb) {
+      const double lv = sm.S[i][j], xv = sm.S[j][i];
+      Ablk[(size_t)i * ld + j] = (j < i) ? lv : (j == i ? sm.dL[i] : 0.0);
+      Dinv[(size_t)i * ldd + j] = (j < i) ? xv : (j == i ? sm.dX[i] : 0.0);
+    }
+  }
+  DIAG_T(9);
 }
 
 // L_ik = A_ik D_k^T for row blocks i = k+1+blockIdx.x (in place).
+// In place: a TM=64 sub-tile reads the whole 128-wide row panel of A_ik and writes half of it, so the
+// result goes to `out` (a scratch panel) and is copied back by panel_copy_kernel.
+template <int TM>
 __global__ void __launch_bounds__(kGemmThreads)
-panel_trsm_kernel(double* __restrict__ A, int ld, int k, const double* __restrict__ Dk) {
-  __shared__ TileSmem sm;
-  const int r0 = (k + 1 + blockIdx.x) * NB, c0 = k * NB;
-  double acc[8][8];
+panel_trsm_kernel(const double* __restrict__ A, int ld, int k, const double* __restrict__ Dk, double* __restrict__ out,
+                  int ldo) {
+  __shared__ TileSmem<TM> sm;
+  const int r0 = (k + 1 + blockIdx.x) * NB + sub_r<TM>(), c0 = k * NB, cs = sub_c<TM>();
+  double acc[TM / 16][TM / 16];
   tile_zero(acc);
-  tile_gemm<true>(sm, A, ld, r0, c0, Dk, NB, 0, 0, NB, acc);  // C[r][j] = sum_p A[r][c0+p] D[j][p]
-  tile_store<false>(A, ld, r0, c0, acc, 1.0);
+  tile_gemm<true, TM>(sm, A, ld, r0, c0, Dk, NB, cs, 0, NB, acc);  // C[r][j] = sum_p A[r][c0+p] D[j][p]
+  tile_store<false, TM>(out, ldo, (int)blockIdx.x * NB + sub_r<TM>(), cs, acc, 1.0);
+}
+
+// A[(k+1) NB + r][k NB + c] = src[r][c]
+__global__ void panel_copy_kernel(double* __restrict__ A, int ld, int k, const double* __restrict__ src, int lds, int rows) {
+  const int c = threadIdx.x, r = blockIdx.x * blockDim.y + threadIdx.y;
+  if (r < rows) A[(size_t)((k + 1) * NB + r) * ld + k * NB + c] = src[(size_t)r * lds + c];
 }
 
 // A_ij -= L_ik L_jk^T over the lower block pairs i >= j > k.
+template <int TM>
 __global__ void __launch_bounds__(kGemmThreads)
 syrk_kernel(double* __restrict__ A, int ld, int k) {
-  __shared__ TileSmem sm;
+  __shared__ TileSmem<TM> sm;
   // blockIdx.x enumerates pairs (a >= b) of the trailing blocks: t = a(a+1)/2 + b
   int a = (int)((sqrt(8.0 * (double)blockIdx.x + 1.0) - 1.0) * 0.5);
   while ((a + 1) * (a + 2) / 2 <= (int)blockIdx.x) ++a;
   while (a * (a + 1) / 2 > (int)blockIdx.x) --a;
   const int b = blockIdx.x - a * (a + 1) / 2;
-  const int r0 = (k + 1 + a) * NB, c0 = (k + 1 + b) * NB, kc = k * NB;
-  double acc[8][8];
+  const int r0 = (k + 1 + a) * NB + sub_r<TM>(), c0 = (k + 1 + b) * NB + sub_c<TM>(), kc = k * NB;
+  double acc[TM / 16][TM / 16];
   tile_zero(acc);
-  tile_gemm<true>(sm, A, ld, r0, kc, A, ld, c0, kc, NB, acc);
-  tile_store<true>(A, ld, r0, c0, acc, -1.0);
+  tile_gemm<true, TM>(sm, A, ld, r0, kc, A, ld, c0, kc, NB, acc);
+  tile_store<true, TM>(A, ld, r0, c0, acc, -1.0);
 }
 
-// X_kc = D_k B_kc for c = blockIdx.x < k (in place in Linv); X_kk = D_k.
+// X_kc = D_k B_kc for c = blockIdx.x < k (in place in Linv: reads rows of block row k, columns of its own
+// sub-tile only, and writes that sub-tile... after reading ALL rows of the block row in those columns, so a
+// TM=64 sub-tile (upper half rows) would overwrite what the lower-half sub-tile still reads: `out` scratch
+// + row_copy_kernel, like the panel); X_kk = D_k.
+template <int TM>
 __global__ void __launch_bounds__(kGemmThreads)
-trtri_row_kernel(double* __restrict__ X, int ld, int k, const double* __restrict__ Dk) {
-  __shared__ TileSmem sm;
+trtri_row_kernel(const double* __restrict__ X, int ld, int k, const double* __restrict__ Dk, double* __restrict__ out,
+                 int ldo) {
+  __shared__ TileSmem<TM> sm;
   const int c = blockIdx.x;
-  const int r0 = k * NB, c0 = c * NB;
+  const int r0 = k * NB, c0 = c * NB + sub_c<TM>(), rs = sub_r<TM>();
   if (c == k) {
-    for (int e = threadIdx.x; e < NB * NB; e += kGemmThreads) {
-      const int i = e / NB, j = e - i * NB;
-      X[(size_t)(r0 + i) * ld + c0 + j] = Dk[(size_t)i * NB + j];
+    for (int e = threadIdx.x; e < TM * TM; e += kGemmThreads) {
+      const int i = e / TM, j = e - i * TM;
+      out[(size_t)(rs + i) * ldo + c0 + j] = Dk[(size_t)(rs + i) * NB + sub_c<TM>() + j];
     }
     return;
   }
-  double acc[8][8];
+  double acc[TM / 16][TM / 16];
   tile_zero(acc);
-  tile_gemm<false>(sm, Dk, NB, 0, 0, X, ld, c0, r0, NB, acc);  // C[r][j] = sum_p D[r][p] B[r0+p][c0+j]
-  tile_store<false>(X, ld, r0, c0, acc, 1.0);
+  tile_gemm<false, TM>(sm, Dk, NB, rs, 0, X, ld, c0, r0, NB, acc);  // C[r][j] = sum_p D[r][p] B[r0+p][c0+j]
+  tile_store<false, TM>(out, ldo, rs, c0, acc, 1.0);
+}
+
+// X[k NB + r][c] = src[r][c] for c < cols
+__global__ void row_copy_kernel(double* __restrict__ X, int ld, int k, const double* __restrict__ src, int lds, int cols) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x, r = blockIdx.y;
+  if (c < cols) X[(size_t)(k * NB + r) * ld + c] = src[(size_t)r * lds + c];
 }
 
 // B_ic -= L_ik X_kc for i = k+1+blockIdx.y, c = blockIdx.x <= k.
+template <int TM>
 __global__ void __launch_bounds__(kGemmThreads)
 trtri_update_kernel(double* __restrict__ X, int ld, const double* __restrict__ A, int k) {
-  __shared__ TileSmem sm;
-  const int r0 = (k + 1 + blockIdx.y) * NB, c0 = blockIdx.x * NB, kc = k * NB;
-  double acc[8][8];
+  __shared__ TileSmem<TM> sm;
+  const int r0 = (k + 1 + blockIdx.y) * NB + sub_r<TM>(), c0 = blockIdx.x * NB + sub_c<TM>(), kc = k * NB;
+  double acc[TM / 16][TM / 16];
   tile_zero(acc);
-  tile_gemm<false>(sm, A, ld, r0, kc, X, ld, c0, kc, NB, acc);
-  tile_store<true>(X, ld, r0, c0, acc, -1.0);
+  tile_gemm<false, TM>(sm, A, ld, r0, kc, X, ld, c0, kc, NB, acc);
+  tile_store<true, TM>(X, ld, r0, c0, acc, -1.0);
 }
 
 // Zero the identity padding of L^-1 (rows/cols in [n, np)) so padded rows contribute nothing.
@@ -460,6 +688,16 @@ int32_t compute_alpha(sbo_ctx* ctx, int n) {
 
 }  // namespace
 
+static int32_t ensure_factor_streams(sbo_ctx* ctx, int nblk) {
+  if (!ctx->aux_stream) SBO_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
+  while ((int)ctx->ev_factor.size() < 1 + 2 * nblk) {
+    cudaEvent_t e;
+    SBO_CUDA(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    ctx->ev_factor.push_back(e);
+  }
+  return SBO_OK;
+}
+
 int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end) {
   if (!ctx->d_planes || row_end <= row_begin) return SBO_OK;
   const int ld = ctx->n_cap;
@@ -498,26 +736,61 @@ int32_t factor_full(sbo_ctx* ctx) {
     build_K_kernel<<<g, b, 0, st>>>(ctx->d_xy, n, np, ld, sf2, inv2l2, ctx->cfg.noise_var, ctx->d_A);
     SBO_LAUNCH_CHECK(ctx, "build_K_kernel");
   }
+  // Two chains: the Cholesky steps (diag -> panel -> trailing update) on the context's stream, the rows of
+  // L^-1 (which only need D_k and the finished panel k) on an auxiliary stream, joined at the end.
+  // Small n: 64x64 tiles (four CTAs per 128-block) -- a launch then has fewer 128-tiles than SMs and its
+  // duration is one thread's serial FMA count.
+  const bool small = nblk * (nblk + 1) / 2 <= 2 * ctx->sm_count;
+  SBO_TRY(ensure_factor_streams(ctx, nblk));
+  cudaStream_t sb = ctx->aux_stream;
+  double* scr_panel = ctx->d_small;                          // [rem * 128][128]
+  double* scr_row = ctx->d_small + (size_t)kMaxAppend * ld;  // [128][ld]
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev_factor[0], st));
+  SBO_CUDA(ctx, cudaStreamWaitEvent(sb, ctx->ev_factor[0], 0));
+  const dim3 sub(1, 1, small ? 4 : 1);
   for (int k = 0; k < nblk; ++k) {
     double* Dk = ctx->d_Dinv + (size_t)k * NB * NB;
+    cudaEvent_t ev_d = ctx->ev_factor[1 + 2 * k], ev_t = ctx->ev_factor[2 + 2 * k];
     diag_chol_inv_kernel<<<1, kDiagThreads, kDiagSmem, st>>>(ctx->d_A + (size_t)k * NB * ld + (size_t)k * NB, ld, NB,
                                                              Dk, NB, k * NB, ctx->d_info);
     SBO_LAUNCH_CHECK(ctx, "diag_chol_inv_kernel");
+    SBO_CUDA(ctx, cudaEventRecord(ev_d, st));
     const int rem = nblk - k - 1;
     if (rem > 0) {
-      panel_trsm_kernel<<<rem, kGemmThreads, 0, st>>>(ctx->d_A, ld, k, Dk);
-      SBO_LAUNCH_CHECK(ctx, "panel_trsm_kernel");
-      syrk_kernel<<<rem * (rem + 1) / 2, kGemmThreads, 0, st>>>(ctx->d_A, ld, k);
+      if (small) {
+        panel_trsm_kernel<64><<<dim3(rem, 1, 4), kGemmThreads, 0, st>>>(ctx->d_A, ld, k, Dk, scr_panel, NB);
+        SBO_LAUNCH_CHECK(ctx, "panel_trsm_kernel");
+        panel_copy_kernel<<<(rem * NB + 7) / 8, dim3(NB, 8), 0, st>>>(ctx->d_A, ld, k, scr_panel, NB, rem * NB);
+        SBO_LAUNCH_CHECK(ctx, "panel_copy_kernel");
+      } else {
+        panel_trsm_kernel<128><<<rem, kGemmThreads, 0, st>>>(ctx->d_A, ld, k, Dk,
+                                                             ctx->d_A + (size_t)(k + 1) * NB * ld + (size_t)k * NB, ld);
+        SBO_LAUNCH_CHECK(ctx, "panel_trsm_kernel");
+      }
+      SBO_CUDA(ctx, cudaEventRecord(ev_t, st));
+      if (small) syrk_kernel<64><<<dim3(rem * (rem + 1) / 2, 1, 4), kGemmThreads, 0, st>>>(ctx->d_A, ld, k);
+      else syrk_kernel<128><<<rem * (rem + 1) / 2, kGemmThreads, 0, st>>>(ctx->d_A, ld, k);
       SBO_LAUNCH_CHECK(ctx, "syrk_kernel");
     }
-    trtri_row_kernel<<<k + 1, kGemmThreads, 0, st>>>(ctx->d_Linv, ld, k, Dk);
-    SBO_LAUNCH_CHECK(ctx, "trtri_row_kernel");
+    SBO_CUDA(ctx, cudaStreamWaitEvent(sb, ev_d, 0));
+    if (small) {
+      trtri_row_kernel<64><<<dim3(k + 1, 1, 4), kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, k, Dk, scr_row, ld);
+      SBO_LAUNCH_CHECK(ctx, "trtri_row_kernel");
+      row_copy_kernel<<<dim3(((k + 1) * NB + 255) / 256, NB), 256, 0, sb>>>(ctx->d_Linv, ld, k, scr_row, ld, (k + 1) * NB);
+      SBO_LAUNCH_CHECK(ctx, "row_copy_kernel");
+    } else {
+      trtri_row_kernel<128><<<k + 1, kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, k, Dk, ctx->d_Linv + (size_t)k * NB * ld, ld);
+      SBO_LAUNCH_CHECK(ctx, "trtri_row_kernel");
+    }
     if (rem > 0) {
-      dim3 g(k + 1, rem);
-      trtri_update_kernel<<<g, kGemmThreads, 0, st>>>(ctx->d_Linv, ld, ctx->d_A, k);
+      SBO_CUDA(ctx, cudaStreamWaitEvent(sb, ev_t, 0));
+      if (small) trtri_update_kernel<64><<<dim3(k + 1, rem, 4), kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, ctx->d_A, k);
+      else trtri_update_kernel<128><<<dim3(k + 1, rem, 1), kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, ctx->d_A, k);
       SBO_LAUNCH_CHECK(ctx, "trtri_update_kernel");
     }
   }
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev_factor[0], sb));
+  SBO_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_factor[0], 0));
   if (np > n) {
     clear_pad_kernel<<<(np - n + 127) / 128, 128, 0, st>>>(ctx->d_Linv, ld, n, np);
     SBO_LAUNCH_CHECK(ctx, "clear_pad_kernel");
@@ -574,3 +847,9 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
 }
 
 }  // namespace sbo
+
+#ifdef SBO_DIAG_TIMING
+extern "C" int32_t sbo_debug_diag_timing(long long* host16) {
+  return cudaMemcpyFromSymbol(host16, sbo::g_diag_t, sizeof(long long) * 16) == cudaSuccess ? 0 : -3;
+}
+#endif
