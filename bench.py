@@ -283,8 +283,14 @@ def main():
         else:
             peak, peak_note = 40.0, "fp64 FMA pipe, nominal (no measured fp64 peak on file)"
         achieved = flops / (ms_post * 1e-3) / 1e12
+        traffic = None
+        try:   # per-launch DRAM bytes of the dominant kernel from the committed ncu --set full capture of this workload
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic_r01.json")))
+            traffic = tj["posterior_tc_kernel" if used_tc else "posterior_simt_kernel"][args.workload]["dram_bytes_per_launch"]
+        except Exception:
+            traffic = None
         roofline = {"bound": "tensor" if used_tc else "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                    "frac": achieved / peak, "traffic": None, "kernel": "posterior_tc_kernel" if used_tc else "posterior_simt_kernel",
+                    "frac": achieved / peak, "traffic": traffic, "kernel": "posterior_tc_kernel" if used_tc else "posterior_simt_kernel",
                     "peak_source": peak_note, "ms_kernel": ms_post, "credited_flops_per_launch": flops,
                     "executed_over_credited": executed_over_credited(p.n) if used_tc else 1.0}
         cpu = None

@@ -29,6 +29,20 @@ def test_factor_matches_oracle(pkg, oracle, coracle, n):
         assert np.array_equal(np.triu(ctx.linv(), 1), np.zeros((n, n)))
 
 
+def test_factor_large_tiles_match_scipy(pkg, oracle):
+    """n > 2944 takes the 128x128-tile kernels (factor_full picks 64x64 tiles below that); scipy/LAPACK
+    is the checker here, the plain-C oracle being O(n^3) single-threaded."""
+    n = 3100
+    p = S.make_problem("C3", n=n, W=16, H=16)
+    hp = oracle.Hyper(p.sigma_f, p.length, p.noise_var, p.prior_mean)
+    with make_ctx(pkg, p, precision="fp64") as ctx:
+        ctx.set_observations(p.xy, p.y)
+        order = ctx.order()
+        _, Linv_sorted, _ = oracle.gp_fit_scipy(p.xy[order], p.y[order], hp)
+        _, _, alpha = oracle.gp_fit_scipy(p.xy, p.y, hp)
+        assert _rel(ctx.linv(), Linv_sorted) < 1e-9 and _rel(ctx.alpha(), alpha) < 1e-9
+
+
 @pytest.mark.parametrize("n0,ks", [(0, [1, 3]), (1, [1]), (100, [1, 1, 16]), (250, [16, 128, 5]), (120, [200])])
 def test_append_equals_full_refactor(pkg, oracle, coracle, n0, ks):
     total = n0 + sum(ks)

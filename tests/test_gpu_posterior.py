@@ -72,6 +72,8 @@ def check_argmax(res, ref, band, mask):
 CASES = [  # (cfg, n, W, H) -- ragged sizes on purpose: n % 32, n % 256, W % 128 != 0, single rows, tiny grids
     ("C2", 0, 64, 8), ("C2", 1, 128, 4), ("C2", 31, 130, 9), ("C2", 32, 128, 16), ("C2", 200, 96, 48),
     ("C2", 256, 256, 32), ("C2", 257, 200, 40), ("C2", 700, 384, 24), ("C2", 1024, 512, 64), ("C3", 1100, 1, 300),
+    # odd tile counts (the second CTA of the last pair has no tile), more row blocks than TMEM stages
+    ("C2", 300, 128, 5), ("C2", 65, 384, 1), ("C3", 2304, 640, 3),
 ]
 
 
@@ -177,6 +179,23 @@ def test_optimizer_core_end_to_end(pkg, oracle, coracle):
     core.process_observations(p.xy, p.y, (p.x0, p.y0, p.rx, p.ry, p.W, p.H))
     assert np.array_equal(core.S_, ref["mask"]) and core.GetNextSubgoal() == want
     core.ctx.close()
+
+
+def test_single_cta_variant_matches_pair(pkg, oracle, coracle, monkeypatch):
+    """SBO_TC_CTA_GROUP=1 runs the same kernel as one CTA per tile (cta_group::1); both forms must meet the
+    oracle and agree with each other to rounding (the MMA order per accumulator is identical)."""
+    p = S.make_problem("C2", n=700, W=384, H=9)
+    ref = reference(oracle, coracle, p)
+    out = {}
+    for cg in ("1", "2"):
+        monkeypatch.setenv("SBO_TC_CTA_GROUP", cg)
+        with make_ctx(pkg, p, kernel="tcgen05") as ctx:
+            ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+            ctx.set_observations(p.xy, p.y)
+            res, mask = ctx.step(p.beta, p.f_min)
+            out[cg] = (ctx.mu(), ctx.sigma2())
+            check_step(p, ref, res, mask, out[cg][0], out[cg][1], "fp32", label=f"cta_group::{cg}")
+    assert np.array_equal(out["1"][0], out["2"][0]) and np.array_equal(out["1"][1], out["2"][1])
 
 
 def test_full_size_c2_properties(pkg):
