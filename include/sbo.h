@@ -56,7 +56,8 @@ typedef enum {
 typedef enum {
   SBO_KERNEL_AUTO = 0,     /* tcgen05 path for SBO_FP32, SIMT fp64 for SBO_FP64 */
   SBO_KERNEL_SIMT = 1,     /* force the SIMT kernel (any precision)             */
-  SBO_KERNEL_TCGEN05 = 2   /* force the tcgen05 kernel (SBO_FP32 only)          */
+  SBO_KERNEL_TCGEN05 = 2,  /* force the tcgen05 kernel (SBO_FP32 only)          */
+  SBO_KERNEL_THIN = 3      /* reported only: the O(m n k) kernel of sbo_step_incremental after <= 8 new rows */
 } sbo_kernel_choice;
 
 /* GP hyper-parameters of the external mapping node the library replaces

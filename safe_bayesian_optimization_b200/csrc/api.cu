@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -97,8 +98,16 @@ int32_t run_step(sbo_ctx* ctx, double beta, double f_min, bool incremental, int*
   }
   SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
-  if (which == SBO_KERNEL_TCGEN05) SBO_TRY(launch_posterior_tc(ctx, j_lo, j_hi, accumulate));
-  else SBO_TRY(launch_posterior_simt(ctx, j_lo, j_hi, accumulate));
+  // a few new rows: the thin SIMT kernel (O(m n k)); otherwise the row blocks that hold them
+  static const bool thin_off = std::getenv("SBO_THIN") && std::atoi(std::getenv("SBO_THIN")) == 0;
+  if (incremental && !thin_off && j_hi - j_lo <= kThinMaxRows) {
+    SBO_TRY(launch_posterior_thin(ctx, j_lo));
+    which = SBO_KERNEL_THIN;
+  } else if (which == SBO_KERNEL_TCGEN05) {
+    SBO_TRY(launch_posterior_tc(ctx, j_lo, j_hi, accumulate));
+  } else {
+    SBO_TRY(launch_posterior_simt(ctx, j_lo, j_hi, accumulate));
+  }
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
   SBO_TRY(launch_sets_step(ctx, beta, f_min));
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));

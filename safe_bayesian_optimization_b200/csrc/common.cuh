@@ -15,6 +15,7 @@ namespace sbo {
 constexpr int kFactorNB = 128;   // block size of the fp64 factorisation kernels
 constexpr int kObsPad = 256;     // observation capacity is rounded up to this (tcgen05 N tile)
 constexpr int kMaxAppend = 128;  // rows per rank-k append pass
+constexpr int kThinMaxRows = 8;  // incremental steps with at most this many new rows take the thin SIMT kernel
 
 // Result record of the CI/mask/argmax pass, written by the device.
 struct SetsResult {
@@ -154,6 +155,10 @@ int32_t tc_init(sbo_ctx* ctx);                     // tensor map, attributes, pl
 void tc_plane_shifts(const sbo_config& cfg, int* shift_a, int* shift_b);
 int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
 void tc_destroy(sbo_ctx* ctx);
+int32_t tc_pack_observations(sbo_ctx* ctx);       // d_xy -> d_obs_f32 (scaled fp32 hi/lo pairs)
+
+// posterior_thin.cu
+int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo);   // incremental step, n - row_lo <= kThinMaxRows
 
 // comm.cu
 int32_t comm_gather_reduce(sbo_ctx* ctx);          // d_result -> d_result (global), over all ranks

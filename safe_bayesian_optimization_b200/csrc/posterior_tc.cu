@@ -635,6 +635,15 @@ void tc_destroy(sbo_ctx* ctx) {
 
 static float* g_dbg_v = nullptr;
 
+int32_t tc_pack_observations(sbo_ctx* ctx) {
+  if (!ctx->d_obs_f32) return fail(ctx, SBO_ERR_STATE, "packed observation buffer missing (fp32 mode only)");
+  const double xscale = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
+  pack_obs_kernel<<<(ctx->n_cap + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_xy, ctx->n, ctx->n_cap, xscale,
+                                                                     reinterpret_cast<float4*>(ctx->d_obs_f32));
+  SBO_LAUNCH_CHECK(ctx, "pack_obs_kernel");
+  return SBO_OK;
+}
+
 int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   if (!ctx->tc_ok) return fail(ctx, SBO_ERR_STATE, "tcgen05 kernel not initialised");
   if (ctx->m_local == 0) return SBO_OK;
@@ -661,9 +670,7 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.sf2 = (float)sf2;
   p.prior_mean = (float)ctx->cfg.prior_mean;
   p.dbg_v = g_dbg_v;
-  pack_obs_kernel<<<(ctx->n_cap + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_xy, ctx->n, ctx->n_cap, p.xscale,
-                                                                     reinterpret_cast<float4*>(ctx->d_obs_f32));
-  SBO_LAUNCH_CHECK(ctx, "pack_obs_kernel");
+  SBO_TRY(tc_pack_observations(ctx));
   const long long ntiles = (long long)p.rows_local * ((p.W + BM - 1) / BM);
   const CUtensorMap& tmap = *static_cast<CUtensorMap*>(ctx->tmap_planes);
   if (ctx->tc_cg == 1) {

@@ -94,10 +94,12 @@ def test_step_matches_oracle(pkg, oracle, coracle, cfg, n, W, H, precision, kern
 
 
 @pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp64", "simt")])
-@pytest.mark.parametrize("n0,ks", [(300, [1, 16]), (250, [6, 1, 40]), (0, [5])])
+@pytest.mark.parametrize("n0,ks", [(300, [1, 16]), (250, [6, 1, 40]), (0, [5]), (700, [1, 2, 3, 8, 9]), (1030, [4, 0, 1])])
 def test_incremental_step_equals_full(pkg, oracle, coracle, precision, kernel, n0, ks):
+    """<= 8 new rows take the thin O(m n k) kernel (kernel_used 3), more the row-block kernels; W = 300 is not a
+    multiple of the thin kernel's cell span on purpose."""
     total = n0 + sum(ks)
-    p = S.make_problem("C3", n=total, W=256, H=24)
+    p = S.make_problem("C3", n=total, W=300, H=21)
     with make_ctx(pkg, p, precision=precision, kernel=kernel, max_obs=total) as ctx:
         ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
         ctx.set_observations(p.xy[:n0], p.y[:n0])
@@ -107,7 +109,8 @@ def test_incremental_step_equals_full(pkg, oracle, coracle, precision, kernel, n
             ctx.append_observations(p.xy[n:n + k], p.y[n:n + k])
             n += k
             res, mask = ctx.step(p.beta, p.f_min, incremental=True)
-            q = S.make_problem("C3", n=total, W=256, H=24); q.xy, q.y = p.xy[:n], p.y[:n]
+            assert res.kernel_used == (3 if k <= 8 else {"tcgen05": 2, "simt": 1}[kernel])
+            q = S.make_problem("C3", n=total, W=300, H=21); q.xy, q.y = p.xy[:n], p.y[:n]
             ref = reference(oracle, coracle, q)
             band = check_step(q, ref, res, mask, ctx.mu(), ctx.sigma2(), precision, label=f"incr+{k}")
             check_argmax(res, ref, band, mask)
