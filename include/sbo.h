@@ -180,6 +180,33 @@ int32_t sbo_compute_sets(sbo_ctx* ctx, const double* mu, const double* std_dev, 
 int32_t sbo_select_subgoal(sbo_ctx* ctx, const int32_t* frontier, int64_t F, double goal_x,
                            double goal_y, int32_t* out_cell);
 
+/* ---- the stages right after the mask -------------------- */
+
+/* The pixel <-> cell maps of FindSafetyContourIndices on this grid, with the
+ * reference's own arithmetic: bounds truncated to int (:431-434), pixel =
+ * int((coord - min) / (max - min) * dim) (:450-451), out-of-image cells
+ * dropped (:453), last writer of a pixel wins (:468-475).  col_of_px[W] /
+ * row_of_py[H]: cell column / row stored at that pixel column / row, or -1.
+ * These W + H integers replace the nested unordered_map over all m cells.
+ * Error (INVALID_ARG) when an axis extent truncates to zero: the reference
+ * divides by zero there. */
+int32_t sbo_frontier_pixel_maps(sbo_ctx* ctx, int32_t* col_of_px, int32_t* row_of_py);
+/* The CV_8UC1 image the reference hands to cv::findContours (:444-456), built
+ * on the GPU from the mask of the last sbo_step by a gather through the maps
+ * above; img_host is H*W bytes (0/255), the maps are returned as well.  A
+ * contour point (x, y) maps back to cell row_of_py[y] * W + col_of_px[x].
+ * Single-shard contexts only.  replaces: :431-456 and :468-475. */
+int32_t sbo_frontier_image(sbo_ctx* ctx, uint8_t* img_host, int32_t* col_of_px, int32_t* row_of_py);
+
+typedef enum {
+  SBO_CELLS_SAFE = 0,     /* every safe cell (the gather in front of the alpha shape, :944-949)          */
+  SBO_CELLS_BORDER = 1    /* safe cells with an unsafe cell or the grid frame in their 8-neighbourhood   */
+} sbo_cell_set;
+/* Global indices of the selected cells of this shard in ascending order
+ * (stream compaction on the GPU).  *count = how many exist; at most `cap` are
+ * written to idx_host (may be NULL when cap == 0: count only). */
+int32_t sbo_compact_cells(sbo_ctx* ctx, int32_t mode, int32_t* idx_host, int64_t cap, int64_t* count);
+
 /* Bulk read-back of the last step's posterior for this shard.  fp32 or fp64
  * according to cfg.precision (sbo_copy_*_f64 always converts to double). */
 int32_t sbo_copy_mu(sbo_ctx* ctx, void* host_dst);

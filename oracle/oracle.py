@@ -244,12 +244,10 @@ def gp_posterior_sklearn(xy, y, hp: Hyper, grid: Grid, cells):
 
 # ---- frontier (reference :418-497), host stage that consumes the mask ("next" row N1) ----
 
-def find_safety_contour_indices(mask, grid: Grid):
-    """FindSafetyContourIndices restated with cv2.findContours (same Suzuki-Abe
-    border following as the C++ call at :461-462), including the reference's
-    int-truncated bounds (:431-434), pixel mapping (:450-451), drop rule (:453)
-    and last-writer-wins pixel->cell map (:468-475)."""
-    import cv2
+def safety_image(mask, grid: Grid):
+    """The image and the pixel -> cell table of FindSafetyContourIndices, cell by cell as the reference does it:
+    int-truncated bounds (:431-434), pixel mapping (:450-451), drop rule (:453), last-writer-wins (:454, :468-475).
+    Returns (img uint8 H x W, lut int64 W x H with -1 where no cell landed)."""
     m = grid.m
     x, y = grid.cell_xy()
     min_x, max_x = int(x.min()), int(x.max())   # static_cast<int>: truncation toward zero
@@ -266,6 +264,14 @@ def find_safety_contour_indices(mask, grid: Grid):
     # sequential "last writer wins": later cells overwrite earlier ones
     img[py[ok], px[ok]] = np.where(np.asarray(mask)[ok] != 0, 255, 0)
     lut[px[ok], py[ok]] = idx
+    return img, lut
+
+
+def find_safety_contour_indices(mask, grid: Grid):
+    """FindSafetyContourIndices restated with cv2.findContours (same Suzuki-Abe
+    border following as the C++ call at :461-462) on the image of safety_image()."""
+    import cv2
+    img, lut = safety_image(mask, grid)
     contours, _ = cv2.findContours(img, cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_NONE)
     out = []
     for c in contours:
@@ -273,3 +279,18 @@ def find_safety_contour_indices(mask, grid: Grid):
         li = lut[pts[:, 0], pts[:, 1]]
         out.extend(li[li >= 0].tolist())
     return np.asarray(out, dtype=np.int32)
+
+
+def compact_cells(mask, grid: Grid, border=False):
+    """Ascending indices of the safe cells (reference :944-949 gathers exactly these for the alpha shape); border=True
+    keeps only safe cells with an unsafe cell or the grid frame among their 8 neighbours."""
+    s = (np.asarray(mask).reshape(grid.H, grid.W) != 0)
+    if border:
+        p = np.zeros((grid.H + 2, grid.W + 2), dtype=bool)
+        p[1:-1, 1:-1] = s
+        full = np.ones_like(s)
+        for dy in (0, 1, 2):
+            for dx in (0, 1, 2):
+                full &= p[dy:dy + grid.H, dx:dx + grid.W]
+        s = s & ~full
+    return np.flatnonzero(s.reshape(-1)).astype(np.int32)

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <new>
+#include <string>
 #include <vector>
 
 #include "common.cuh"
@@ -37,7 +38,7 @@ bool all_finite(const double* p, size_t count) {
 void free_all(sbo_ctx* c) {
   tc_destroy(c);
   void* dev[] = {c->d_xy, c->d_r, c->d_A, c->d_Linv, c->d_Dinv, c->d_alpha, c->d_w, c->d_small, c->d_info,
-                 c->d_planes, c->d_alpha_f32, c->d_obs_f32, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
+                 c->d_planes, c->d_alpha_f32, c->d_obs_f32, c->d_fr_img, c->d_fr_lut, c->d_cp_idx, c->d_cp_counts, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
                  c->d_partials, c->d_result, c->d_ticket, c->d_frontier, c->d_sel_keys, c->d_sel_width, c->d_sel_out,
                  c->d_gather};
   for (void* p : dev)
@@ -491,6 +492,51 @@ int32_t sbo_compute_sets_device(sbo_ctx* ctx, const double* mu_dev, const double
   ctx->source = keep;
   ctx->source_m = keep_m;
   return st;
+}
+
+// ---------------------------------------------------------------------------------------------
+// frontier stage helpers (reference FindSafetyContourIndices :418-497, safe-cell gather :944-949)
+// ---------------------------------------------------------------------------------------------
+int32_t sbo_frontier_pixel_maps(sbo_ctx* ctx, int32_t* col_of_px, int32_t* row_of_py) {
+  if (!ctx || !col_of_px || !row_of_py) return SBO_ERR_INVALID_ARG;
+  if (!ctx->grid_set) return fail(ctx, SBO_ERR_STATE, "sbo_frontier_pixel_maps: grid not set");
+  const int W = ctx->W, H = ctx->H;
+  // :431-434 -- bounds of the cell coordinates truncated to int (coordinates ascend with the index on a regular grid)
+  auto axis = [&](double o, double r, int dim, int32_t* map, const char* name) -> int32_t {
+    const double c0 = o, c1 = o + (double)(dim - 1) * r;
+    const int mn = (int)std::min(c0, c1), mx = (int)std::max(c0, c1);
+    if (mx == mn)
+      return fail(ctx, SBO_ERR_INVALID_ARG, std::string("sbo_frontier_pixel_maps: ") + name +
+                                                " extent below one unit: the reference divides by zero here (:450-451)");
+    for (int i = 0; i < dim; ++i) map[i] = -1;
+    for (int i = 0; i < dim; ++i) {               // ascending cell order: the last writer of a pixel wins (:468-475)
+      const double c = o + (double)i * r;         // same expression as the grid formula of sbo_set_grid
+      const int px = (int)((c - mn) / (double)(mx - mn) * dim);  // :450-451
+      if (px >= 0 && px < dim) map[px] = i;       // :453
+    }
+    return SBO_OK;
+  };
+  SBO_TRY(axis(ctx->x0, ctx->rx, W, col_of_px, "x"));
+  SBO_TRY(axis(ctx->y0, ctx->ry, H, row_of_py, "y"));
+  return SBO_OK;
+}
+
+int32_t sbo_frontier_image(sbo_ctx* ctx, uint8_t* img_host, int32_t* col_of_px, int32_t* row_of_py) {
+  if (!ctx || !img_host || !col_of_px || !row_of_py) return SBO_ERR_INVALID_ARG;
+  if (ctx->source != PosteriorSource::kStep)
+    return fail(ctx, SBO_ERR_STATE, "sbo_frontier_image: no safe mask on the device yet (call sbo_step first)");
+  SBO_TRY(sbo_frontier_pixel_maps(ctx, col_of_px, row_of_py));
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  return frontier_image(ctx, col_of_px, row_of_py, img_host);
+}
+
+int32_t sbo_compact_cells(sbo_ctx* ctx, int32_t mode, int32_t* idx_host, int64_t cap, int64_t* count) {
+  if (!ctx || !count || cap < 0 || (cap > 0 && !idx_host)) return SBO_ERR_INVALID_ARG;
+  if (mode != SBO_CELLS_SAFE && mode != SBO_CELLS_BORDER) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_compact_cells: bad mode");
+  if (ctx->source != PosteriorSource::kStep)
+    return fail(ctx, SBO_ERR_STATE, "sbo_compact_cells: no safe mask on the device yet (call sbo_step first)");
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  return compact_cells(ctx, mode, idx_host, cap, count);
 }
 
 int32_t sbo_select_subgoal(sbo_ctx* ctx, const int32_t* frontier, int64_t F, double goal_x, double goal_y,

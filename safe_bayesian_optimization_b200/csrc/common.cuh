@@ -100,6 +100,14 @@ struct sbo_ctx {
   int32_t* h_sel_out = nullptr;  // pinned
   int32_t* d_sel_out = nullptr;
 
+  // frontier / compaction scratch (lazy; frontier.cu)
+  uint8_t* d_fr_img = nullptr;
+  int32_t* d_fr_lut = nullptr;   // [W + H] pixel -> cell tables
+  long long fr_cap = 0;
+  int32_t* d_cp_idx = nullptr;   // [m_local]
+  unsigned int* d_cp_counts = nullptr;
+  long long cp_cap = 0;
+
   // communicator
   void* nccl_comm = nullptr;
   int rank = 0, world = 1;
@@ -159,6 +167,10 @@ int32_t tc_pack_observations(sbo_ctx* ctx);       // d_xy -> d_obs_f32 (scaled f
 
 // posterior_thin.cu
 int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo);   // incremental step, n - row_lo <= kThinMaxRows
+
+// frontier.cu
+int32_t frontier_image(sbo_ctx* ctx, const int32_t* col_of_px, const int32_t* row_of_py, uint8_t* img_host);
+int32_t compact_cells(sbo_ctx* ctx, int mode, int32_t* idx_host, int64_t cap, int64_t* count_out);
 
 // comm.cu
 int32_t comm_gather_reduce(sbo_ctx* ctx);          // d_result -> d_result (global), over all ranks

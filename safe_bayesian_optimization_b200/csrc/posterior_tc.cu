@@ -418,7 +418,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     uint32_t acc_it = 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
       const long long tile = gt * CG + rank;
-      double rsum = 0.0;
+      float rs_hi = 0.f, rs_lo = 0.f;  // sum of squares of this cell's row of V (scaled), double-word fp32
       for (int jb = jb_lo; jb < jb_hi; ++jb, ++acc_it) {
         const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
         mbar_wait(&sh->tmem_full[as], aph);
@@ -442,8 +442,9 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
               if (jc + i < p.j_lo || jc + i >= p.j_hi) v[i] = 0u;
           }
           // squares are exact inside the FMA; four 8-term fp32 partial sums (relative error <= ~1e-7 each,
-          // uncorrelated) then fp64: the fp32->fp64 conversions are XU-pipe instructions and would
-          // otherwise compete with the generators' MUFU.EX2 32 times per group instead of 4
+          // uncorrelated), then a double-word fp32 running sum (2Sum).  No fp64 here: with F2F/DADD the four
+          // epilogue warps spent 3/4 of their samples in math-pipe throttle behind the generators' MUFU traffic
+          // and the short row blocks of small n were paced by the epilogue (profiles/ncu_posterior_tc_r01b.md).
           float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
           for (int i = 0; i < 32; i += 4) {
@@ -454,7 +455,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             s2 = fmaf(x2, x2, s2);
             s3 = fmaf(x3, x3, s3);
           }
-          rsum += ((double)s0 + (double)s1) + ((double)s2 + (double)s3);
+          two_sum_acc(rs_hi, rs_lo, (s0 + s1) + (s2 + s3));
         }
         tc_fence_before();
         __syncwarp();
@@ -468,7 +469,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         if (col < p.W) {
           const long long lc = (long long)lrow * p.W + col;
           const double prev = p.accumulate ? (double)p.s2[lc] : (double)p.sf2;
-          p.s2[lc] = (float)(prev - rsum * p.v_unscale2);
+          p.s2[lc] = (float)(prev - ((double)rs_hi + (double)rs_lo) * p.v_unscale2);
         }
       }
     }

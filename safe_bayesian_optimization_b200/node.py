@@ -66,6 +66,20 @@ def find_safety_contour_indices(mask_img: np.ndarray, x0, y0, rx, ry):
     return (iy[keep] * W + ix[keep]).astype(np.int32)
 
 
+def contour_indices_from_image(img: np.ndarray, col_of_px: np.ndarray, row_of_py: np.ndarray):
+    """cv::findContours (:461-462) on the GPU-built safety image, contour pixels mapped back to cell indices through
+    the two pixel -> cell tables (what :481-492 does with its hash map)."""
+    import cv2
+    H, W = img.shape
+    contours, _ = cv2.findContours(img, cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_NONE)
+    if not contours:
+        return np.zeros(0, dtype=np.int32)
+    pts = np.concatenate([c.reshape(-1, 2) for c in contours], axis=0)
+    ix, iy = col_of_px[pts[:, 0]].astype(np.int64), row_of_py[pts[:, 1]].astype(np.int64)
+    keep = (ix >= 0) & (iy >= 0)
+    return (iy[keep] * W + ix[keep]).astype(np.int32)
+
+
 class OptimizerCore:
     """One safe-BO step at a time, single caller thread (reference :1503)."""
 
@@ -79,6 +93,7 @@ class OptimizerCore:
         self.current_goal_ = (0.0, 0.0)          # default-constructed PointStamped (:171)
         self.terrain_width_cells_ = self.terrain_height_cells_ = 0
         self.last = None
+        self._mask_on_device = False             # True after a step that left its mask in the context (sbo_step)
 
     # -- goal_point_callback (:1324-1327) --------------------------------------
     def goal_point_callback(self, x, y):
@@ -110,6 +125,7 @@ class OptimizerCore:
         self.S_ = mask
         self.Q_ = np.stack([q0, q1], axis=1)
         self.last = res
+        self._mask_on_device = False
         return res
 
     # -- the integrated path: observations in, sets out ---------------------------
@@ -126,6 +142,7 @@ class OptimizerCore:
         self.S_ = mask
         self.mu_ = self.std_ = self.Q_ = None      # stay on the device unless asked for
         self.last = res
+        self._mask_on_device = True
         return res
 
     def FindSafetyContourIndices(self):
@@ -133,6 +150,9 @@ class OptimizerCore:
             log.warning("D_ or S_ is empty")     # :419-422
             return np.zeros(0, dtype=np.int32)
         x0, y0, rx, ry, W, H = self.grid
+        if getattr(self, "last", None) is not None and self.ctx.row0 == 0 and self.ctx.row1 == H and self._mask_on_device:
+            img, col_of_px, row_of_py = self.ctx.frontier_image()     # image + tables built on the GPU (frontier.cu)
+            return contour_indices_from_image(img, col_of_px, row_of_py)
         return find_safety_contour_indices(self.S_.reshape(H, W), x0, y0, rx, ry)
 
     def GetNextSubgoal(self) -> int:

@@ -192,6 +192,26 @@ class SboContext:
         return int(cell.value)
 
     # -- read-back ----------------------------------------------------------
+    def frontier_image(self):
+        """(img H x W uint8 0/255, col_of_px int32[W], row_of_py int32[H]): the image of reference :444-456 built on the
+        GPU with the reference's pixel map, and the pixel -> cell tables that replace its hash map (:468-475)."""
+        img = np.empty((self.H, self.W), dtype=np.uint8)
+        col = np.empty(self.W, dtype=np.int32)
+        row = np.empty(self.H, dtype=np.int32)
+        i32 = C.POINTER(C.c_int32)
+        self._check(self.lib.sbo_frontier_image(self._h, _u8ptr(img), col.ctypes.data_as(i32), row.ctypes.data_as(i32)))
+        return img, col, row
+
+    def compact_cells(self, border=False, cap=None):
+        """Ascending global indices of the safe cells (border=True: only those with an unsafe cell or the grid frame
+        in their 8-neighbourhood) of this shard, compacted on the GPU.  Returns (indices int32, total count)."""
+        cap = self.m_local if cap is None else int(cap)
+        idx = np.empty(max(cap, 1), dtype=np.int32)
+        cnt = C.c_int64(0)
+        self._check(self.lib.sbo_compact_cells(self._h, 1 if border else 0, idx.ctypes.data_as(C.POINTER(C.c_int32)), cap,
+                                               C.byref(cnt)))
+        return idx[:min(cap, cnt.value)], cnt.value
+
     def mu(self):
         out = np.empty(self.m_local)
         self._check(self.lib.sbo_copy_mu_f64(self._h, _dptr(out)))

@@ -109,3 +109,28 @@ def test_two_rank_gloo_sharding_equals_single(oracle, coracle):
     assert np.array_equal(mask, mask2) and merged.safe_count == cnt and merged.n_cells == p.m
     assert merged.argmax_ucb == coracle.argmax_safe(q1, mask)
     assert merged.argmax_width == coracle.argmax_safe(q1 - q0, mask)
+
+
+def test_compact_cells_known_answers(oracle):
+    """Hand-checked cases of the safe / border cell lists (the checker of tests/test_gpu_frontier.py)."""
+    g = oracle.Grid(0.0, 0.0, 1.0, 1.0, 5, 4)
+    full = np.full(20, 255, dtype=np.uint8)
+    assert oracle.compact_cells(full, g).tolist() == list(range(20))
+    # all safe: only the frame is border; the interior 3 x 2 block (cells 6,7,8,11,12,13) is not
+    assert oracle.compact_cells(full, g, border=True).tolist() == [c for c in range(20) if c not in (6, 7, 8, 11, 12, 13)]
+    holed = full.copy(); holed[7] = 0                      # one unsafe interior cell: all its 8 neighbours become border
+    assert oracle.compact_cells(holed, g, border=True).tolist() == [c for c in range(20) if c != 7]
+    assert oracle.compact_cells(np.zeros(20, dtype=np.uint8), g, border=True).size == 0
+
+
+def test_safety_image_reference_quirks(oracle):
+    """Unit pitch: the reference's int((c - min) / (max - min) * dim) maps cell i of W to pixel int(i * W / (W - 1)), so the
+    last column and row fall outside the image and are dropped (:453), and one pixel column/row stays empty."""
+    W, H = 6, 5
+    g = oracle.Grid(0.0, 0.0, 1.0, 1.0, W, H)
+    mask = np.full(W * H, 255, dtype=np.uint8)
+    img, lut = oracle.safety_image(mask, g)
+    px = [int(i / (W - 1) * W) for i in range(W)]          # 0,1,2,3,4,6 -> the last one is outside
+    assert px[-1] == W and sorted(set(px[:-1])) == [0, 1, 2, 3, 4]
+    assert (img[:, 5] == 0).all() and (img[4, :] == 0).all() and (img[:4, :5] == 255).all()
+    assert (lut[5, :] == -1).all() and lut[2, 3] == 3 * W + 2
