@@ -38,7 +38,7 @@ bool all_finite(const double* p, size_t count) {
 void free_all(sbo_ctx* c) {
   tc_destroy(c);
   void* dev[] = {c->d_xy, c->d_r, c->d_A, c->d_Linv, c->d_Dinv, c->d_alpha, c->d_w, c->d_small, c->d_info,
-                 c->d_planes, c->d_alpha_f32, c->d_obs_f32, c->d_fr_img, c->d_fr_lut, c->d_cp_idx, c->d_cp_counts, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
+                 c->d_planes, c->d_alpha_f32, c->d_obs_f32, c->d_chunk_bbox, c->d_fr_img, c->d_fr_lut, c->d_cp_idx, c->d_cp_counts, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
                  c->d_partials, c->d_result, c->d_ticket, c->d_frontier, c->d_sel_keys, c->d_sel_width, c->d_sel_out,
                  c->d_gather};
   for (void* p : dev)
@@ -222,6 +222,7 @@ int32_t sbo_create(const sbo_config* cfg, sbo_ctx** out) {
     CREATE_CUDA(cudaMemset(c->d_planes, 0, sizeof(uint16_t) * 2 * nc * nc));
     CREATE_CUDA(cudaMalloc(&c->d_obs_f32, sizeof(float) * 4 * nc));
     CREATE_CUDA(cudaMemset(c->d_obs_f32, 0, sizeof(float) * 4 * nc));
+    CREATE_CUDA(cudaMalloc(&c->d_chunk_bbox, sizeof(float) * 4 * (nc / 64 + 1)));
     CREATE_CUDA(cudaMalloc(&c->d_alpha_f32, sizeof(float) * nc));
     CREATE_CUDA(cudaMemset(c->d_alpha_f32, 0, sizeof(float) * nc));
   }
@@ -286,6 +287,7 @@ int32_t sbo_set_grid(sbo_ctx* ctx, double x0, double y0, double rx, double ry, i
   ctx->cell0 = (int64_t)row0 * W;
   ctx->m_local = m_local;
   ctx->grid_set = true;
+  ctx->tc_skip_plan = -1;
   ctx->posterior_valid = false;
   ctx->source = PosteriorSource::kNone;
   return SBO_OK;
@@ -344,10 +346,13 @@ int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, in
   ctx->order.swap(order);
   ctx->n = n;
   ctx->posterior_valid = false;
+  ctx->h_xy_sorted.swap(sxy);
+  ctx->tc_skip_plan = -1;
   const int32_t st = factor_full(ctx);
   if (st != SBO_OK) {
     ctx->n = 0;  // the factor buffers were overwritten: no observations until the next successful fit
     ctx->order.clear();
+    ctx->h_xy_sorted.clear();
     cudaMemsetAsync(ctx->d_Linv, 0, sizeof(double) * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
     cudaMemsetAsync(ctx->d_alpha, 0, sizeof(double) * (size_t)ctx->n_cap, ctx->stream);
     if (ctx->d_planes) cudaMemsetAsync(ctx->d_planes, 0, sizeof(uint16_t) * 2 * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
@@ -377,7 +382,9 @@ int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y,
                                   ctx->stream));
     SBO_TRY(factor_append(ctx, kk));  // on failure n is unchanged: rows >= n of L^-1 are not part of the state
     for (int i = 0; i < kk; ++i) ctx->order.push_back(n + i);
+    ctx->h_xy_sorted.insert(ctx->h_xy_sorted.end(), xy + 2 * (size_t)done, xy + 2 * (size_t)(done + kk));
     ctx->n = n + kk;
+    if (ctx->tc_skip_plan == 0) ctx->tc_skip_plan = -1;  // a decision to skip survives appends; a decision not to is re-examined
     done += kk;
   }
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -68,6 +68,10 @@ struct sbo_ctx {
   uint16_t* d_planes = nullptr;
   int shift_a = 0, shift_b = 0;  // power-of-two scales of the K* and L^-1 planes (tc_plane_shifts)
   int tc_cg = 2;                 // CTAs per tcgen05.mma group (2 = CTA pair, 1 = single CTA)
+  bool tc_skip = true;           // leave out K* chunks that are < 2^-44 sigma_f^2 for a whole cell tile
+  int tc_skip_plan = -1;         // cached decision of tc_plan_skip for this grid + observation set (-1: stale)
+  std::vector<double> h_xy_sorted;  // host copy of d_xy (internal order), for the skip planner
+  float* d_chunk_bbox = nullptr; // [n_cap / 64] float4 scaled bounding boxes of the observation chunks
   float* d_alpha_f32 = nullptr;  // [n_cap]
   float* d_obs_f32 = nullptr;    // [n_cap] float4: scaled observation coordinates as fp32 (hi, lo) pairs (posterior_tc.cu)
   void* tmap_planes = nullptr;   // host copy of the CUtensorMap (128 B), 256-row box
@@ -163,6 +167,7 @@ int32_t tc_init(sbo_ctx* ctx);                     // tensor map, attributes, pl
 void tc_plane_shifts(const sbo_config& cfg, int* shift_a, int* shift_b);
 int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
 void tc_destroy(sbo_ctx* ctx);
+bool tc_plan_skip(sbo_ctx* ctx);                   // worth walking chunk masks on this grid / observation set?
 int32_t tc_pack_observations(sbo_ctx* ctx);       // d_xy -> d_obs_f32 (scaled fp32 hi/lo pairs)
 
 // posterior_thin.cu

@@ -49,6 +49,8 @@ constexpr int kThreadsTc = 768;
 constexpr int kGenWarps = 16;
 constexpr uint32_t kABytes = BM * BK * 2;   // 16 KB per plane
 constexpr uint32_t kTmemCols = 512;
+constexpr int kMaskWords = 16;         // chunk masks cover 512 chunks = 32 768 observations; beyond that: dense
+constexpr float kSkipBits = 44.f;      // K* < 2^-44 sigma_f^2 over a whole 128-cell x 64-observation tile: skipped
 
 template <int CG> struct TcCfg {
   static constexpr uint32_t kBRows = BN / CG;                    // rows of a B tile held by one CTA
@@ -68,6 +70,7 @@ struct __align__(16) TcShared {
   float4 obs_y[kGenWarps][4];      //   y factor of K* (incl. sigma_f^2 and the A scale)
   float4 obs_a[kGenWarps][4];      //   alpha
   float mu_part[2][3][BM];         // partial mu of k-quarters 1..3, double-buffered by tile parity
+  uint32_t cmask[kThreadsTc / 32][kMaskWords];  // per warp: bit c set = chunk c is contracted for the current tile (pair)
 };
 
 struct TcParams {
@@ -87,6 +90,8 @@ struct TcParams {
   float v_unscale;         // 2^-(shift_a + shift_b) (debug dump only)
   float sf2, prior_mean;
   float* dbg_v;            // debug: V of tile 0 ([128][n_cap]) when non-null
+  const float4* bbox;      // [n_cap / 64] scaled bounding box (xmin, xmax, ymin, ymax) of every 64-observation chunk
+  int skip;                // 1: chunks whose K* entries are all below 2^-kSkipBits sigma_f^2 for a tile are not contracted
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -242,6 +247,82 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 // number of k-chunks of row block jb
 __device__ __forceinline__ int chunks_of(int jb, int n_pad) { return min(n_pad, (jb + 1) * BN) / BK; }
 
+// ---- block sparsity of K* ------------------------------------------------------------------------
+// The observations are stored in spatial order (sbo_set_observations), so a chunk of 64 consecutive ones
+// covers a small box, and K*[cell, k] = sigma_f^2 2^-(d^2) in the scaled coordinates.  A chunk whose box is
+// farther than sqrt(kSkipBits) from every cell of the tile (pair) contributes less than 2^-44 sigma_f^2 per
+// entry -- below the fp16 split's own resolution (2^-22) squared -- and is left out by every role alike:
+// each warp builds the same bit mask for itself (no cross-warp hand-over) and walks its set bits.
+__device__ __forceinline__ float box_dist2(const float4 b, float xlo, float xhi, float y) {
+  const float dx = fmaxf(fmaxf(b.x - xhi, xlo - b.y), 0.f), dy = fmaxf(fmaxf(b.z - y, y - b.w), 0.f);
+  return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
+}
+
+// __noinline__ on purpose: every role of both CTAs must derive bit-identical masks (they walk them in lock step
+// through the mbarrier pipelines), so there is exactly one compiled copy of this arithmetic.
+struct MaskGeom {  // by value: taking the address of the kernel parameter block would move it to local memory
+  double x0, y0, rx, ry, xscale;
+  const float4* bbox;
+  int row0, skip;
+};
+
+template <int CG>
+__device__ __noinline__ void build_chunk_mask(uint32_t* mask, const MaskGeom p, long long gt, long long ntiles,
+                                              int tiles_per_row, int nchunks) {
+  const int lane = threadIdx.x & 31;
+  float xlo[CG], xhi[CG], yy[CG];
+#pragma unroll
+  for (int t = 0; t < CG; ++t) {
+    const long long tile = min(gt * CG + t, ntiles - 1);
+    const int lrow = (int)(tile / tiles_per_row), col0 = (int)(tile % tiles_per_row) * BM;
+    const double xs = cell_coord(p.x0, p.rx, col0) * p.xscale, ys = cell_coord(p.y0, p.ry, p.row0 + lrow) * p.xscale;
+    const double w = (double)(BM - 1) * p.rx * p.xscale;
+    xlo[t] = (float)fmin(xs, xs + w) - 1e-3f;   // margin: the box test runs in fp32
+    xhi[t] = (float)fmax(xs, xs + w) + 1e-3f;
+    yy[t] = (float)ys;
+  }
+  __syncwarp();  // the previous tile's walks of this warp's mask are over
+#pragma unroll 1
+  for (int w = 0; w < kMaskWords; ++w) {
+    const int c = w * 32 + lane;
+    bool on = false;
+    if (c < nchunks) {
+      on = true;
+      if (p.skip) {
+        const float4 b = p.bbox[c];
+        on = false;
+#pragma unroll
+        for (int t = 0; t < CG; ++t) on = on || box_dist2(b, xlo[t], xhi[t], yy[t]) <= kSkipBits + 0.5f;
+      }
+    }
+    const uint32_t bits = __ballot_sync(0xffffffffu, on);
+    if (lane == 0) mask[w] = bits;
+  }
+  __syncwarp();
+}
+
+// Walk over the set bits of a chunk mask in ascending order: one shared-memory load per 32 chunks, a pop
+// (bits &= bits - 1) per chunk -- this sits on the per-chunk path of every role.  kSkip = false (the host found
+// next to nothing to skip for this grid and observation set, tc_plan_skip): plain counting, no mask at all.
+template <bool kSkip> struct ChunkIter {
+  const uint32_t* m;
+  int w;
+  uint32_t bits;
+  __device__ __forceinline__ void reset(const uint32_t* mask) {
+    if (kSkip) { m = mask; w = 0; bits = mask[0]; } else { w = 0; }
+  }
+  __device__ __forceinline__ int next() {  // next contracted chunk, or a large number when none is left
+    if (!kSkip) return w++;
+    while (!bits) {
+      if (++w >= kMaskWords) return 1 << 30;
+      bits = m[w];
+    }
+    const int c = w * 32 + __ffs(bits) - 1;
+    bits &= bits - 1;
+    return c;
+  }
+};
+
 // One thread's share of a K* chunk: cell r of the tile x 16 observations (2 groups of 8 = 2 16-byte
 // swizzle units of the row), written as fp16 hi / lo planes.  Returns sum_k K*[r,k] alpha[k] (scaled).
 //   K*[r,k] 2^shift_a = ex2(-(xs_k - cxs_r)^2) ey_k,   xs, cxs = x sqrt(log2(e) / 2 l^2),
@@ -308,8 +389,31 @@ __global__ void pack_obs_kernel(const double* __restrict__ xy, int n, int n_cap,
   out[k] = o;
 }
 
+// Bounding box (scaled coordinates) of every 64-observation chunk; an empty chunk gets an inverted box at infinity.
+__global__ void chunk_bbox_kernel(const float4* __restrict__ obs, int n, int nchunks, float4* __restrict__ bbox) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (c >= nchunks) return;
+  float xmin = INFINITY, xmax = -INFINITY, ymin = INFINITY, ymax = -INFINITY;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int k = c * BK + h * 32 + lane;
+    if (k < n) {
+      const float4 o = obs[k];
+      const float x = o.x + o.y, y = o.z + o.w;
+      xmin = fminf(xmin, x); xmax = fmaxf(xmax, x);
+      ymin = fminf(ymin, y); ymax = fmaxf(ymax, y);
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    xmin = fminf(xmin, __shfl_xor_sync(0xffffffffu, xmin, d)); xmax = fmaxf(xmax, __shfl_xor_sync(0xffffffffu, xmax, d));
+    ymin = fminf(ymin, __shfl_xor_sync(0xffffffffu, ymin, d)); ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, d));
+  }
+  if (lane == 0) bbox[c] = make_float4(xmin, xmax, ymin, ymax);
+}
+
 // ---- the kernel ----------------------------------------------------------------------------------
-template <int CG>
+template <int CG, bool kSkip>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   using Cfg = TcCfg<CG>;
@@ -334,6 +438,9 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   const long long ngtiles = (ntiles + CG - 1) / CG;  // tiles of CTA groups
   const int n_pad = (p.n + BK - 1) / BK * BK;
   const int jb_lo = p.j_lo / BN, jb_hi = (p.j_hi + BN - 1) / BN;
+  const int nchunks = n_pad / BK;
+  uint32_t* cmask = sh->cmask[warp];
+  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip};
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -354,17 +461,23 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
 
   if (warp == 0) {
     // =============================== TMA producer ===============================
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (long long gt = group; gt < ngtiles; gt += ngroups) {
+    uint32_t it = 0;
+    for (long long gt = group; gt < ngtiles; gt += ngroups) {
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (lane == 0) {
         for (int jb = jb_lo; jb < jb_hi; ++jb) {
           const int nch = chunks_of(jb, n_pad);
-          for (int kc = 0; kc < nch; ++kc, ++it) {
+          bool fresh = true;
+          ChunkIter<kSkip> ci;
+          ci.reset(cmask);
+          for (int kc = ci.next(); kc < nch; kc = ci.next(), ++it) {
             const int s = it % kStages;
             const uint32_t ph = (it / kStages) & 1u;
             // chunk c = kc - 4 jb >= 0 of the diagonal block only meets rows >= 64 c of this row block (L^-1 is
-            // lower triangular): the tile starts there and the MMA narrows to N = 256 - 64 c (see the issuer)
-            const int c = max(kc - jb * (BN / BK), 0);
+            // lower triangular): the tile starts there and the MMA narrows to N = 256 - 64 c (see the issuer).
+            // The first contracted chunk of a row block runs at full N: it initialises every accumulator column.
+            const int c = fresh ? 0 : max(kc - jb * (BN / BK), 0);
+            fresh = false;
             const int row = jb * BN + c * BK + (int)rank * ((int)Cfg::kBRows - c * (BK / 2));
             mbar_wait(&sh->empty[s], ph ^ 1u);
             const uint32_t bar = CG == 1 ? smem_u32(&sh->full[s]) : mapa(smem_u32(&sh->full[s]), 0);
@@ -374,20 +487,27 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           }
         }
       }
+      it = __shfl_sync(0xffffffffu, it, 0);
     }
-    __syncwarp();
   } else if (warp == 1) {
     // =============================== MMA issuer (leader CTA) ===============================
-    if (lane == 0 && rank == 0) {
-      uint32_t it = 0, acc_it = 0;
-      for (long long gt = group; gt < ngtiles; gt += ngroups) {
-        for (int jb = jb_lo; jb < jb_hi; ++jb, ++acc_it) {
+    uint32_t it = 0, acc_it = 0;
+    for (long long gt = group; rank == 0 && gt < ngtiles; gt += ngroups) {
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (lane == 0) {
+        for (int jb = jb_lo; jb < jb_hi; ++jb) {
+          const int nch = chunks_of(jb, n_pad);
+          ChunkIter<kSkip> ci;
+          ci.reset(cmask);
+          int kc = ci.next();
+          if (kc >= nch) continue;  // no chunk of this row block matters for the tile: V = 0, nothing to do
           const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
+          ++acc_it;
           mbar_wait(&sh->tmem_empty[as], aph ^ 1u);  // epilogue has drained this accumulator
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * BN;
-          const int nch = chunks_of(jb, n_pad);
-          for (int kc = 0; kc < nch; ++kc, ++it) {
+          bool fresh = true;
+          for (; kc < nch; kc = ci.next(), ++it) {
             const int s = it % kStages;
             const uint32_t ph = (it / kStages) & 1u;
             mbar_wait(&sh->full[s], ph);  // TMA bytes landed and generators stored their planes
@@ -395,22 +515,24 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(s))), dal = umma_desc_sw128(smem_u32(a_lo(s)));
             const uint64_t dbh = umma_desc_sw128(smem_u32(b_hi(s))), dbl = umma_desc_sw128(smem_u32(b_lo(s)));
             // diagonal block, chunk c: columns < 64 c of the accumulator get no contribution (zeros of L^-1)
-            const uint32_t c = (uint32_t)max(kc - jb * (BN / BK), 0);
+            const uint32_t c = fresh ? 0u : (uint32_t)max(kc - jb * (BN / BK), 0);
             const uint32_t idesc = idesc_f16<CG>(BN - c * BK), d_col = d_tmem + c * BK;
 #pragma unroll
             for (int ks = 0; ks < BK / UK; ++ks) {
               const uint64_t adv = (uint64_t)((ks * UK * 2) >> 4);  // +32 bytes along K inside the swizzle row
-              umma_f16<CG>(d_col, dal + adv, dbh + adv, idesc, (kc | ks) != 0);
+              umma_f16<CG>(d_col, dal + adv, dbh + adv, idesc, (fresh && ks == 0) ? 0u : 1u);
               umma_f16<CG>(d_col, dah + adv, dbl + adv, idesc, 1u);
               umma_f16<CG>(d_col, dah + adv, dbh + adv, idesc, 1u);
             }
+            fresh = false;
             umma_commit<CG>(&sh->empty[s]);  // stage reusable once these MMAs have read it
           }
           umma_commit<CG>(&sh->tmem_full[as]);  // accumulator complete
         }
       }
+      it = __shfl_sync(0xffffffffu, it, 0);
+      acc_it = __shfl_sync(0xffffffffu, acc_it, 0);
     }
-    __syncwarp();
   } else if (warp >= 4 && warp < 8) {
     // =============================== epilogue ===============================
     const int q = warp & 3;
@@ -418,9 +540,15 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     uint32_t acc_it = 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
       const long long tile = gt * CG + rank;
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
       float rs_hi = 0.f, rs_lo = 0.f;  // sum of squares of this cell's row of V (scaled), double-word fp32
-      for (int jb = jb_lo; jb < jb_hi; ++jb, ++acc_it) {
+      ChunkIter<kSkip> ci0;
+      ci0.reset(cmask);
+      const int first_chunk = ci0.next();
+      for (int jb = jb_lo; jb < jb_hi; ++jb) {
+        if (first_chunk >= chunks_of(jb, n_pad)) continue;  // row block skipped by the issuer: V = 0
         const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
+        ++acc_it;
         mbar_wait(&sh->tmem_full[as], aph);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
@@ -486,14 +614,11 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     const float cxs = (float)((double)r * p.rx * p.xscale);  // scaled offset of this thread's cell from the tile origin
     uint32_t it = 0;
     uint32_t tile_par = 0;
-    // observation data of the NEXT chunk is fetched while the current one is generated (chunk 0 always follows
-    // the last chunk of a row block, whatever the tile)
+    // observation data of the NEXT contracted chunk is fetched while the current one is generated; the guess
+    // (next set bit, else the first one again) is wrong only across tiles with different masks: checked at use
     float4 o_next = make_float4(0.f, 0.f, 0.f, 0.f);
     float a_next = 0.f;
-    if (lane < 16) {
-      o_next = p.obs[kq * 16 + lane];
-      a_next = p.alpha[kq * 16 + lane];
-    }
+    int c_next = -1;
     for (long long gt = group; gt < ngtiles; gt += ngroups, tile_par ^= 1u) {
       const long long tile = min(gt * CG + (long long)rank, ntiles - 1);  // an odd last tile: the peer recomputes it, no store
       const bool live = gt * CG + rank < ntiles;
@@ -503,22 +628,34 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       const float oxh = (float)ox0, oxl = (float)(ox0 - (double)oxh);
       const float oyh = (float)oy0, oyl = (float)(oy0 - (double)oyh);
       float mu_hi = 0.f, mu_lo = 0.f;  // fp32 inside a 16-observation quarter-chunk, double-word fp32 across chunks
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      ChunkIter<kSkip> ci;
+      ci.reset(cmask);
+      const int first_chunk = ci.next();
       for (int jb = jb_lo; jb < jb_hi; ++jb) {
         const bool last = (jb == jb_hi - 1);
         const int nch = chunks_of(jb, n_pad);
-        for (int kc = 0; kc < nch; ++kc, ++it) {
+        ci.reset(cmask);
+        int kc = ci.next();
+        for (int kn; kc < nch; kc = kn, ++it) {
+          kn = ci.next();  // the chunk after this one (one look-ahead serves the loop and the prefetch below)
           const int s = it % kStages;
           const uint32_t ph = (it / kStages) & 1u;
           // per-observation terms of this quarter-chunk, one observation per lane (lanes 0-15)
           if (lane < 16) {
             const int k = kc * BK + kq * 16 + lane;
+            if (c_next != kc) {  // warp-uniform
+              o_next = p.obs[k];
+              a_next = p.alpha[k];
+            }
             const float yr = (o_next.z - oyh) + (o_next.w - oyl);
             ox[lane] = (o_next.x - oxh) + (o_next.y - oxl);  // (the previous chunk's readers passed the __syncwarp below)
             oy[lane] = k < p.n ? ex2_approx(-yr * yr) * p.a_scale : 0.f;
             oa[lane] = a_next;
-            const int kn = (kc + 1 < nch ? (kc + 1) * BK : 0) + kq * 16 + lane;  // < n_cap: the buffers are padded
-            o_next = p.obs[kn];
-            a_next = p.alpha[kn];
+            c_next = kn < nch ? kn : first_chunk;  // (a tile without any chunk never gets here)
+            const int kp = c_next * BK + kq * 16 + lane;  // < n_cap: the buffers are padded
+            o_next = p.obs[kp];
+            a_next = p.alpha[kp];
           }
           __syncwarp();
           uint32_t hi[8], lo[8];
@@ -602,6 +739,8 @@ int32_t tc_init(sbo_ctx* ctx) {
   int cg = 2;
   if (const char* s = std::getenv("SBO_TC_CTA_GROUP")) cg = (std::atoi(s) == 1) ? 1 : 2;
   ctx->tc_cg = cg;
+  ctx->tc_skip = true;   // SBO_TC_SKIP=0: contract every chunk (dense), for A/B measurements
+  if (const char* s = std::getenv("SBO_TC_SKIP")) ctx->tc_skip = std::atoi(s) != 0;
   tc_plane_shifts(ctx->cfg, &ctx->shift_a, &ctx->shift_b);
   CUtensorMap* map = new CUtensorMap;
   const cuuint64_t nc = (cuuint64_t)ctx->n_cap;
@@ -616,9 +755,13 @@ int32_t tc_init(sbo_ctx* ctx) {
     delete map;
     return fail(ctx, SBO_ERR_CUDA, "tc_init: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
   }
-  e = cudaFuncSetAttribute(posterior_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<1>());
+  e = cudaFuncSetAttribute(posterior_tc_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<1>());
   if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(posterior_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
+    e = cudaFuncSetAttribute(posterior_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<1>());
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(posterior_tc_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(posterior_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
   if (e != cudaSuccess) {
     delete map;
     return cuda_fail(ctx, e, "tc_init: cudaFuncSetAttribute(max dynamic smem)");
@@ -642,7 +785,52 @@ int32_t tc_pack_observations(sbo_ctx* ctx) {
   pack_obs_kernel<<<(ctx->n_cap + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_xy, ctx->n, ctx->n_cap, xscale,
                                                                      reinterpret_cast<float4*>(ctx->d_obs_f32));
   SBO_LAUNCH_CHECK(ctx, "pack_obs_kernel");
+  const int nchunks = ctx->n_cap / BK;
+  chunk_bbox_kernel<<<(nchunks * 32 + 255) / 256, 256, 0, ctx->stream>>>(reinterpret_cast<const float4*>(ctx->d_obs_f32), ctx->n,
+                                                                         nchunks, reinterpret_cast<float4*>(ctx->d_chunk_bbox));
+  SBO_LAUNCH_CHECK(ctx, "chunk_bbox_kernel");
   return SBO_OK;
+}
+
+// Is there enough to skip on this grid with these observations to pay for the mask walk (~3 % at C2, where
+// almost every chunk matters everywhere)?  Host-side estimate on a sample of cell tiles: the fraction of
+// (row block, chunk) visits that the box test keeps, with the same boxes and cut-off as the kernel.  Cached
+// until the grid or the observations change.
+bool tc_plan_skip(sbo_ctx* ctx) {
+  if (!ctx->tc_skip) return false;
+  if (ctx->tc_skip_plan >= 0) return ctx->tc_skip_plan != 0;
+  const int n = ctx->n, nchunks = (n + BK - 1) / BK;
+  ctx->tc_skip_plan = 0;
+  if (nchunks < 8 || (int)ctx->h_xy_sorted.size() < 2 * n) return false;
+  const double xs = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
+  std::vector<double> box(4 * (size_t)nchunks);
+  for (int c = 0; c < nchunks; ++c) {
+    double x0 = 1e300, x1 = -1e300, y0 = 1e300, y1 = -1e300;
+    for (int k = c * BK; k < std::min(n, (c + 1) * BK); ++k) {
+      const double x = ctx->h_xy_sorted[2 * (size_t)k] * xs, y = ctx->h_xy_sorted[2 * (size_t)k + 1] * xs;
+      x0 = std::min(x0, x); x1 = std::max(x1, x); y0 = std::min(y0, y); y1 = std::max(y1, y);
+    }
+    box[4 * c] = x0; box[4 * c + 1] = x1; box[4 * c + 2] = y0; box[4 * c + 3] = y1;
+  }
+  const int rows = ctx->row1 - ctx->row0, tiles_per_row = (ctx->W + BM - 1) / BM;
+  const int nblocks = (n + BN - 1) / BN;
+  const int sr = std::min(rows, 24), sc = std::min(tiles_per_row, 24);
+  double kept = 0.0, total = 0.0;
+  for (int a = 0; a < sr; ++a)
+    for (int b = 0; b < sc; ++b) {
+      const int row = ctx->row0 + (int)((long long)a * rows / sr), col0 = (int)((long long)b * tiles_per_row / sc) * BM;
+      const double tx0 = (ctx->x0 + col0 * ctx->rx) * xs, tx1 = tx0 + (BM - 1) * ctx->rx * xs;
+      const double xlo = std::min(tx0, tx1), xhi = std::max(tx0, tx1), y = (ctx->y0 + row * ctx->ry) * xs;
+      for (int c = 0; c < nchunks; ++c) {
+        const double wgt = nblocks - c / (BN / BK);  // row blocks that walk chunk c
+        const double dx = std::max(std::max(box[4 * c] - xhi, xlo - box[4 * c + 1]), 0.0);
+        const double dy = std::max(std::max(box[4 * c + 2] - y, y - box[4 * c + 3]), 0.0);
+        total += wgt;
+        if (dx * dx + dy * dy <= kSkipBits + 0.5) kept += wgt;
+      }
+    }
+  ctx->tc_skip_plan = (total > 0.0 && kept < 0.85 * total) ? 1 : 0;
+  return ctx->tc_skip_plan != 0;
 }
 
 int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
@@ -671,12 +859,17 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.sf2 = (float)sf2;
   p.prior_mean = (float)ctx->cfg.prior_mean;
   p.dbg_v = g_dbg_v;
+  p.bbox = reinterpret_cast<const float4*>(ctx->d_chunk_bbox);
+  p.skip = tc_plan_skip(ctx) ? 1 : 0;
+  if ((ctx->n + BK - 1) / BK > kMaskWords * 32)
+    return fail(ctx, SBO_ERR_CAPACITY, "tcgen05 posterior kernel: more than 32 768 observations (chunk mask capacity)");
   SBO_TRY(tc_pack_observations(ctx));
   const long long ntiles = (long long)p.rows_local * ((p.W + BM - 1) / BM);
   const CUtensorMap& tmap = *static_cast<CUtensorMap*>(ctx->tmap_planes);
   if (ctx->tc_cg == 1) {
     const unsigned grid = (unsigned)std::min<long long>(ntiles, ctx->sm_count);  // persistent: one CTA per SM
-    posterior_tc_kernel<1><<<grid, kThreadsTc, tc_smem_bytes<1>(), ctx->stream>>>(tmap, p);
+    if (p.skip) posterior_tc_kernel<1, true><<<grid, kThreadsTc, tc_smem_bytes<1>(), ctx->stream>>>(tmap, p);
+    else posterior_tc_kernel<1, false><<<grid, kThreadsTc, tc_smem_bytes<1>(), ctx->stream>>>(tmap, p);
   } else {
     // persistent CTA pairs: one cluster of 2 per TPC
     const long long pairs = std::min<long long>((ntiles + 1) / 2, ctx->sm_count / 2);
@@ -692,7 +885,8 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    const cudaError_t e = cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2>, tmap, p);
+    const cudaError_t e = p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, true>, tmap, p)
+                                 : cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, false>, tmap, p);
     if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_kernel<2> (cluster launch)");
   }
   SBO_LAUNCH_CHECK(ctx, "posterior_tc_kernel");

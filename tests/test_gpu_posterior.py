@@ -201,6 +201,31 @@ def test_single_cta_variant_matches_pair(pkg, oracle, coracle, monkeypatch):
     assert np.array_equal(out["1"][0], out["2"][0]) and np.array_equal(out["1"][1], out["2"][1])
 
 
+@pytest.mark.parametrize("spread", [1.0, 4.0, 12.0])
+def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, monkeypatch, spread):
+    """The tcgen05 kernel leaves out 64-observation chunks whose K* entries are all < 2^-44 sigma_f^2 for a cell tile
+    (posterior_tc.cu, block sparsity of K*).  Stretching the domain (spread) makes most chunks, whole row blocks and
+    for some tiles everything skippable; results must still meet the oracle and agree with the dense walk
+    (SBO_TC_SKIP=0) far below the tolerance."""
+    p = S.make_problem("C3", n=1500, W=384, H=7)
+    p.xy = p.xy * spread
+    p.rx, p.ry = p.rx * spread, p.ry * spread * 9.0        # a tall grid: rows far from each other
+    ref = reference(oracle, coracle, p)
+    out = {}
+    for skip in ("1", "0"):
+        monkeypatch.setenv("SBO_TC_SKIP", skip)
+        with make_ctx(pkg, p, kernel="tcgen05") as ctx:
+            ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+            ctx.set_observations(p.xy, p.y)
+            res, mask = ctx.step(p.beta, p.f_min)
+            out[skip] = (ctx.mu(), ctx.sigma2(), res.ms_posterior)
+            band = check_step(p, ref, res, mask, out[skip][0], out[skip][1], "fp32", label=f"spread {spread} skip={skip}")
+            check_argmax(res, ref, band, mask)
+    print(f"    posterior ms: skipping {out['1'][2]:.3f}, dense {out['0'][2]:.3f}")
+    assert np.abs(out["1"][0] - out["0"][0]).max() <= 1e-9 * max(1.0, np.abs(ref["mu"]).max()) + 2e-6
+    assert np.abs(out["1"][1] - out["0"][1]).max() <= 1e-6
+
+
 def test_full_size_c2_properties(pkg):
     """BASELINE config C2 at full size (1024 obs x 1M cells): size-independent properties."""
     p = S.make_problem("C2")
