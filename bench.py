@@ -307,6 +307,15 @@ def main():
                     "frac": achieved / peak, "traffic": traffic, "kernel": "posterior_tc_kernel" if used_tc else "posterior_simt_kernel",
                     "peak_source": peak_note, "ms_kernel": ms_post, "credited_flops_per_launch": flops,
                     "executed_over_credited": executed_over_credited(p.n) if used_tc else 1.0}
+        if used_tc:
+            cg, skipping, kept = ctx.tc_plan()
+            roofline["cta_group"] = cg
+            if skipping:   # block-sparse K*: the credited (dense triangular) flops include work that is never executed
+                roofline["executed_over_credited"] *= kept
+                roofline["block_sparse"] = {"kept_fraction_estimate": kept,
+                                            "note": "chunks of 64 observations whose K* entries are all < 2^-44 sigma_f^2 for a "
+                                                    "cell tile are skipped; frac counts the dense triangular flops, so it can "
+                                                    "exceed 1/3 (SBO_TC_SKIP=0 runs the dense walk)"}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cpu = cpu_posterior_sample(p, args.cpu_seconds)

@@ -242,6 +242,11 @@ int32_t sbo_merge_step_out(const sbo_step_out* parts, int32_t count, sbo_step_ou
 
 /* Number of kernel launches issued by this context since creation. */
 int64_t sbo_launch_count(const sbo_ctx* ctx);
+/* How the tcgen05 posterior kernel will run on the current grid and observations: CTAs per MMA group (2 = CTA
+ * pair), whether it walks block-sparsity masks of K* (chunks of 64 observations farther than the kernel's reach
+ * from a whole cell tile are left out: every skipped entry is < 2^-44 sigma_f^2), and the planner's estimate of the
+ * share of (row block, chunk) visits that remain (1.0 when dense). */
+int32_t sbo_tc_plan(sbo_ctx* ctx, int32_t* cta_group, int32_t* skipping, double* kept_fraction);
 /* Device properties the library sees: SM count, and 1 if tcgen05 path usable. */
 int32_t sbo_device_info(const sbo_ctx* ctx, int32_t* sm_count, int32_t* tcgen05_ok);
 

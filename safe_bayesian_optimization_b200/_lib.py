@@ -68,6 +68,7 @@ SYMBOLS = {
     "sbo_frontier_pixel_maps": (C.c_int32, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "sbo_frontier_image": (C.c_int32, [_P, _U8, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "sbo_compact_cells": (C.c_int32, [_P, C.c_int32, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int64)]),
+    "sbo_tc_plan": (C.c_int32, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double)]),
     "sbo_copy_mu": (C.c_int32, [_P, _P]),
     "sbo_copy_sigma2": (C.c_int32, [_P, _P]),
     "sbo_copy_mu_f64": (C.c_int32, [_P, _D]),

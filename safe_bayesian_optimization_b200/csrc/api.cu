@@ -297,6 +297,15 @@ int32_t sbo_num_observations(const sbo_ctx* ctx) { return ctx ? ctx->n : SBO_ERR
 
 int64_t sbo_launch_count(const sbo_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
+int32_t sbo_tc_plan(sbo_ctx* ctx, int32_t* cta_group, int32_t* skipping, double* kept_fraction) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  const bool skip = ctx->tc_ok && ctx->grid_set ? tc_plan_skip(ctx) : false;
+  if (cta_group) *cta_group = ctx->tc_cg;
+  if (skipping) *skipping = skip ? 1 : 0;
+  if (kept_fraction) *kept_fraction = skip ? ctx->tc_kept_frac : 1.0;
+  return SBO_OK;
+}
+
 int32_t sbo_device_info(const sbo_ctx* ctx, int32_t* sm_count, int32_t* tcgen05_ok) {
   if (!ctx) return SBO_ERR_INVALID_ARG;
   if (sm_count) *sm_count = ctx->sm_count;

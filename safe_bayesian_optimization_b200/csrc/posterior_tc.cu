@@ -801,6 +801,7 @@ bool tc_plan_skip(sbo_ctx* ctx) {
   if (ctx->tc_skip_plan >= 0) return ctx->tc_skip_plan != 0;
   const int n = ctx->n, nchunks = (n + BK - 1) / BK;
   ctx->tc_skip_plan = 0;
+  ctx->tc_kept_frac = 1.0;
   if (nchunks < 8 || (int)ctx->h_xy_sorted.size() < 2 * n) return false;
   const double xs = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
   std::vector<double> box(4 * (size_t)nchunks);
@@ -829,6 +830,7 @@ bool tc_plan_skip(sbo_ctx* ctx) {
         if (dx * dx + dy * dy <= kSkipBits + 0.5) kept += wgt;
       }
     }
+  ctx->tc_kept_frac = total > 0.0 ? kept / total : 1.0;
   ctx->tc_skip_plan = (total > 0.0 && kept < 0.85 * total) ? 1 : 0;
   return ctx->tc_skip_plan != 0;
 }

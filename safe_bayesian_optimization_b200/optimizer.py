@@ -192,6 +192,12 @@ class SboContext:
         return int(cell.value)
 
     # -- read-back ----------------------------------------------------------
+    def tc_plan(self):
+        """(cta_group, skipping, kept_fraction) of the tcgen05 posterior kernel on the current grid + observations."""
+        cg, sk, kf = C.c_int32(0), C.c_int32(0), C.c_double(1.0)
+        self._check(self.lib.sbo_tc_plan(self._h, C.byref(cg), C.byref(sk), C.byref(kf)))
+        return cg.value, bool(sk.value), kf.value
+
     def frontier_image(self):
         """(img H x W uint8 0/255, col_of_px int32[W], row_of_py int32[H]): the image of reference :444-456 built on the
         GPU with the reference's pixel map, and the pixel -> cell tables that replace its hash map (:468-475)."""
