@@ -7,9 +7,12 @@
 // like (one measurement per second, src/turtlesim_spatial_publisher.py:43) and what BASELINE configs C3/C5 time.
 // The contraction has N = k (<= 8) columns: far too thin for a tensor-core tile (the 256-row block kernel of
 // posterior_tc.cu spends 256/k times the necessary MMAs on it), and its cost is the K* entries themselves --
-// one ex2 (fp32) or exp (fp64) per cell and observation.  Hence a SIMT kernel: one thread owns C cells of a grid
-// row, a CTA stages 256 observations at a time (tile-relative coordinate, y factor, alpha, the k new rows of
-// L^-1) in shared memory and every thread reads them as broadcast 16-byte vectors.
+// one ex2 (fp32) or exp (fp64) per cell and observation if done naively.  The RBF kernel on a grid is separable,
+//   k*(cell(ix, iy), obs j) = sigma_f^2 ex(ix, j) ey(iy, j),
+// so a thread that owns C columns x R rows of cells needs ex only once per (column, observation) and the row
+// factor arrives pre-multiplied:  the CTA stages, per observation, the tile-relative x and the R (1 + k) products
+// ey(r, j) alpha_j and ey(r, j) Linv[new row q][j]; the inner loop is then one FMA per (cell, observation, output)
+// and 1/R exponentials per (cell, observation), with all staged values read as broadcast 16-byte vectors.
 //
 // Numerics: fp32 mode accumulates in fp32 over 64 observations and in fp64 across (an fp32 running sum over
 // n = 16 384 terms would cost ~1e-5); coordinates are tile-relative fp32 (hi, lo) differences as in the
@@ -23,7 +26,6 @@ namespace sbo {
 namespace {
 
 constexpr int kThinThreads = 256;
-constexpr int kChunk = 256;   // observations staged per pass
 constexpr int kSub = 64;      // fp32 accumulation span
 
 struct ThinParams {
@@ -55,110 +57,139 @@ __device__ __forceinline__ void load4(const double* p, double (&v)[4]) {
   v[0] = t0.x; v[1] = t0.y; v[2] = t1.x; v[3] = t1.y;
 }
 
-template <typename T, int KR>
-struct __align__(16) ThinSmem {
-  T x[kChunk];       // tile-relative x of the observation (fp32 mode: scaled)
-  T e[kChunk];       // y factor: sigma_f^2 exp(-dy^2 / 2 l^2), 0 beyond n
-  T a[kChunk];       // alpha
-  T l[KR][kChunk];   // the new rows of L^-1
+// Tile = (kThinThreads * C) columns x R grid rows; thread = C columns x R rows.  NP products per observation:
+// slot r (1 + KR) is ey_r alpha, slots r (1 + KR) + 1 + q are ey_r Linv[new row q].
+template <typename T, int KR, int C, int R>
+struct ThinCfg {
+  static constexpr int kNP = R * (1 + KR);
+  static constexpr int kChunk = sizeof(T) == 4 ? 256 : 128;   // observations staged per pass (<= 48 KB static smem)
+  static_assert(kNP % 4 == 0, "products are read as 4-vectors");
 };
 
-// K* entry from the tile-relative x difference and the staged y factor
-__device__ __forceinline__ float kstar(float dx, float e, double) { return ex2f(-dx * dx) * e; }
-__device__ __forceinline__ double kstar(double dx, double e, double inv2l2) { return exp(-dx * dx * inv2l2) * e; }
+template <typename T, int KR, int C, int R>
+struct __align__(16) ThinSmem {
+  T x[ThinCfg<T, KR, C, R>::kChunk];                               // tile-relative x (fp32 mode: scaled)
+  T p[ThinCfg<T, KR, C, R>::kChunk][ThinCfg<T, KR, C, R>::kNP];    // zero beyond n and beyond the last grid row
+};
 
-template <typename T, int KR, int C>
+// x factor of a K* entry from the tile-relative difference
+__device__ __forceinline__ float xfactor(float dx, double) { return ex2f(-dx * dx); }
+__device__ __forceinline__ double xfactor(double dx, double inv2l2) { return exp(-dx * dx * inv2l2); }
+
+template <typename T, int KR, int C, int R>
 __global__ void __launch_bounds__(kThinThreads)
 posterior_thin_kernel(ThinParams p, T* __restrict__ mu_out, T* __restrict__ s2_out) {
-  __shared__ ThinSmem<T, KR> sm;
+  using Cfg = ThinCfg<T, KR, C, R>;
+  constexpr int NP = Cfg::kNP, kChunk = Cfg::kChunk;
   constexpr bool kF32 = sizeof(T) == 4;
+  __shared__ ThinSmem<T, KR, C, R> sm;
   const int tid = threadIdx.x;
   const int span = kThinThreads * C;
   const int tiles_per_row = (p.W + span - 1) / span;
-  const long long ntiles = (long long)p.rows_local * tiles_per_row;
+  const int row_groups = (p.rows_local + R - 1) / R;
+  const long long ntiles = (long long)row_groups * tiles_per_row;
 
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int lrow = (int)(tile / tiles_per_row), col0 = (int)(tile % tiles_per_row) * span;
+    const int r0 = (int)(tile / tiles_per_row) * R, col0 = (int)(tile % tiles_per_row) * span;
     // tile origin; fp32 mode works in scaled units with (hi, lo) pairs, fp64 mode in plain coordinates
-    const double ox = cell_coord(p.x0, p.rx, col0), oy = cell_coord(p.y0, p.ry, p.row0 + lrow);
-    const double oxs = ox * p.xscale, oys = oy * p.xscale;
+    const double ox = cell_coord(p.x0, p.rx, col0);
+    const double oxs = ox * p.xscale;
     const float oxh = (float)oxs, oxl = (float)(oxs - (double)oxh);
-    const float oyh = (float)oys, oyl = (float)(oys - (double)oyh);
     T cx[C];
 #pragma unroll
     for (int q = 0; q < C; ++q) {
       const double off = (double)(q * kThinThreads + tid) * p.rx;
       cx[q] = kF32 ? (T)(off * p.xscale) : (T)off;
     }
-    double mu[C], u[C][KR];
+    double acc[C][NP];   // fp32 mode: sums across 64-observation spans; fp64 mode: the accumulators themselves
 #pragma unroll
-    for (int q = 0; q < C; ++q) {
-      mu[q] = 0.0;
+    for (int q = 0; q < C; ++q)
 #pragma unroll
-      for (int r = 0; r < KR; ++r) u[q][r] = 0.0;
-    }
+      for (int t = 0; t < NP; ++t) acc[q][t] = 0.0;
 
     for (int k0 = 0; k0 < p.n; k0 += kChunk) {
-      // ---- stage observations k0 .. k0+255 ----
-      {
+      // ---- stage observations k0 .. k0 + kChunk - 1 ----
+      if (tid < kChunk) {
         const int j = k0 + tid;
-        T tx = (T)0, te = (T)0, ta = (T)0;
-        if (j < p.n) {
+        const bool live = j < p.n;
+        T tx = (T)0, ta = (T)0, tl[KR];
+        float4 of = make_float4(0.f, 0.f, 0.f, 0.f);
+        double2 od = make_double2(0.0, 0.0);
+#pragma unroll
+        for (int q = 0; q < KR; ++q) tl[q] = (T)0;
+        if (live) {
           if (kF32) {
-            const float4 o = p.obs_f32[j];
-            const float yr = (o.z - oyh) + (o.w - oyl);
-            tx = (T)((o.x - oxh) + (o.y - oxl));
-            te = (T)(ex2f(-yr * yr) * (float)p.sf2);
+            of = p.obs_f32[j];
+            tx = (T)((of.x - oxh) + (of.y - oxl));
           } else {
-            const double2 o = *reinterpret_cast<const double2*>(p.xy + 2 * (size_t)j);
-            const double dy = o.y - oy;
-            tx = (T)(o.x - ox);
-            te = (T)(p.sf2 * exp(-dy * dy * p.inv2l2));
+            od = *reinterpret_cast<const double2*>(p.xy + 2 * (size_t)j);
+            tx = (T)(od.x - ox);
           }
           ta = (T)p.alpha[j];
-        }
-        sm.x[tid] = tx; sm.e[tid] = te; sm.a[tid] = ta;
 #pragma unroll
-        for (int r = 0; r < KR; ++r)
-          sm.l[r][tid] = (j < p.n && r < p.k_new) ? (T)p.Linv[(size_t)(p.row_lo + r) * p.ld + j] : (T)0;
+          for (int q = 0; q < KR; ++q)
+            if (q < p.k_new) tl[q] = (T)p.Linv[(size_t)(p.row_lo + q) * p.ld + j];
+        }
+        sm.x[tid] = tx;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          T e = (T)0;
+          if (live && r0 + r < p.rows_local) {
+            const double oy = cell_coord(p.y0, p.ry, p.row0 + r0 + r);
+            if (kF32) {
+              const double oys = oy * p.xscale;
+              const float oyh = (float)oys, oyl = (float)(oys - (double)oyh);
+              const float yr = (of.z - oyh) + (of.w - oyl);
+              e = (T)(ex2f(-yr * yr) * (float)p.sf2);
+            } else {
+              const double dy = od.y - oy;
+              e = (T)(p.sf2 * exp(-dy * dy * p.inv2l2));
+            }
+          }
+          sm.p[tid][r * (1 + KR)] = e * ta;
+#pragma unroll
+          for (int q = 0; q < KR; ++q) sm.p[tid][r * (1 + KR) + 1 + q] = e * tl[q];
+        }
       }
       __syncthreads();
       const int cnt = min(kChunk, p.n - k0);
       for (int s0 = 0; s0 < cnt; s0 += kSub) {
-        T fmu[C], fu[C][KR];
+        T f[C][NP];
+        if (kF32) {
 #pragma unroll
-        for (int q = 0; q < C; ++q) {
-          fmu[q] = (T)0;
+          for (int q = 0; q < C; ++q)
 #pragma unroll
-          for (int r = 0; r < KR; ++r) fu[q][r] = (T)0;
+            for (int t = 0; t < NP; ++t) f[q][t] = (T)0;
+        } else {
+#pragma unroll
+          for (int q = 0; q < C; ++q)
+#pragma unroll
+            for (int t = 0; t < NP; ++t) f[q][t] = (T)acc[q][t];
         }
-#pragma unroll 2
+#pragma unroll 1
         for (int j4 = s0; j4 < s0 + kSub; j4 += 4) {  // the chunk is zero-padded: no bound check inside
-          T xs[4], es[4], as[4], ls[KR][4];
+          T xs[4];
           load4(&sm.x[j4], xs);
-          load4(&sm.e[j4], es);
-          load4(&sm.a[j4], as);
-#pragma unroll
-          for (int r = 0; r < KR; ++r) load4(&sm.l[r][j4], ls[r]);
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
+            T ex[C];
 #pragma unroll
-            for (int q = 0; q < C; ++q) {
-              const T kv = kstar(xs[i] - cx[q], es[i], p.inv2l2);
-              fmu[q] = fma(kv, as[i], fmu[q]);
+            for (int q = 0; q < C; ++q) ex[q] = xfactor(xs[i] - cx[q], p.inv2l2);
 #pragma unroll
-              for (int r = 0; r < KR; ++r) {
-                fu[q][r] = fma(kv, ls[r][i], fu[q][r]);
-              }
+            for (int t0 = 0; t0 < NP; t0 += 4) {
+              T pv[4];
+              load4(&sm.p[j4 + i][t0], pv);
+#pragma unroll
+              for (int t = 0; t < 4; ++t)
+#pragma unroll
+                for (int q = 0; q < C; ++q) f[q][t0 + t] = fma(ex[q], pv[t], f[q][t0 + t]);
             }
           }
         }
 #pragma unroll
-        for (int q = 0; q < C; ++q) {
-          mu[q] += (double)fmu[q];
+        for (int q = 0; q < C; ++q)
 #pragma unroll
-          for (int r = 0; r < KR; ++r) u[q][r] += (double)fu[q][r];
-        }
+          for (int t = 0; t < NP; ++t) acc[q][t] = kF32 ? acc[q][t] + (double)f[q][t] : (double)f[q][t];
       }
       __syncthreads();
     }
@@ -166,24 +197,29 @@ posterior_thin_kernel(ThinParams p, T* __restrict__ mu_out, T* __restrict__ s2_o
 #pragma unroll
     for (int q = 0; q < C; ++q) {
       const int col = col0 + q * kThinThreads + tid;
-      if (col < p.W) {
-        const long long lc = (long long)lrow * p.W + col;
-        double red = 0.0;
 #pragma unroll
-        for (int r = 0; r < KR; ++r) red = fma(u[q][r], u[q][r], red);
-        s2_out[lc] = (T)((double)s2_out[lc] - red);
-        mu_out[lc] = (T)(p.prior_mean + mu[q]);
+      for (int r = 0; r < R; ++r) {
+        if (col < p.W && r0 + r < p.rows_local) {
+          const long long lc = (long long)(r0 + r) * p.W + col;
+          double red = 0.0;
+#pragma unroll
+          for (int t = 0; t < KR; ++t) red = fma(acc[q][r * (1 + KR) + 1 + t], acc[q][r * (1 + KR) + 1 + t], red);
+          s2_out[lc] = (T)((double)s2_out[lc] - red);
+          mu_out[lc] = (T)(p.prior_mean + acc[q][r * (1 + KR)]);
+        }
       }
     }
   }
 }
 
-template <typename T, int KR, int C>
+template <typename T, int KR, int C, int R>
 void launch_thin(sbo_ctx* ctx, const ThinParams& p) {
   const int span = kThinThreads * C;
-  const long long ntiles = (long long)p.rows_local * ((p.W + span - 1) / span);
-  const unsigned grid = (unsigned)std::min<long long>(ntiles, (long long)ctx->sm_count * 8);
-  posterior_thin_kernel<T, KR, C><<<grid, kThinThreads, 0, ctx->stream>>>(p, static_cast<T*>(ctx->d_mu), static_cast<T*>(ctx->d_s2));
+  const long long ntiles = (long long)((p.rows_local + R - 1) / R) * ((p.W + span - 1) / span);
+  int per_sm = 1;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, posterior_thin_kernel<T, KR, C, R>, kThinThreads, 0);
+  const unsigned grid = (unsigned)std::min<long long>(ntiles, (long long)ctx->sm_count * std::max(per_sm, 1));
+  posterior_thin_kernel<T, KR, C, R><<<grid, kThinThreads, 0, ctx->stream>>>(p, static_cast<T*>(ctx->d_mu), static_cast<T*>(ctx->d_s2));
 }
 
 }  // namespace
@@ -207,17 +243,17 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
   if (ctx->cfg.precision == SBO_FP32) {
     SBO_TRY(tc_pack_observations(ctx));
     switch (kr) {
-      case 1: launch_thin<float, 1, 4>(ctx, p); break;
-      case 2: launch_thin<float, 2, 4>(ctx, p); break;
-      case 4: launch_thin<float, 4, 2>(ctx, p); break;
-      default: launch_thin<float, 8, 2>(ctx, p); break;
+      case 1: launch_thin<float, 1, 2, 8>(ctx, p); break;
+      case 2: launch_thin<float, 2, 2, 4>(ctx, p); break;
+      case 4: launch_thin<float, 4, 1, 8>(ctx, p); break;
+      default: launch_thin<float, 8, 1, 4>(ctx, p); break;
     }
   } else {
     switch (kr) {
-      case 1: launch_thin<double, 1, 2>(ctx, p); break;
-      case 2: launch_thin<double, 2, 2>(ctx, p); break;
-      case 4: launch_thin<double, 4, 2>(ctx, p); break;
-      default: launch_thin<double, 8, 1>(ctx, p); break;
+      case 1: launch_thin<double, 1, 1, 8>(ctx, p); break;
+      case 2: launch_thin<double, 2, 1, 8>(ctx, p); break;
+      case 4: launch_thin<double, 4, 1, 4>(ctx, p); break;
+      default: launch_thin<double, 8, 1, 4>(ctx, p); break;
     }
   }
   SBO_LAUNCH_CHECK(ctx, "posterior_thin_kernel");
