@@ -3,11 +3,13 @@
 // include/sbo.h.  Plain C++17, no CUDA headers, no torch: what a maintainer's node links against.
 //
 //   ctor (:48-77)                         -> sbo_create + sbo_set_grid
-//   measurements (publisher.py:137-145)   -> sbo_set_observations / sbo_append_observations
+//   measurements (publisher.py:137-145)   -> sbo_set_observations, then sbo_ingest_measurements one at a time
 //   request + unpack + ComputeSets        -> sbo_step / sbo_step_incremental (mask lands in the "cv::Mat" buffer)
 //   FindSafetyContourIndices (:418-497)   -> stays on the host (OpenCV in the node; a 4-neighbour border
 //                                            scan stands in for cv::findContours here, OpenCV-C++ is absent)
-//   GetNextSubgoal (:499-550)             -> sbo_select_subgoal
+//   GetNextSubgoal (:499-550) + goal-in-polygon test and polydist projection (:650-706)
+//                                         -> sbo_subgoal_point (a fixed quadrilateral stands in for the eroded alpha
+//                                            shape: CGAL / Boost are absent here and stay on the host in the node)
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -64,9 +66,13 @@ int main(int argc, char** argv) {
     sbo_step_out out{};
     if (step == 0) CHECK(sbo_step(ctx, beta, f_min, safety_image.data(), &out));
     else {
-      double nxy[2] = {U(rng), U(rng)};
-      double ny = terrain(nxy[0], nxy[1], L) + N(rng);
-      CHECK(sbo_append_observations(ctx, nxy, &ny, 1));          // one measurement per second (:43)
+      sbo_measurement msg{};                                     // one SpatialMeasurement per second (:43, :137-145)
+      msg.x = U(rng); msg.y = U(rng); msg.z = 0.0;
+      msg.value = terrain(msg.x, msg.y, L) + N(rng);
+      msg.uncertainty = 0.1; msg.stamp_sec = step;
+      int32_t size = 0, refit = 0;
+      CHECK(sbo_ingest_measurements(ctx, &msg, 1, &size, &refit));
+      if (size != n + step || refit) { std::fprintf(stderr, "ingestion: size %d refit %d\n", size, refit); return 3; }
       CHECK(sbo_step_incremental(ctx, beta, f_min, safety_image.data(), &out));
     }
     // frontier: safe cells with an unsafe (or outside) 4-neighbour -- the node uses cv::findContours here
@@ -79,17 +85,28 @@ int main(int argc, char** argv) {
                           !safety_image[(size_t)(iy + 1) * W + ix];
         if (edge) frontier.push_back(iy * W + ix);
       }
-    int32_t cell = -1;
-    CHECK(sbo_select_subgoal(ctx, frontier.data(), (int64_t)frontier.size(), goal[0], goal[1], &cell));
+    // stand-in for eroded_concave_polygon_: a quadrilateral in the lower-left of the domain (the goal lies outside it,
+    // so the frontier subgoal is chosen and projected; step 2 moves the goal inside to take the other branch)
+    const double poly[8] = {0.1 * L, 0.1 * L, 0.6 * L, 0.15 * L, 0.55 * L, 0.6 * L, 0.12 * L, 0.5 * L};
+    const int32_t ring_size = 4;
+    const double gx = step == 2 ? 0.3 * L : goal[0], gy = step == 2 ? 0.3 * L : goal[1];
+    int32_t cell = -1, kind = SBO_SUBGOAL_NONE;
+    double subgoal[2] = {NAN, NAN}, pdist = 0.0;
+    CHECK(sbo_subgoal_point(ctx, frontier.data(), (int64_t)frontier.size(), gx, gy, poly, &ring_size, 1, subgoal, &cell,
+                            &kind, &pdist));
+    if (step == 2 && (kind != SBO_SUBGOAL_GOAL || subgoal[0] != gx || subgoal[1] != gy)) {
+      std::fprintf(stderr, "goal inside the polygon must be its own subgoal\n");
+      return 3;
+    }
     long long count = 0;
     for (uint8_t v : safety_image) count += v == 255;
-    std::printf("step %d: n=%d safe=%lld (mask count %lld) argmax_ucb=(%lld, %.4f) frontier=%zu subgoal cell=%d "
-                "(%.3f, %.3f) kernel=%d posterior %.3f ms total %.3f ms\n",
+    std::printf("step %d: n=%d safe=%lld (mask count %lld) argmax_ucb=(%lld, %.4f) frontier=%zu subgoal kind=%d cell=%d "
+                "raw (%.3f, %.3f) -> published (%.3f, %.3f) dist %.3f kernel=%d posterior %.3f ms total %.3f ms\n",
                 step, out.n_obs, (long long)out.safe_count, count, (long long)out.argmax_ucb.idx, out.argmax_ucb.value,
-                frontier.size(), cell, cell >= 0 ? (cell % W) * rx : NAN, cell >= 0 ? (cell / W) * ry : NAN,
-                out.kernel_used, out.ms_posterior, out.ms_total);
+                frontier.size(), kind, cell, cell >= 0 ? (cell % W) * rx : NAN, cell >= 0 ? (cell / W) * ry : NAN,
+                subgoal[0], subgoal[1], pdist, out.kernel_used, out.ms_posterior, out.ms_total);
     if (count != out.safe_count) { std::fprintf(stderr, "mask / safe_count mismatch\n"); return 3; }
-    if (frontier.empty() != (cell < 0)) { std::fprintf(stderr, "subgoal sentinel mismatch\n"); return 3; }
+    if (step != 2 && frontier.empty() != (cell < 0)) { std::fprintf(stderr, "subgoal sentinel mismatch\n"); return 3; }
   }
   sbo_destroy(ctx);
   std::printf("host_example OK\n");

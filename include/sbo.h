@@ -215,6 +215,49 @@ int32_t sbo_copy_mu_f64(sbo_ctx* ctx, double* host_dst);
 int32_t sbo_copy_sigma2_f64(sbo_ctx* ctx, double* host_dst);
 int32_t sbo_copy_mask(sbo_ctx* ctx, uint8_t* host_dst);
 
+/* ---- N3: from the chosen cell to the published subgoal (host arithmetic) --- */
+
+/* bg::within(goal_point, eroded_concave_polygon_) of reference src/safe_bayesian_optimization_node.cpp:657
+ * (Boost.Geometry winding strategy: boundary points are not within; inside or on a hole is not within).
+ * rings_xy = the rings' vertices back to back as (x, y) pairs, ring_sizes[0] = outer ring, the rest holes;
+ * either orientation; an open ring gets its closing segment.  n_rings = 0: the empty polygon. */
+int32_t sbo_point_within_polygon(const double* rings_xy, const int32_t* ring_sizes, int32_t n_rings,
+                                 double px, double py, int32_t* within);
+/* polydist(polygon, point) of reference src/libraries/polygeom_lib.cpp:400-474 as the node calls it (:677-691:
+ * outer ring copied, bg::correct to closed + counter-clockwise).  As written there it returns the nearest
+ * VERTEX (its rolled vertex list equals the list, :437), first minimum in corrected order; this restates the
+ * same arithmetic.  nv = 0: dist 1e8, point (0, 0) (:419-423). */
+int32_t sbo_polydist(const double* ring_xy, int32_t nv, double px, double py, double* proj_xy, double* dist);
+
+typedef enum {
+  SBO_SUBGOAL_NONE = 0,       /* goal outside the polygon and no frontier: "No valid subgoal found" (:700-703) */
+  SBO_SUBGOAL_GOAL = 1,       /* goal within the polygon: the goal itself (:657-666) */
+  SBO_SUBGOAL_PROJECTED = 2   /* frontier cell of GetNextSubgoal, projected with polydist (:667-699) */
+} sbo_subgoal_kind;
+/* Reference :650-706 in one call.  cell (may be NULL) = the frontier cell used, -1 otherwise; dist (may be NULL)
+ * = polydist's distance. */
+int32_t sbo_subgoal_point(sbo_ctx* ctx, const int32_t* frontier, int64_t F, double goal_x, double goal_y,
+                          const double* rings_xy, const int32_t* ring_sizes, int32_t n_rings,
+                          double* subgoal_xy, int32_t* cell, int32_t* kind, double* dist);
+
+/* ---- N4: observation ingestion --------------------------------------------- */
+
+/* One SpatialMeasurement as the publisher fills it (reference src/turtlesim_spatial_publisher.py:137-145):
+ * position, value, uncertainty, stamp (unit / source_name strings are not needed by the GP). */
+typedef struct {
+  double x, y, z;
+  double value;
+  double uncertainty;        /* carried, not used: the noise level is a hyper-parameter (config/lpsc.yaml:37) */
+  int32_t stamp_sec;
+  uint32_t stamp_nanosec;
+} sbo_measurement;
+/* Feed `count` measurements: rank-k append, or a full re-sorted refit when there are no observations yet or the
+ * appended tail would exceed max(64, n_at_last_fit / 4).  spatial_data_size (may be NULL) = the observation count
+ * afterwards -- the number whose change triggers a step in the node (:552-566); refitted (may be NULL) = 1 when
+ * the full fit ran.  On error nothing is ingested. */
+int32_t sbo_ingest_measurements(sbo_ctx* ctx, const sbo_measurement* recs, int32_t count,
+                                int32_t* spatial_data_size, int32_t* refitted);
+
 /* ---- device-resident variants (bench / pipelines that keep data in HBM) -- */
 
 /* Step with no host traffic: results stay on the device; `out` is filled

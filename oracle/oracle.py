@@ -294,3 +294,75 @@ def compact_cells(mask, grid: Grid, border=False):
                 full &= p[dy:dy + grid.H, dx:dx + grid.W]
         s = s & ~full
     return np.flatnonzero(s.reshape(-1)).astype(np.int32)
+
+
+# ---- N3: goal-in-polygon and polydist (host arithmetic of the reference, restated independently) ----
+
+def point_within_polygon(rings, p):
+    """bg::within(point, polygon) (reference src/safe_bayesian_optimization_node.cpp:657): strictly inside the outer
+    ring and strictly outside every hole.  Even-odd ray casting plus an explicit on-boundary test -- a different
+    algorithm from the library's winding count, on purpose."""
+    def on_segment(a, b, q):
+        cross = (b[0] - a[0]) * (q[1] - a[1]) - (b[1] - a[1]) * (q[0] - a[0])
+        scale = max(1.0, abs(b[0] - a[0]), abs(b[1] - a[1]), abs(q[0] - a[0]), abs(q[1] - a[1]))
+        if abs(cross) > np.finfo(np.float64).eps * scale:
+            return False
+        return min(a[0], b[0]) <= q[0] <= max(a[0], b[0]) and min(a[1], b[1]) <= q[1] <= max(a[1], b[1])
+
+    def ring_state(r, q):          # -1 outside, 0 boundary, 1 inside
+        r = [tuple(map(float, v)) for v in r]
+        if len(r) < 3:
+            return -1
+        if r[0] != r[-1]:
+            r = r + [r[0]]
+        inside = False
+        for a, b in zip(r[:-1], r[1:]):
+            if on_segment(a, b, q):
+                return 0
+            if (a[1] > q[1]) != (b[1] > q[1]):
+                xi = a[0] + (q[1] - a[1]) * (b[0] - a[0]) / (b[1] - a[1])
+                if xi > q[0]:
+                    inside = not inside
+        return 1 if inside else -1
+
+    q = (float(p[0]), float(p[1]))
+    if len(rings) == 0 or ring_state(rings[0], q) != 1:
+        return False
+    return all(ring_state(h, q) == -1 for h in rings[1:])
+
+
+def polydist(ring, p):
+    """polydist (reference src/libraries/polygeom_lib.cpp:400-474) after the node's bg::correct on a closed,
+    counter-clockwise polygon type (node :677-683, include/polygeom_lib.h:60).  Line-by-line restatement, including
+    VertexListRolled[j] = VertexList[j] (:437), which makes the result the nearest vertex.  Returns ((x, y), dist)."""
+    import math
+    V = [[float(v[0]), float(v[1])] for v in ring]
+    if len(V) == 0:
+        return (0.0, 0.0), 100000000.0                                      # :419-423
+    if len(V) > 2 and V[0] != V[-1]:                                        # bg::correct: close ...
+        V.append(list(V[0]))
+    area2 = sum(V[i][0] * V[i + 1][1] - V[i + 1][0] * V[i][1] for i in range(len(V) - 1))
+    if area2 < 0.0:                                                         # ... and make counter-clockwise
+        V.reverse()
+    V.pop()                                                                 # :427
+    n = len(V)
+    if n == 0:
+        return (0.0, 0.0), 100000000.0
+    rolled = [[0.0, 0.0] for _ in range(n)]; dxy = [[0.0, 0.0] for _ in range(n)]; norm = [0.0] * n
+    for i in range(n):                                                      # :433-443
+        j = (i + 1) % n
+        rolled[j] = [V[j][0], V[j][1]]
+        dxy[j] = [V[j][0] - V[i][0], V[j][1] - V[i][1]]
+        norm[j] = math.sqrt(dxy[j][0] * dxy[j][0] + dxy[j][1] * dxy[j][1])
+        if norm[j] == 0.0:
+            norm[j] = 1.0
+    dtemp = []; ctemp = []
+    for i in range(n):                                                      # :449-459
+        n2 = norm[i] ** 2
+        w_temp = (p[0] - V[i][0]) * (dxy[i][0] / n2) + (p[1] - V[i][1]) * (dxy[i][1] / n2)
+        w = max(min(w_temp, 1.0), 0.0)
+        c = [(1 - w) * V[i][0] + w * rolled[i][0], (1 - w) * V[i][1] + w * rolled[i][1]]
+        ctemp.append(c)
+        dtemp.append(math.sqrt((p[0] - c[0]) ** 2 + (p[1] - c[1]) ** 2))
+    k = min(range(n), key=lambda i: (dtemp[i], i))                          # std::min_element: first minimum
+    return (ctemp[k][0], ctemp[k][1]), dtemp[k]

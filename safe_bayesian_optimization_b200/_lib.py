@@ -39,6 +39,13 @@ class SboStepOut(C.Structure):
                 ("ms_comm", C.c_float), ("ms_total", C.c_float)]
 
 
+class SboMeasurement(C.Structure):
+    _fields_ = [("x", C.c_double), ("y", C.c_double), ("z", C.c_double), ("value", C.c_double),
+                ("uncertainty", C.c_double), ("stamp_sec", C.c_int32), ("stamp_nanosec", C.c_uint32)]
+
+
+SBO_SUBGOAL_NONE, SBO_SUBGOAL_GOAL, SBO_SUBGOAL_PROJECTED = 0, 1, 2
+
 # every symbol include/sbo.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
 _D = C.POINTER(C.c_double)
@@ -68,6 +75,14 @@ SYMBOLS = {
     "sbo_frontier_pixel_maps": (C.c_int32, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "sbo_frontier_image": (C.c_int32, [_P, _U8, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "sbo_compact_cells": (C.c_int32, [_P, C.c_int32, C.POINTER(C.c_int32), C.c_int64, C.POINTER(C.c_int64)]),
+    "sbo_point_within_polygon": (C.c_int32, [_D, C.POINTER(C.c_int32), C.c_int32, C.c_double, C.c_double,
+                                             C.POINTER(C.c_int32)]),
+    "sbo_polydist": (C.c_int32, [_D, C.c_int32, C.c_double, C.c_double, _D, _D]),
+    "sbo_subgoal_point": (C.c_int32, [_P, C.POINTER(C.c_int32), C.c_int64, C.c_double, C.c_double, _D,
+                                      C.POINTER(C.c_int32), C.c_int32, _D, C.POINTER(C.c_int32),
+                                      C.POINTER(C.c_int32), _D]),
+    "sbo_ingest_measurements": (C.c_int32, [_P, C.POINTER(SboMeasurement), C.c_int32, C.POINTER(C.c_int32),
+                                            C.POINTER(C.c_int32)]),
     "sbo_tc_plan": (C.c_int32, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double)]),
     "sbo_copy_mu": (C.c_int32, [_P, _P]),
     "sbo_copy_sigma2": (C.c_int32, [_P, _P]),

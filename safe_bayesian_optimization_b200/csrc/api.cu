@@ -357,11 +357,19 @@ int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, in
   ctx->posterior_valid = false;
   ctx->h_xy_sorted.swap(sxy);
   ctx->tc_skip_plan = -1;
+  if (xy != ctx->h_xy_arrival.data()) {   // (the ingestion path refits from these very vectors)
+    ctx->h_xy_arrival.assign(xy, xy + 2 * (size_t)n);
+    ctx->h_y_arrival.assign(y, y + (size_t)n);
+  }
+  ctx->n_at_fit = n;
   const int32_t st = factor_full(ctx);
   if (st != SBO_OK) {
     ctx->n = 0;  // the factor buffers were overwritten: no observations until the next successful fit
     ctx->order.clear();
     ctx->h_xy_sorted.clear();
+    ctx->h_xy_arrival.clear();
+    ctx->h_y_arrival.clear();
+    ctx->n_at_fit = 0;
     cudaMemsetAsync(ctx->d_Linv, 0, sizeof(double) * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
     cudaMemsetAsync(ctx->d_alpha, 0, sizeof(double) * (size_t)ctx->n_cap, ctx->stream);
     if (ctx->d_planes) cudaMemsetAsync(ctx->d_planes, 0, sizeof(uint16_t) * 2 * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
@@ -392,11 +400,81 @@ int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y,
     SBO_TRY(factor_append(ctx, kk));  // on failure n is unchanged: rows >= n of L^-1 are not part of the state
     for (int i = 0; i < kk; ++i) ctx->order.push_back(n + i);
     ctx->h_xy_sorted.insert(ctx->h_xy_sorted.end(), xy + 2 * (size_t)done, xy + 2 * (size_t)(done + kk));
+    ctx->h_xy_arrival.insert(ctx->h_xy_arrival.end(), xy + 2 * (size_t)done, xy + 2 * (size_t)(done + kk));
+    ctx->h_y_arrival.insert(ctx->h_y_arrival.end(), y + done, y + done + kk);
     ctx->n = n + kk;
     if (ctx->tc_skip_plan == 0) ctx->tc_skip_plan = -1;  // a decision to skip survives appends; a decision not to is re-examined
     done += kk;
   }
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return SBO_OK;
+}
+
+// N4 -- observation ingestion.  One record per SpatialMeasurement message as the publisher fills it
+// (reference src/turtlesim_spatial_publisher.py:137-145).  The GP's noise level is a hyper-parameter (lpsc.yaml:37),
+// so `uncertainty` is carried but not used; z and the stamp likewise.  The count returned is what the mapping node
+// publishes as spatial_data_size and what triggers a step in the optimiser node when it changes (:552-566).
+int32_t sbo_ingest_measurements(sbo_ctx* ctx, const sbo_measurement* recs, int32_t count, int32_t* spatial_data_size,
+                                int32_t* refitted) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (refitted) *refitted = 0;
+  if (spatial_data_size) *spatial_data_size = ctx->n;
+  if (count < 0 || (count > 0 && !recs)) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_ingest_measurements: null input or count < 0");
+  if (count == 0) return SBO_OK;
+  if ((int64_t)ctx->n + count > ctx->cfg.max_obs) return fail(ctx, SBO_ERR_CAPACITY, "sbo_ingest_measurements: n + count exceeds max_obs");
+  std::vector<double> xy(2 * (size_t)count), y((size_t)count);
+  for (int i = 0; i < count; ++i) {
+    xy[2 * i] = recs[i].x; xy[2 * i + 1] = recs[i].y; y[i] = recs[i].value;
+  }
+  if (!all_finite(xy.data(), xy.size()) || !all_finite(y.data(), y.size()))
+    return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_ingest_measurements: NaN/Inf in a measurement");
+  // Appended observations sit behind the spatially ordered ones: fine for a few, but the chunk boxes of the
+  // tcgen05 kernel (and its rounding behaviour) want the spatial order back once the tail is long.  Refit from
+  // all observations, re-sorted, when the tail would exceed a quarter of the last full fit (at least 64).
+  const int64_t tail = (int64_t)ctx->n - ctx->n_at_fit + count;
+  const bool refit = ctx->n == 0 || tail > std::max<int64_t>(64, ctx->n_at_fit / 4);
+  int32_t st;
+  if (refit) {
+    ctx->h_xy_arrival.insert(ctx->h_xy_arrival.end(), xy.begin(), xy.end());
+    ctx->h_y_arrival.insert(ctx->h_y_arrival.end(), y.begin(), y.end());
+    const int32_t n_all = (int32_t)ctx->h_y_arrival.size();
+    st = sbo_set_observations(ctx, ctx->h_xy_arrival.data(), ctx->h_y_arrival.data(), n_all);
+    if (refitted && st == SBO_OK) *refitted = 1;
+  } else {
+    st = sbo_append_observations(ctx, xy.data(), y.data(), count);
+  }
+  if (spatial_data_size) *spatial_data_size = ctx->n;
+  return st;
+}
+
+// N3 -- reference :650-706 in one call: the goal itself when it lies within the (eroded) safe polygon, else the
+// frontier cell chosen by GetNextSubgoal (:508-549, on the GPU), its coordinates (the x_coords / y_coords the
+// reference reads at :671-672 are the grid formula) run through polydist against the polygon's outer ring.
+int32_t sbo_subgoal_point(sbo_ctx* ctx, const int32_t* frontier, int64_t F, double goal_x, double goal_y,
+                          const double* rings_xy, const int32_t* ring_sizes, int32_t n_rings, double* subgoal_xy,
+                          int32_t* cell, int32_t* kind, double* dist) {
+  if (!ctx || !subgoal_xy || !kind) return SBO_ERR_INVALID_ARG;
+  *kind = SBO_SUBGOAL_NONE;
+  if (cell) *cell = -1;
+  if (dist) *dist = 0.0;
+  int32_t within = 0;
+  const int32_t st = sbo_point_within_polygon(rings_xy, ring_sizes, n_rings, goal_x, goal_y, &within);
+  if (st != SBO_OK) return fail(ctx, st, "sbo_subgoal_point: bad polygon arguments");
+  if (within) {
+    subgoal_xy[0] = goal_x; subgoal_xy[1] = goal_y;
+    *kind = SBO_SUBGOAL_GOAL;
+    return SBO_OK;
+  }
+  int32_t c = -1;
+  SBO_TRY(sbo_select_subgoal(ctx, frontier, F, goal_x, goal_y, &c));
+  if (c < 0) return SBO_OK;   // "No valid subgoal found" (:700-703)
+  const int iy = c / ctx->W, ix = c - iy * ctx->W;
+  const double raw_x = ctx->x0 + (double)ix * ctx->rx, raw_y = ctx->y0 + (double)iy * ctx->ry;
+  double d = 0.0;
+  SBO_TRY(sbo_polydist(rings_xy, n_rings > 0 ? ring_sizes[0] : 0, raw_x, raw_y, subgoal_xy, &d));
+  if (cell) *cell = c;
+  if (dist) *dist = d;
+  *kind = SBO_SUBGOAL_PROJECTED;
   return SBO_OK;
 }
 

@@ -69,6 +69,8 @@ struct sbo_ctx {
   int shift_a = 0, shift_b = 0;  // power-of-two scales of the K* and L^-1 planes (tc_plane_shifts)
   int tc_cg = 2;                 // CTAs per tcgen05.mma group (2 = CTA pair, 1 = single CTA)
   bool tc_skip = true;           // leave out K* chunks that are < 2^-44 sigma_f^2 for a whole cell tile
+  std::vector<double> h_xy_arrival, h_y_arrival;   // every observation in arrival order (ingestion refits from these)
+  int n_at_fit = 0;              // observations at the last full factorisation
   double tc_kept_frac = 1.0;     // planner's estimate: share of (row block, chunk) visits that survive the box test
   int tc_skip_plan = -1;         // cached decision of tc_plan_skip for this grid + observation set (-1: stale)
   std::vector<double> h_xy_sorted;  // host copy of d_xy (internal order), for the skip planner

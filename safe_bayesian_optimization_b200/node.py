@@ -161,3 +161,35 @@ class OptimizerCore:
             log.warning("No frontier points found")   # :503-506
             return -1
         return self.ctx.select_subgoal(frontier, self.current_goal_)
+
+    # -- the tail of process_terrain_map (:650-706): goal or projected frontier subgoal ---------------
+    def ComputeSubgoal(self, eroded_polygon_rings):
+        """eroded_polygon_rings = [outer ring, holes...] of ``eroded_concave_polygon_`` (the alpha-shape / erosion
+        stage stays with the host's CGAL/Boost).  Returns (x, y) or None ("No valid subgoal found", :700-703)."""
+        from . import _lib as L
+        frontier = np.zeros(0, dtype=np.int32)
+        from .optimizer import point_within_polygon
+        if not point_within_polygon(eroded_polygon_rings, self.current_goal_):
+            frontier = self.FindSafetyContourIndices()      # only needed when the goal is not safe (:667)
+        kind, xy, cell, dist = self.ctx.subgoal_point(frontier, self.current_goal_, eroded_polygon_rings)
+        if kind == L.SBO_SUBGOAL_NONE:
+            log.warning("No valid subgoal found")
+            return None
+        if kind == L.SBO_SUBGOAL_GOAL:
+            log.info("Goal is within eroded safe region, using goal as subgoal: (%f, %f)", *xy)
+        else:
+            log.info("Projected subgoal point: (%f, %f), distance: %f", xy[0], xy[1], dist)
+        return xy
+
+    # -- SpatialMeasurement ingestion + the spatial_data_size trigger (:552-566) -----------------------
+    def spatial_measurement_callback(self, x, y, value, uncertainty=0.0):
+        size, _ = self.ctx.ingest([[x, y]], [value], [uncertainty])
+        return self.spatial_data_size_callback(size)
+
+    def spatial_data_size_callback(self, current_size) -> bool:
+        """True when the size changed, i.e. when the reference requests a new terrain map (= runs a step)."""
+        if current_size != getattr(self, "last_spatial_data_size_", 0):
+            log.info("Spatial data size changed: %d -> %d", getattr(self, "last_spatial_data_size_", 0), current_size)
+            self.last_spatial_data_size_ = current_size
+            return True
+        return False

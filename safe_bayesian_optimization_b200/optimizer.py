@@ -52,6 +52,36 @@ def _u8ptr(a):
     return a.ctypes.data_as(C.POINTER(C.c_uint8))
 
 
+def _pack_rings(rings):
+    rings = [np.ascontiguousarray(r, dtype=np.float64).reshape(-1, 2) for r in rings]
+    sizes = np.array([r.shape[0] for r in rings], dtype=np.int32)
+    xy = np.ascontiguousarray(np.concatenate(rings, axis=0)) if rings else np.zeros((0, 2))
+    return xy, sizes
+
+
+def point_within_polygon(rings, p) -> bool:
+    """bg::within(point, polygon) of reference :657 (host arithmetic in libsbo.so, no GPU involved)."""
+    lib = L.load()
+    xy, sizes = _pack_rings(rings)
+    w = C.c_int32(0)
+    st = lib.sbo_point_within_polygon(_dptr(xy), sizes.ctypes.data_as(C.POINTER(C.c_int32)), sizes.size,
+                                      float(p[0]), float(p[1]), C.byref(w))
+    if st != L.SBO_OK:
+        raise ValueError(f"sbo_point_within_polygon: status {st}")
+    return bool(w.value)
+
+
+def polydist(ring, p):
+    """polydist of reference polygeom_lib.cpp:400-474 as the node calls it: ((x, y), dist)."""
+    lib = L.load()
+    ring = np.ascontiguousarray(ring, dtype=np.float64).reshape(-1, 2)
+    out, d = np.zeros(2), C.c_double(0.0)
+    st = lib.sbo_polydist(_dptr(ring), ring.shape[0], float(p[0]), float(p[1]), _dptr(out), C.byref(d))
+    if st != L.SBO_OK:
+        raise ValueError(f"sbo_polydist: status {st}")
+    return (float(out[0]), float(out[1])), float(d.value)
+
+
 class SboContext:
     """Owns one ``sbo_ctx`` (one GPU, one shard of grid rows)."""
 
@@ -190,6 +220,32 @@ class SboContext:
         self._check(self.lib.sbo_select_subgoal(self._h, fr.ctypes.data_as(C.POINTER(C.c_int32)), fr.size,
                                                 float(goal_xy[0]), float(goal_xy[1]), C.byref(cell)))
         return int(cell.value)
+
+    def subgoal_point(self, frontier, goal_xy, rings):
+        """Reference :650-706: (kind, (x, y), cell, dist).  rings = [outer, hole, ...] as (k, 2) arrays."""
+        fr = np.ascontiguousarray(frontier, dtype=np.int32).reshape(-1)
+        xy, sizes = _pack_rings(rings)
+        out = np.zeros(2)
+        cell, kind, dist = C.c_int32(-1), C.c_int32(0), C.c_double(0.0)
+        self._check(self.lib.sbo_subgoal_point(self._h, fr.ctypes.data_as(C.POINTER(C.c_int32)), fr.size,
+                                               float(goal_xy[0]), float(goal_xy[1]), _dptr(xy),
+                                               sizes.ctypes.data_as(C.POINTER(C.c_int32)), sizes.size, _dptr(out),
+                                               C.byref(cell), C.byref(kind), C.byref(dist)))
+        return kind.value, (float(out[0]), float(out[1])), int(cell.value), float(dist.value)
+
+    def ingest(self, xy, values, uncertainty=None, stamps=None):
+        """Feed SpatialMeasurement records (position x/y, value); returns (spatial_data_size, refitted)."""
+        xy = np.asarray(xy, dtype=np.float64).reshape(-1, 2)
+        values = np.asarray(values, dtype=np.float64).reshape(-1)
+        recs = (L.SboMeasurement * len(values))()
+        for i in range(len(values)):
+            recs[i].x, recs[i].y, recs[i].z, recs[i].value = xy[i, 0], xy[i, 1], 0.0, values[i]
+            recs[i].uncertainty = 0.0 if uncertainty is None else float(uncertainty[i])
+            if stamps is not None:
+                recs[i].stamp_sec, recs[i].stamp_nanosec = int(stamps[i][0]), int(stamps[i][1])
+        size, refit = C.c_int32(0), C.c_int32(0)
+        self._check(self.lib.sbo_ingest_measurements(self._h, recs, len(values), C.byref(size), C.byref(refit)))
+        return int(size.value), bool(refit.value)
 
     # -- read-back ----------------------------------------------------------
     def tc_plan(self):
