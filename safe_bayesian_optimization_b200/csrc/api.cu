@@ -55,8 +55,12 @@ void free_all(sbo_ctx* c) {
 
 // Which posterior kernel runs for this context.
 int32_t pick_kernel(sbo_ctx* ctx, int* which) {
-  if (ctx->cfg.precision == SBO_FP64 || ctx->cfg.kernel == SBO_KERNEL_SIMT) {
+  if (ctx->cfg.kernel == SBO_KERNEL_SIMT) {
     *which = SBO_KERNEL_SIMT;
+    return SBO_OK;
+  }
+  if (ctx->cfg.precision == SBO_FP64) {
+    *which = SBO_KERNEL_DMMA;
     return SBO_OK;
   }
   if (!ctx->tc_ok)
@@ -106,6 +110,8 @@ int32_t run_step(sbo_ctx* ctx, double beta, double f_min, bool incremental, int*
     which = SBO_KERNEL_THIN;
   } else if (which == SBO_KERNEL_TCGEN05) {
     SBO_TRY(launch_posterior_tc(ctx, j_lo, j_hi, accumulate));
+  } else if (which == SBO_KERNEL_DMMA) {
+    SBO_TRY(launch_posterior_f64(ctx, j_lo, j_hi, accumulate));
   } else {
     SBO_TRY(launch_posterior_simt(ctx, j_lo, j_hi, accumulate));
   }

@@ -174,6 +174,7 @@ bool tc_plan_skip(sbo_ctx* ctx);                   // worth walking chunk masks 
 int32_t tc_pack_observations(sbo_ctx* ctx);       // d_xy -> d_obs_f32 (scaled fp32 hi/lo pairs)
 
 // posterior_thin.cu
+int32_t launch_posterior_f64(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);   // fp64 mode, DMMA
 int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo);   // incremental step, n - row_lo <= kThinMaxRows
 
 // frontier.cu

@@ -1,0 +1,264 @@
+// posterior_f64.cu -- GP posterior over the cells of this shard in fp64 mode (BASELINE config C5, and C1):
+//   mu(x*)      = prior_mean + k*^T alpha
+//   sigma^2(x*) = sigma_f^2 - | L^-1 k* |^2
+// tcgen05 has no fp64 kind; the fp64 tensor path of sm_100a is mma.sync m8n8k4 (DMMA), which runs at the same
+// 37 TFLOP/s as DFMA on this part (scripts/probe/fp64_peak.cu) but needs one instruction per 256 FMAs instead
+// of eight, so the issue slots, the register file and the fp64 pipe stay free for the fragment loads and the
+// K* generation.  (The register-tile DFMA kernel in posterior_simt.cu reaches 14.5 TFLOP/s credited; it stays as
+// the cross-check, kernel = SBO_KERNEL_SIMT.)
+//
+// Tile = a patch of 16 columns x 8 rows of cells (128 cells) x 128 rows j of L^-1, 16 observations per stage,
+// 256 threads = 8 warps as 2 (cells) x 4 (rows j), warp tile 64 x 32 = 8 x 4 DMMA tiles, 64 fp64 accumulators
+// per thread.  The patch shape is what makes K* cheap: the RBF kernel on a grid is separable,
+//   k*(cell(ix, iy), x_k) = ex[ix][k] * (sigma_f^2 ey[iy][k]),
+// so a stage needs 16 x 16 + 8 x 16 exponentials for its 2048 entries instead of 2048.  Software pipeline, one
+// __syncthreads per stage: while the DMMAs of stage s run, the L^-1 slab of stage s+1 arrives by cp.async (rows of
+// L^-1 are K-contiguous: a straight copy, zero-filled above the diagonal and outside [j_lo, j_hi)), the K* slab of
+// stage s+1 is formed from the factor tables of stage s+1, and the factor tables of stage s+2 are computed.
+// Shared-memory rows are padded to 20 doubles: the (row = lane / 4, k = lane % 4) fragment reads of a half-warp
+// then cover all 32 banks once.  Row block jb walks k < 128 (jb + 1) only (L^-1 is lower triangular); when it is
+// finished the accumulators are squared and row-summed in registers, V itself never leaves them.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace sbo {
+namespace {
+
+constexpr int FT = 256;            // threads
+constexpr int PC = 16, PR = 8;     // patch of cells: columns x rows
+constexpr int FM = PC * PR;        // 128 cells per tile
+constexpr int FN = 128;            // rows of L^-1 per row block
+constexpr int FK = 16;             // observations per stage
+constexpr int LD = 20;             // padded stage row (doubles)
+
+struct F64Params {
+  const double* xy;     // [n][2]
+  const double* Linv;   // [n_cap][ld]
+  const double* alpha;  // [n]
+  int n, ld;
+  int j_lo, j_hi;       // rows of L^-1 to contract
+  int accumulate;       // 1: sigma^2 -= |rows|^2 on top of the stored value, mu refreshed
+  double x0, y0, rx, ry;
+  int W, rows_local, row0;
+  double sf2, inv2l2, prior_mean;
+};
+
+struct F64Smem {
+  double A[2][FM * LD];      // K* stage, A[cell][k]
+  double B[2][FN * LD];      // L^-1 stage, B[j][k]
+  double ex[3][FK][PC];      // x factors of a stage
+  double ey[3][FK][PR];      // sigma_f^2 * y factors; 0 beyond n and below the last grid row
+  double al[3][FK];          // alpha; 0 beyond n
+  double red[4][FM];         // row sums of the four warp columns
+  double mu_part[2][FM];
+};
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, int src_bytes) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gmem_src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+__device__ __forceinline__ void dmma(double (&c)[2], double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c[0]), "+d"(c[1])
+               : "d"(a), "d"(b));
+}
+
+// (row block, first observation) of a stage; row block jb walks k0 = 0, 16, .. < kd(jb)
+struct Cursor {
+  int jb, k0;
+};
+
+__global__ void __launch_bounds__(FT, 1)
+posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restrict__ s2_out) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  F64Smem& sm = *reinterpret_cast<F64Smem*>(smem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int wm = warp >> 2, wn = warp & 3;      // warp tile: cells [64 wm, +64) x rows j [32 wn, +32)
+  const int g = lane >> 2, t = lane & 3;        // DMMA fragment coordinates
+  const int tiles_x = (p.W + PC - 1) / PC, tiles_y = (p.rows_local + PR - 1) / PR;
+  const long long ntiles = (long long)tiles_x * tiles_y;
+  const int n_pad = (p.n + FK - 1) / FK * FK;
+  const int jb_lo = p.j_lo / FN, jb_hi = (p.j_hi + FN - 1) / FN;   // row blocks [jb_lo, jb_hi)
+  auto kd = [&](int jb) { return min(n_pad, (jb + 1) * FN); };
+  auto advance = [&](Cursor& c) {
+    c.k0 += FK;
+    if (c.k0 >= kd(c.jb)) { c.jb += 1; c.k0 = 0; }
+  };
+
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int col0 = (int)(tile % tiles_x) * PC, r0 = (int)(tile / tiles_x) * PR;
+
+    // ---- per-stage producers -------------------------------------------------------------------------
+    auto make_tables = [&](int k0, int tb) {   // factor tables of the stage that starts at observation k0
+      {
+        const int kk = tid >> 4, pc = tid & 15, k = k0 + kk;
+        double v = 0.0;
+        if (k < p.n) {
+          const double dx = cell_coord(p.x0, p.rx, col0 + pc) - p.xy[2 * (size_t)k];
+          v = exp(-dx * dx * p.inv2l2);
+        }
+        sm.ex[tb][kk][pc] = v;
+      }
+      if (tid < FK * PR) {
+        const int kk = tid >> 3, pr = tid & 7, k = k0 + kk;
+        double v = 0.0;
+        if (k < p.n && r0 + pr < p.rows_local) {
+          const double dy = cell_coord(p.y0, p.ry, p.row0 + r0 + pr) - p.xy[2 * (size_t)k + 1];
+          v = p.sf2 * exp(-dy * dy * p.inv2l2);
+        }
+        sm.ey[tb][kk][pr] = v;
+      } else if (tid < FK * PR + FK) {
+        const int kk = tid - FK * PR, k = k0 + kk;
+        sm.al[tb][kk] = k < p.n ? p.alpha[k] : 0.0;
+      }
+    };
+    double mu_acc = 0.0;
+    auto make_a = [&](int tb, int buf, bool with_mu) {   // K* stage from its tables: thread = (cell, half of the 16 k)
+      const int c = tid >> 1, h = tid & 1, pc = c & 15, pr = c >> 4;
+      double v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = sm.ex[tb][h * 8 + i][pc] * sm.ey[tb][h * 8 + i][pr];
+      if (with_mu) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) mu_acc = fma(v[i], sm.al[tb][h * 8 + i], mu_acc);
+      }
+      double2* dst = reinterpret_cast<double2*>(&sm.A[buf][c * LD + h * 8]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) dst[i] = make_double2(v[2 * i], v[2 * i + 1]);
+    };
+    auto load_b = [&](Cursor cur, int buf) {   // 128 rows x 16 k of L^-1: 1024 granules of two doubles
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int gi = q * FT + tid, r = gi >> 3, kq = (gi & 7) * 2;
+        const int j = cur.jb * FN + r, k = cur.k0 + kq;
+        const bool live = j >= p.j_lo && j < p.j_hi && k <= j;
+        const double* src = p.Linv + (size_t)(live ? j : 0) * p.ld + (live ? k : 0);
+        cp_async16(&sm.B[buf][r * LD + kq], src, live ? 16 : 0);
+      }
+    };
+
+    double rs[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) rs[i] = 0.0;
+
+    if (jb_hi > jb_lo) {
+      double acc[8][4][2];
+#pragma unroll
+      for (int mi = 0; mi < 8; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+
+      // ---- prologue: tables of stages 0 and 1, K* and L^-1 of stage 0 ----
+      Cursor cur{jb_lo, 0};                       // stage being contracted
+      Cursor nxt = cur; advance(nxt);             // stage being staged
+      Cursor nx2 = nxt; if (nxt.jb < jb_hi) advance(nx2);
+      make_tables(cur.k0, 0);
+      if (nxt.jb < jb_hi) make_tables(nxt.k0, 1);
+      load_b(cur, 0);
+      __syncthreads();
+      make_a(0, 0, cur.jb == jb_hi - 1);
+      cp_async_wait_all();
+      __syncthreads();
+
+      int s = 0;   // stage counter: A/B buffer s & 1, table buffer s % 3
+      while (cur.jb < jb_hi) {
+        const bool have_next = nxt.jb < jb_hi;
+        if (have_next) {
+          load_b(nxt, (s + 1) & 1);
+          if (nx2.jb < jb_hi) make_tables(nx2.k0, (s + 2) % 3);
+          make_a((s + 1) % 3, (s + 1) & 1, nxt.jb == jb_hi - 1);
+        }
+        // ---- contract stage s: 4 k-steps of 8 x 4 DMMA tiles ----
+        const double* As = &sm.A[s & 1][(wm * 64 + g) * LD + t];
+        const double* Bs = &sm.B[s & 1][(wn * 32 + g) * LD + t];
+#pragma unroll
+        for (int k4 = 0; k4 < FK / 4; ++k4) {
+          double a[8], b[4];
+#pragma unroll
+          for (int mi = 0; mi < 8; ++mi) a[mi] = As[mi * 8 * LD + k4 * 4];
+#pragma unroll
+          for (int ni = 0; ni < 4; ++ni) b[ni] = Bs[ni * 8 * LD + k4 * 4];
+#pragma unroll
+          for (int mi = 0; mi < 8; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) dmma(acc[mi][ni], a[mi], b[ni]);
+        }
+        // ---- end of a row block: squared row sums of this 128 x 128 block of V ----
+        if (cur.k0 + FK >= kd(cur.jb)) {
+#pragma unroll
+          for (int mi = 0; mi < 8; ++mi) {
+            double q = 0.0;
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) {
+              q = fma(acc[mi][ni][0], acc[mi][ni][0], q);
+              q = fma(acc[mi][ni][1], acc[mi][ni][1], q);
+              acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+            }
+            rs[mi] += q;
+          }
+        }
+        cp_async_wait_all();
+        __syncthreads();
+        cur = nxt; nxt = nx2;
+        if (nx2.jb < jb_hi) advance(nx2);
+        ++s;
+      }
+    }
+
+    // ---- finish the tile: reduce over the lanes and warps that share a cell, write mu / sigma^2 ----
+#pragma unroll
+    for (int mi = 0; mi < 8; ++mi) {
+      rs[mi] += __shfl_xor_sync(0xffffffffu, rs[mi], 1);
+      rs[mi] += __shfl_xor_sync(0xffffffffu, rs[mi], 2);
+      if (t == 0) sm.red[wn][wm * 64 + mi * 8 + g] = rs[mi];
+    }
+    sm.mu_part[tid & 1][tid >> 1] = mu_acc;
+    __syncthreads();
+    if (tid < FM) {
+      const int pc = tid & 15, pr = tid >> 4;
+      const int col = col0 + pc, lrow = r0 + pr;
+      if (col < p.W && lrow < p.rows_local) {
+        const long long lc = (long long)lrow * p.W + col;
+        const double sq = (sm.red[0][tid] + sm.red[1][tid]) + (sm.red[2][tid] + sm.red[3][tid]);
+        const double prev = p.accumulate ? s2_out[lc] : p.sf2;
+        s2_out[lc] = prev - sq;
+        mu_out[lc] = p.prior_mean + (sm.mu_part[0][tid] + sm.mu_part[1][tid]);
+      }
+    }
+    __syncthreads();   // red / mu_part / stage buffers are reused by the next tile
+  }
+}
+
+}  // namespace
+
+int32_t launch_posterior_f64(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
+  if (ctx->cfg.precision != SBO_FP64) return fail(ctx, SBO_ERR_STATE, "posterior_f64: context is not in fp64 mode");
+  if (ctx->m_local == 0) return SBO_OK;
+  if (accumulate && j_hi <= j_lo) return SBO_OK;   // no new rows: the stored posterior stands
+  F64Params p;
+  p.xy = ctx->d_xy; p.Linv = ctx->d_Linv; p.alpha = ctx->d_alpha;
+  p.n = ctx->n; p.ld = ctx->n_cap;
+  p.j_lo = j_hi > j_lo ? j_lo : 0; p.j_hi = j_hi > j_lo ? j_hi : 0;
+  p.accumulate = accumulate ? 1 : 0;
+  p.x0 = ctx->x0; p.y0 = ctx->y0; p.rx = ctx->rx; p.ry = ctx->ry;
+  p.W = ctx->W; p.rows_local = ctx->row1 - ctx->row0; p.row0 = ctx->row0;
+  p.sf2 = ctx->cfg.sigma_f * ctx->cfg.sigma_f;
+  p.inv2l2 = 1.0 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale);
+  p.prior_mean = ctx->cfg.prior_mean;
+  if (p.ld % 2 != 0) return fail(ctx, SBO_ERR_STATE, "posterior_f64: odd leading dimension of L^-1");
+  static bool attr_set = false;
+  if (!attr_set) {
+    SBO_CUDA(ctx, cudaFuncSetAttribute(posterior_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F64Smem)));
+    attr_set = true;
+  }
+  const long long ntiles = (long long)((p.W + PC - 1) / PC) * ((p.rows_local + PR - 1) / PR);
+  const unsigned grid = (unsigned)std::min<long long>(ntiles, ctx->sm_count);
+  posterior_f64_kernel<<<grid, FT, sizeof(F64Smem), ctx->stream>>>(p, static_cast<double*>(ctx->d_mu), static_cast<double*>(ctx->d_s2));
+  SBO_LAUNCH_CHECK(ctx, "posterior_f64_kernel");
+  return SBO_OK;
+}
+
+}  // namespace sbo

@@ -78,7 +78,7 @@ CASES = [  # (cfg, n, W, H) -- ragged sizes on purpose: n % 32, n % 256, W % 128
 
 
 @pytest.mark.parametrize("cfg,n,W,H", CASES)
-@pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp32", "simt"), ("fp64", "simt")])
+@pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp32", "simt"), ("fp64", "simt"), ("fp64", "auto")])
 def test_step_matches_oracle(pkg, oracle, coracle, cfg, n, W, H, precision, kernel):
     p = S.make_problem(cfg, n=n, W=W, H=H)
     ref = reference(oracle, coracle, p)
@@ -86,14 +86,14 @@ def test_step_matches_oracle(pkg, oracle, coracle, cfg, n, W, H, precision, kern
         ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
         ctx.set_observations(p.xy, p.y)
         res, mask = ctx.step(p.beta, p.f_min)
-        assert res.kernel_used == {"tcgen05": 2, "simt": 1}[kernel] and res.n_obs == n and res.n_cells == p.m
+        assert res.kernel_used == {"tcgen05": 2, "simt": 1, "auto": 4}[kernel] and res.n_obs == n and res.n_cells == p.m
         band = check_step(p, ref, res, mask, ctx.mu(), ctx.sigma2(), precision, label=kernel)
         assert res.safe_count == int((mask == 255).sum())
         check_argmax(res, ref, band, mask)
         assert np.array_equal(ctx.mask(), mask)
 
 
-@pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp64", "simt")])
+@pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp64", "simt"), ("fp64", "auto")])
 @pytest.mark.parametrize("n0,ks", [(300, [1, 16]), (250, [6, 1, 40]), (0, [5]), (700, [1, 2, 3, 8, 9]), (1030, [4, 0, 1])])
 def test_incremental_step_equals_full(pkg, oracle, coracle, precision, kernel, n0, ks):
     """<= 8 new rows take the thin O(m n k) kernel (kernel_used 3), more the row-block kernels; W = 300 is not a
@@ -109,14 +109,14 @@ def test_incremental_step_equals_full(pkg, oracle, coracle, precision, kernel, n
             ctx.append_observations(p.xy[n:n + k], p.y[n:n + k])
             n += k
             res, mask = ctx.step(p.beta, p.f_min, incremental=True)
-            assert res.kernel_used == (3 if k <= 8 else {"tcgen05": 2, "simt": 1}[kernel])
+            assert res.kernel_used == (3 if k <= 8 else {"tcgen05": 2, "simt": 1, "auto": 4}[kernel])
             q = S.make_problem("C3", n=total, W=300, H=21); q.xy, q.y = p.xy[:n], p.y[:n]
             ref = reference(oracle, coracle, q)
             band = check_step(q, ref, res, mask, ctx.mu(), ctx.sigma2(), precision, label=f"incr+{k}")
             check_argmax(res, ref, band, mask)
 
 
-@pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp64", "simt")])
+@pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp64", "simt"), ("fp64", "auto")])
 @pytest.mark.parametrize("world", [2, 3, 8])
 def test_row_band_shards_equal_single(pkg, oracle, coracle, precision, kernel, world):
     """G shards emulated one after the other on one GPU: identical bytes, merged argmax."""
