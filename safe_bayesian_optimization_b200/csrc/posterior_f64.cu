@@ -7,15 +7,15 @@
 // K* generation.  (The register-tile DFMA kernel in posterior_simt.cu reaches 14.5 TFLOP/s credited; it stays as
 // the cross-check, kernel = SBO_KERNEL_SIMT.)
 //
-// Tile = a patch of 16 columns x 8 rows of cells (128 cells) x 128 rows j of L^-1, 16 observations per stage,
-// 256 threads = 8 warps as 2 (cells) x 4 (rows j), warp tile 64 x 32 = 8 x 4 DMMA tiles, 64 fp64 accumulators
+// Tile = a patch of 16 columns x 8 rows of cells (128 cells) x 128 rows j of L^-1, 32 observations per stage,
+// 512 threads = 16 warps as 4 (cells) x 4 (rows j), warp tile 32 x 32 = 4 x 4 DMMA tiles, 32 fp64 accumulators
 // per thread.  The patch shape is what makes K* cheap: the RBF kernel on a grid is separable,
 //   k*(cell(ix, iy), x_k) = ex[ix][k] * (sigma_f^2 ey[iy][k]),
-// so a stage needs 16 x 16 + 8 x 16 exponentials for its 2048 entries instead of 2048.  Software pipeline, one
+// so a stage needs 16 x 32 + 8 x 32 exponentials for its 4096 entries instead of 4096.  Software pipeline, one
 // __syncthreads per stage: while the DMMAs of stage s run, the L^-1 slab of stage s+1 arrives by cp.async (rows of
 // L^-1 are K-contiguous: a straight copy, zero-filled above the diagonal and outside [j_lo, j_hi)), the K* slab of
 // stage s+1 is formed from the factor tables of stage s+1, and the factor tables of stage s+2 are computed.
-// Shared-memory rows are padded to 20 doubles: the (row = lane / 4, k = lane % 4) fragment reads of a half-warp
+// Shared-memory rows are padded to 36 doubles: the (row = lane / 4, k = lane % 4) fragment reads of a half-warp
 // then cover all 32 banks once.  Row block jb walks k < 128 (jb + 1) only (L^-1 is lower triangular); when it is
 // finished the accumulators are squared and row-summed in registers, V itself never leaves them.
 #include <algorithm>
@@ -25,12 +25,16 @@
 namespace sbo {
 namespace {
 
-constexpr int FT = 256;            // threads
+constexpr int FK_ = 32;
+constexpr int FT = 512;            // threads: 16 warps as 4 (cells) x 4 (rows j), warp tile 32 x 32
+constexpr int MI = 4, NI = 4;      // DMMA tiles per warp tile
 constexpr int PC = 16, PR = 8;     // patch of cells: columns x rows
 constexpr int FM = PC * PR;        // 128 cells per tile
+constexpr int NT = FK_ * (PC + PR + 1);   // factor-table entries of a stage: x factors, y factors, alpha
+constexpr int TPT = (NT + FT - 1) / FT;   // ... per thread
 constexpr int FN = 128;            // rows of L^-1 per row block
-constexpr int FK = 16;             // observations per stage
-constexpr int LD = 20;             // padded stage row (doubles)
+constexpr int FK = FK_;            // observations per stage
+constexpr int LD = FK + 4;          // padded stage row (doubles): 2 LD = 8 (mod 32) banks
 
 struct F64Params {
   const double* xy;     // [n][2]
@@ -51,7 +55,7 @@ struct F64Smem {
   double ey[3][FK][PR];      // sigma_f^2 * y factors; 0 beyond n and below the last grid row
   double al[3][FK];          // alpha; 0 beyond n
   double red[4][FM];         // row sums of the four warp columns
-  double mu_part[2][FM];
+  double mu_part[4][FM];
 };
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, int src_bytes) {
@@ -71,12 +75,14 @@ struct Cursor {
   int jb, k0;
 };
 
+static_assert(FT / FM == 4 && FT / 32 == (FM / 32) * (FN / 32) && (FN * FK / 2) % FT == 0 && (2 * LD) % 32 == 8, "thread maps");
+
 __global__ void __launch_bounds__(FT, 1)
 posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restrict__ s2_out) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   F64Smem& sm = *reinterpret_cast<F64Smem*>(smem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int wm = warp >> 2, wn = warp & 3;      // warp tile: cells [64 wm, +64) x rows j [32 wn, +32)
+  const int wm = warp >> 2, wn = warp & 3;      // warp tile: cells [32 wm, +32) x rows j [32 wn, +32)
   const int g = lane >> 2, t = lane & 3;        // DMMA fragment coordinates
   const int tiles_x = (p.W + PC - 1) / PC, tiles_y = (p.rows_local + PR - 1) / PR;
   const long long ntiles = (long long)tiles_x * tiles_y;
@@ -92,47 +98,64 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
     const int col0 = (int)(tile % tiles_x) * PC, r0 = (int)(tile / tiles_x) * PR;
 
     // ---- per-stage producers -------------------------------------------------------------------------
-    auto make_tables = [&](int k0, int tb) {   // factor tables of the stage that starts at observation k0
-      {
-        const int kk = tid >> 4, pc = tid & 15, k = k0 + kk;
-        double v = 0.0;
-        if (k < p.n) {
-          const double dx = cell_coord(p.x0, p.rx, col0 + pc) - p.xy[2 * (size_t)k];
-          v = exp(-dx * dx * p.inv2l2);
+    // factor tables of the stage that starts at observation k0: the global loads are issued by table_load (early
+    // in an iteration), the exponentials and the stores come after the DMMAs (table_store)
+    struct TabIn { double v[TPT]; };
+    auto table_load = [&](int k0) -> TabIn {
+      TabIn o;
+#pragma unroll
+      for (int u = 0; u < TPT; ++u) {
+        const int e = tid + u * FT;
+        o.v[u] = 0.0;
+        if (e < FK * PC) {
+          const int k = k0 + (e >> 4);
+          if (k < p.n) o.v[u] = p.xy[2 * (size_t)k];
+        } else if (e < FK * PC + FK * PR) {
+          const int k = k0 + (e - FK * PC) / PR;
+          if (k < p.n) o.v[u] = p.xy[2 * (size_t)k + 1];
+        } else if (e < NT) {
+          const int k = k0 + (e - FK * PC - FK * PR);
+          if (k < p.n) o.v[u] = p.alpha[k];
         }
-        sm.ex[tb][kk][pc] = v;
       }
-      if (tid < FK * PR) {
-        const int kk = tid >> 3, pr = tid & 7, k = k0 + kk;
-        double v = 0.0;
-        if (k < p.n && r0 + pr < p.rows_local) {
-          const double dy = cell_coord(p.y0, p.ry, p.row0 + r0 + pr) - p.xy[2 * (size_t)k + 1];
-          v = p.sf2 * exp(-dy * dy * p.inv2l2);
+      return o;
+    };
+    auto table_store = [&](int k0, int tb, const TabIn& o) {
+#pragma unroll
+      for (int u = 0; u < TPT; ++u) {
+        const int e = tid + u * FT;
+        if (e < FK * PC) {
+          const int kk = e >> 4, pc = e & 15;
+          const double dx = cell_coord(p.x0, p.rx, col0 + pc) - o.v[u];
+          sm.ex[tb][kk][pc] = k0 + kk < p.n ? exp(-dx * dx * p.inv2l2) : 0.0;
+        } else if (e < FK * PC + FK * PR) {
+          const int kk = (e - FK * PC) / PR, pr = (e - FK * PC) % PR;
+          const double dy = cell_coord(p.y0, p.ry, p.row0 + r0 + pr) - o.v[u];
+          sm.ey[tb][kk][pr] = (k0 + kk < p.n && r0 + pr < p.rows_local) ? p.sf2 * exp(-dy * dy * p.inv2l2) : 0.0;
+        } else if (e < NT) {
+          sm.al[tb][e - FK * PC - FK * PR] = o.v[u];
         }
-        sm.ey[tb][kk][pr] = v;
-      } else if (tid < FK * PR + FK) {
-        const int kk = tid - FK * PR, k = k0 + kk;
-        sm.al[tb][kk] = k < p.n ? p.alpha[k] : 0.0;
       }
     };
     double mu_acc = 0.0;
-    auto make_a = [&](int tb, int buf, bool with_mu) {   // K* stage from its tables: thread = (cell, half of the 16 k)
-      const int c = tid >> 1, h = tid & 1, pc = c & 15, pr = c >> 4;
-      double v[8];
+    constexpr int KPT = FK * FM / FT;   // K* entries per thread and stage
+    auto make_a = [&](int tb, int buf, bool with_mu) {   // K* stage from its tables: thread = (cell, KPT consecutive k)
+      const int c = tid & (FM - 1), h = tid / FM, pc = c & 15, pr = c >> 4;   // a warp: 32 cells, one k group
+      double v[KPT];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = sm.ex[tb][h * 8 + i][pc] * sm.ey[tb][h * 8 + i][pr];
+      for (int i = 0; i < KPT; ++i) v[i] = sm.ex[tb][h * KPT + i][pc] * sm.ey[tb][h * KPT + i][pr];
       if (with_mu) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) mu_acc = fma(v[i], sm.al[tb][h * 8 + i], mu_acc);
+        for (int i = 0; i < KPT; ++i) mu_acc = fma(v[i], sm.al[tb][h * KPT + i], mu_acc);
       }
-      double2* dst = reinterpret_cast<double2*>(&sm.A[buf][c * LD + h * 8]);
+      double2* dst = reinterpret_cast<double2*>(&sm.A[buf][c * LD + h * KPT]);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) dst[i] = make_double2(v[2 * i], v[2 * i + 1]);
+      for (int i = 0; i < KPT / 2; ++i) dst[i] = make_double2(v[2 * i], v[2 * i + 1]);
     };
     auto load_b = [&](Cursor cur, int buf) {   // 128 rows x 16 k of L^-1: 1024 granules of two doubles
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int gi = q * FT + tid, r = gi >> 3, kq = (gi & 7) * 2;
+      for (int q = 0; q < FN * FK / 2 / FT; ++q) {
+        const int gi = q * FT + tid, r = gi / (FK / 2), kq = (gi % (FK / 2)) * 2;
         const int j = cur.jb * FN + r, k = cur.k0 + kq;
         const bool live = j >= p.j_lo && j < p.j_hi && k <= j;
         const double* src = p.Linv + (size_t)(live ? j : 0) * p.ld + (live ? k : 0);
@@ -140,23 +163,25 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
       }
     };
 
-    double rs[8];
+    double rs[MI];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) rs[i] = 0.0;
+    for (int i = 0; i < MI; ++i) rs[i] = 0.0;
 
     if (jb_hi > jb_lo) {
-      double acc[8][4][2];
+      double acc[MI][NI][2];
 #pragma unroll
-      for (int mi = 0; mi < 8; ++mi)
+      for (int mi = 0; mi < MI; ++mi)
 #pragma unroll
-        for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+        for (int ni = 0; ni < NI; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
 
-      // ---- prologue: tables of stages 0 and 1, K* and L^-1 of stage 0 ----
+      // ---- prologue: tables of stages 0 and 1, table inputs of stage 2, K* and L^-1 of stage 0 ----
       Cursor cur{jb_lo, 0};                       // stage being contracted
-      Cursor nxt = cur; advance(nxt);             // stage being staged
+      Cursor nxt = cur; advance(nxt);             // its successors (jb == jb_hi: beyond the end)
       Cursor nx2 = nxt; if (nxt.jb < jb_hi) advance(nx2);
-      make_tables(cur.k0, 0);
-      if (nxt.jb < jb_hi) make_tables(nxt.k0, 1);
+      Cursor nx3 = nx2; if (nx2.jb < jb_hi) advance(nx3);
+      table_store(cur.k0, 0, table_load(cur.k0));
+      if (nxt.jb < jb_hi) table_store(nxt.k0, 1, table_load(nxt.k0));
+      TabIn tab_cur = table_load(nx2.jb < jb_hi ? nx2.k0 : 0);   // inputs of the tables stored during iteration s = 0
       load_b(cur, 0);
       __syncthreads();
       make_a(0, 0, cur.jb == jb_hi - 1);
@@ -165,34 +190,41 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
 
       int s = 0;   // stage counter: A/B buffer s & 1, table buffer s % 3
       while (cur.jb < jb_hi) {
-        const bool have_next = nxt.jb < jb_hi;
-        if (have_next) {
-          load_b(nxt, (s + 1) & 1);
-          if (nx2.jb < jb_hi) make_tables(nx2.k0, (s + 2) % 3);
-          make_a((s + 1) % 3, (s + 1) & 1, nxt.jb == jb_hi - 1);
-        }
-        // ---- contract stage s: 4 k-steps of 8 x 4 DMMA tiles ----
-        const double* As = &sm.A[s & 1][(wm * 64 + g) * LD + t];
+        const bool have_next = nxt.jb < jb_hi, have_nx2 = nx2.jb < jb_hi, have_nx3 = nx3.jb < jb_hi;
+        // ---- contract stage s: FK / 4 k-steps of 4 x 4 DMMA tiles.  The staging work for the following stages
+        // (L^-1 slab of s+1, K* slab of s+1, tables of s+2, table inputs of s+3) sits BETWEEN the k-steps, at
+        // positions that differ for the four warps of a scheduler (they differ in wm): while one of them stages,
+        // the other three keep the fp64 pipe busy, and after the barrier every warp starts with DMMAs. ----
+        const double* As = &sm.A[s & 1][(wm * 32 + g) * LD + t];
         const double* Bs = &sm.B[s & 1][(wn * 32 + g) * LD + t];
+        TabIn tab_new = tab_cur;
 #pragma unroll
         for (int k4 = 0; k4 < FK / 4; ++k4) {
-          double a[8], b[4];
+          double a[MI], b[NI];
 #pragma unroll
-          for (int mi = 0; mi < 8; ++mi) a[mi] = As[mi * 8 * LD + k4 * 4];
+          for (int mi = 0; mi < MI; ++mi) a[mi] = As[mi * 8 * LD + k4 * 4];
 #pragma unroll
-          for (int ni = 0; ni < 4; ++ni) b[ni] = Bs[ni * 8 * LD + k4 * 4];
+          for (int ni = 0; ni < NI; ++ni) b[ni] = Bs[ni * 8 * LD + k4 * 4];
 #pragma unroll
-          for (int mi = 0; mi < 8; ++mi)
+          for (int mi = 0; mi < MI; ++mi)
 #pragma unroll
-            for (int ni = 0; ni < 4; ++ni) dmma(acc[mi][ni], a[mi], b[ni]);
+            for (int ni = 0; ni < NI; ++ni) dmma(acc[mi][ni], a[mi], b[ni]);
+          const int slot = (k4 - wm * (FK / 16)) & (FK / 4 - 1);
+          if (slot == 0 && have_next) {
+            load_b(nxt, (s + 1) & 1);
+            if (have_nx3) tab_new = table_load(nx3.k0);
+          }
+          if (slot == FK / 16 && have_next) make_a((s + 1) % 3, (s + 1) & 1, nxt.jb == jb_hi - 1);
+          if (slot == FK / 8 && have_nx2) table_store(nx2.k0, (s + 2) % 3, tab_cur);
         }
+        tab_cur = tab_new;
         // ---- end of a row block: squared row sums of this 128 x 128 block of V ----
         if (cur.k0 + FK >= kd(cur.jb)) {
 #pragma unroll
-          for (int mi = 0; mi < 8; ++mi) {
+          for (int mi = 0; mi < MI; ++mi) {
             double q = 0.0;
 #pragma unroll
-            for (int ni = 0; ni < 4; ++ni) {
+            for (int ni = 0; ni < NI; ++ni) {
               q = fma(acc[mi][ni][0], acc[mi][ni][0], q);
               q = fma(acc[mi][ni][1], acc[mi][ni][1], q);
               acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
@@ -202,20 +234,20 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
         }
         cp_async_wait_all();
         __syncthreads();
-        cur = nxt; nxt = nx2;
-        if (nx2.jb < jb_hi) advance(nx2);
+        cur = nxt; nxt = nx2; nx2 = nx3;
+        if (nx3.jb < jb_hi) advance(nx3);
         ++s;
       }
     }
 
     // ---- finish the tile: reduce over the lanes and warps that share a cell, write mu / sigma^2 ----
 #pragma unroll
-    for (int mi = 0; mi < 8; ++mi) {
+    for (int mi = 0; mi < MI; ++mi) {
       rs[mi] += __shfl_xor_sync(0xffffffffu, rs[mi], 1);
       rs[mi] += __shfl_xor_sync(0xffffffffu, rs[mi], 2);
-      if (t == 0) sm.red[wn][wm * 64 + mi * 8 + g] = rs[mi];
+      if (t == 0) sm.red[wn][wm * 32 + mi * 8 + g] = rs[mi];
     }
-    sm.mu_part[tid & 1][tid >> 1] = mu_acc;
+    sm.mu_part[tid / FM][tid & (FM - 1)] = mu_acc;
     __syncthreads();
     if (tid < FM) {
       const int pc = tid & 15, pr = tid >> 4;
@@ -225,7 +257,7 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
         const double sq = (sm.red[0][tid] + sm.red[1][tid]) + (sm.red[2][tid] + sm.red[3][tid]);
         const double prev = p.accumulate ? s2_out[lc] : p.sf2;
         s2_out[lc] = prev - sq;
-        mu_out[lc] = p.prior_mean + (sm.mu_part[0][tid] + sm.mu_part[1][tid]);
+        mu_out[lc] = p.prior_mean + ((sm.mu_part[0][tid] + sm.mu_part[1][tid]) + (sm.mu_part[2][tid] + sm.mu_part[3][tid]));
       }
     }
     __syncthreads();   // red / mu_part / stage buffers are reused by the next tile
