@@ -294,17 +294,21 @@ def main():
             key = "bf16_tflops_sustained" if ms_post > 50.0 else "bf16_tflops"
             peak = peaks[key]
             peak_note = f"{key} (kind::f16 tensor rate = the measured cuBLAS bf16 rate) of {peak_src}"
+        elif p.precision == "fp64":
+            # MEASURED_PEAKS.json has no fp64 entry; profiles/fp64_dmma_r01.md: 37.1 TFLOP/s for DFMA and DMMA alike on this pool's B200s
+            peak, peak_note = 37.1, "fp64 pipe (DFMA = DMMA m8n8k4), measured by scripts/probe/fp64_peak.cu (nominal 40)"
         else:
-            peak, peak_note = 40.0, "fp64 FMA pipe, nominal (no measured fp64 peak on file)"
+            peak, peak_note = 75.0, "fp32 FMA pipe, nominal (the SIMT cross-check kernel; not the product path)"
         achieved = flops / (ms_post * 1e-3) / 1e12
         traffic = None
         try:   # per-launch DRAM bytes of the dominant kernel from the committed ncu --set full capture of this workload
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic_r01.json")))
-            traffic = tj["posterior_tc_kernel" if used_tc else "posterior_simt_kernel"][args.workload]["dram_bytes_per_launch"]
+            traffic = tj[{1: "posterior_simt_kernel", 2: "posterior_tc_kernel", 4: "posterior_f64_kernel"}[outs[-1].kernel_used]][args.workload]["dram_bytes_per_launch"]
         except Exception:
             traffic = None
-        roofline = {"bound": "tensor" if used_tc else "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                    "frac": achieved / peak, "traffic": traffic, "kernel": "posterior_tc_kernel" if used_tc else "posterior_simt_kernel",
+        kname = {1: "posterior_simt_kernel", 2: "posterior_tc_kernel", 3: "posterior_thin_kernel", 4: "posterior_f64_kernel"}.get(outs[-1].kernel_used, "?")
+        roofline = {"bound": "tensor" if used_tc else ("fp64" if p.precision == "fp64" else "fp32"), "achieved": achieved, "peak": peak,
+                    "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic, "kernel": kname,
                     "peak_source": peak_note, "ms_kernel": ms_post, "credited_flops_per_launch": flops,
                     "executed_over_credited": executed_over_credited(p.n) if used_tc else 1.0}
         if used_tc:
