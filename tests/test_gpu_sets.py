@@ -94,3 +94,49 @@ def test_full_size_properties(ctx):
     assert np.array_equal(mask_a, mask_b) and a.argmax_ucb == b.argmax_ucb
     assert a.safe_count == int((mask_a == 255).sum()) and set(np.unique(mask_a)) <= {0, 255}
     assert a.argmax_ucb[1] == q1[mask_a == 255].max() and a.argmax_ucb[0] == np.flatnonzero((q1 == a.argmax_ucb[1]) & (mask_a == 255))[0]
+
+
+def _formula(mu32, s232, beta, f_min, noise_add=0.0):
+    """The reference's arithmetic (:409-416) in numpy fp64 on the fp32 posterior the step left on the device --
+    sqrt, *, -, + are IEEE-exact in numpy, so the step's mask and argmax must equal this bit for bit."""
+    mu = mu32.astype(np.float64); v = np.maximum(s232.astype(np.float64), 0.0) + noise_add
+    conf = beta * np.sqrt(v)
+    q0, q1 = mu - conf, mu + conf
+    safe = q0 > f_min
+    return q0, q1, safe
+
+
+def _check_step_sets(res, mask, q0, q1, safe):
+    assert np.array_equal(mask != 0, safe) and res.safe_count == int(safe.sum())
+    if safe.any():
+        u = np.where(safe, q1, -np.inf); w = np.where(safe, q1 - q0, -np.inf)
+        assert res.argmax_ucb == (int(np.argmax(u)), float(u.max()))           # np.argmax: first (lowest) index of the max
+        assert res.argmax_width == (int(np.argmax(w)), float(w.max()))
+    else:
+        assert res.argmax_ucb[0] == -1 and res.argmax_width[0] == -1
+
+
+@pytest.mark.parametrize("shape", [(512, 256, 300), (1024, 1024, 200), (333, 77, 150), (4096, 513, 64)])
+@pytest.mark.parametrize("noise_in_sigma", [False, True])
+def test_step_sets_equal_reference_formula_bit_for_bit(pkg, shape, noise_in_sigma):
+    """fp32 step path: the mask, the safe count and both argmax records must equal the reference's fp64 arithmetic
+    applied to the fp32 posterior on the device, bit for bit -- also when f_min sits exactly on a cell's LCB, one ulp
+    either side of it, at the extremes, and when beta = 0 makes every width tie (lowest index wins)."""
+    W, H, n = shape
+    p = S.make_problem("C2", n=n, W=W, H=H)
+    with make_ctx(pkg, p, precision="fp32", include_noise_in_sigma=noise_in_sigma) as ctx:
+        ctx.set_grid(p.x0, p.y0, p.rx, p.ry, W, H)
+        ctx.set_observations(p.xy, p.y)
+        ctx.step(p.beta, p.f_min)
+        mu32 = ctx.mu().astype(np.float32); s232 = ctx.sigma2().astype(np.float32)
+        assert np.array_equal(mu32.astype(np.float64), ctx.mu())                # the fp64 read-back is the fp32 value
+        noise_add = p.noise_var if noise_in_sigma else 0.0
+        q0, _, _ = _formula(mu32, s232, p.beta, p.f_min, noise_add)
+        on_cell = float(np.sort(q0)[q0.size // 3])
+        cases = [(p.beta, p.f_min), (p.beta, on_cell), (p.beta, float(np.nextafter(on_cell, -np.inf))),
+                 (p.beta, float(np.nextafter(on_cell, np.inf))), (p.beta, -1e300), (p.beta, 1e300), (0.0, p.f_min),
+                 (1e-30, p.f_min), (37.5, float(np.median(q0)) - 80.0)]
+        for beta, f_min in cases:
+            q0, q1, safe = _formula(mu32, s232, beta, f_min, noise_add)
+            res, mask = ctx.step(beta, f_min)
+            _check_step_sets(res, mask, q0, q1, safe)
