@@ -112,15 +112,19 @@ def cpu_posterior_sample(p, seconds, prefer=None):
     _, Linv, alpha = O.gp_fit_scipy(p.xy, p.y, hp)
     t_fit = time.perf_counter() - t0
 
+    sets_time = [0.0]
+
     def run(kind, cells):
         t = time.perf_counter()
         if kind == "c_openmp":
             mu, s2 = co.posterior(p.xy, hp, Linv, alpha, g, 0, cells)
         else:
             mu, s2 = O.gp_posterior_scipy(p.xy, hp, Linv, alpha, g, 0, cells)
-        q0, q1 = co.confidence_intervals(mu, np.sqrt(np.maximum(s2, 0.0)), p.beta)
-        mask, _ = co.safe_set(q0, p.f_min)
+        t1 = time.perf_counter()
+        q0, q1 = co.confidence_intervals(mu, np.sqrt(np.maximum(s2, 0.0)), p.beta)   # the node's own arithmetic (A4 + A5,
+        mask, _ = co.safe_set(q0, p.f_min)                                            # reference :399-416), single thread
         co.argmax_safe(q1, mask)
+        sets_time[0] = time.perf_counter() - t1
         return time.perf_counter() - t
 
     calib = min(p.m, 4096)
@@ -134,7 +138,9 @@ def cpu_posterior_sample(p, seconds, prefer=None):
             "sample": f"{kind} fp64 oracle, {cells} of {p.m} cells ({cells // max(p.W, 1)} grid rows) of {p.name} "
                       f"n={p.n}: posterior+CI+mask+argmax in {dt:.2f} s on {cores} host threads "
                       f"(factorisation {t_fit:.2f} s not included; calibration {rates})",
-            "seconds": dt, "cells": cells}
+            "seconds": dt, "cells": cells,
+            "node_arithmetic": {"what": "ComputeSets (CI + mask) + argmax restated in C, 1 thread, on the sample's mu / sigma",
+                                "ms": sets_time[0] * 1e3, "cells": cells, "cells_per_s": cells / max(sets_time[0], 1e-9)}}
 
 
 def run_reference(args, rank, world):
