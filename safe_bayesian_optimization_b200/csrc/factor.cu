@@ -256,6 +256,66 @@ diag_chol_inv_kernel(double* __restrict__ Ablk, int ld, int nb, double* __restri
   DiagSmem& sm = *reinterpret_cast<DiagSmem*>(smem_diag);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) sm.bad = 0;
+  if (nb <= 8) {
+    // A handful of rows (the node's steady state appends one observation at a time): one thread, same operations
+    // as the warp routine (pivot d, ri = rsqrt(d), column scaled by ri, updates with the unscaled column).
+    if (tid == 0) {
+      double a[8][8], rinv[8];
+      for (int i = 0; i < nb; ++i)
+        for (int j = 0; j <= i; ++j) a[i][j] = Ablk[(size_t)i * ld + j];
+      bool bad = false;
+      for (int j = 0; j < nb && !bad; ++j) {
+        double d = a[j][j];
+        if (!(d > 0.0)) {
+          atomicCAS(info, 0, row_base + j + 1);
+          bad = true;
+          break;
+        }
+        const double ri = rsqrt(d);
+        rinv[j] = ri;
+        for (int i = j + 1; i < nb; ++i) {
+          const double t = a[i][j] * (ri * ri);
+          for (int c = j + 1; c <= i; ++c) a[i][c] = fma(-t, a[c][j], a[i][c]);
+        }
+        for (int i = j + 1; i < nb; ++i) a[i][j] *= ri;
+        a[j][j] = d * ri;
+      }
+      if (!bad) {
+        for (int c = 0; c < nb; ++c) {   // column c of X = L^-1
+          double x[8];
+          for (int i = 0; i < nb; ++i) x[i] = (i == c) ? 1.0 : 0.0;
+          for (int q = c; q < nb; ++q) {
+            x[q] *= rinv[q];
+            for (int i = q + 1; i < nb; ++i) x[i] = fma(-a[i][q], x[q], x[i]);
+          }
+          for (int i = 0; i < nb; ++i) Dinv[(size_t)i * ldd + c] = (i >= c) ? x[i] : 0.0;
+        }
+        for (int i = 0; i < nb; ++i)
+          for (int j = 0; j < nb; ++j) Ablk[(size_t)i * ld + j] = (j <= i) ? a[i][j] : 0.0;
+      }
+    }
+    return;
+  }
+  if (nb <= SB) {
+    // One sub-block (the Schur complement of a rank-k append, k <= 32): the warp-level routine is the whole job;
+    // loading, factoring and inverting the other 15 sub-blocks of identity padding cost 60 of this kernel's 69 us.
+    for (int e = tid; e < SB * SB; e += kDiagThreads) {
+      const int i = e >> 5, j = e & (SB - 1);
+      double v = (i == j) ? 1.0 : 0.0;
+      if (i < nb && j < nb) v = (j <= i) ? Ablk[(size_t)i * ld + j] : 0.0;
+      sm.S[i][j] = v;
+    }
+    __syncthreads();
+    if (warp == 0) warp_chol_inv32(sm, 0, row_base, info);
+    __syncthreads();
+    if (sm.bad) return;
+    for (int e = tid; e < nb * nb; e += kDiagThreads) {
+      const int i = e / nb, j = e - i * nb;
+      Ablk[(size_t)i * ld + j] = (j < i) ? sm.S[i][j] : (j == i ? sm.dL[i] : 0.0);
+      Dinv[(size_t)i * ldd + j] = (j < i) ? sm.S[j][i] : (j == i ? sm.dX[i] : 0.0);
+    }
+    return;
+  }
 #pragma unroll 4
   for (int e = tid; e < NB * NB; e += kDiagThreads) {
     const int i = e >> 7, j = e & (NB - 1);
@@ -635,6 +695,7 @@ append_t_kernel(const double* __restrict__ X, int ld, int n, int k, const double
     double s[8];
 #pragma unroll
     for (int q = 0; q < 8; ++q) s[q] = 0.0;
+#pragma unroll 4
     for (int p = max(p_lo, c); p < p_hi; ++p) {
       const double x = X[(size_t)p * ld + c];
 #pragma unroll
@@ -664,6 +725,39 @@ append_rows_kernel(double* __restrict__ X, int ld, int n, int k, const double* _
     v = (q <= i) ? X22[i * kMaxAppend + q] : 0.0;
   }
   X[(size_t)(n + i) * ld + c] = v;
+}
+
+// alpha after a rank-k append without the two O(n^2) products: with w = L^-1 r,
+//   w_new[i] = X[n+i][0 .. n+i] . r           (the old entries of w do not change: L^-1 only gains rows)
+//   alpha    = L^-T w  =  alpha_old (0 beyond n)  +  sum_i X[n+i][:]^T w_new[i].
+__global__ void __launch_bounds__(256)
+append_w_kernel(const double* __restrict__ X, int ld, int n, int k, const double* __restrict__ r, double* __restrict__ w) {
+  __shared__ double red[8];
+  const int i = blockIdx.x;
+  const double* row = X + (size_t)(n + i) * ld;
+  double s = 0.0;
+  for (int c = threadIdx.x; c <= n + i; c += 256) s = fma(row[c], r[c], s);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) t += red[q];
+    w[n + i] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+append_alpha_kernel(const double* __restrict__ X, int ld, int n, int k, const double* __restrict__ w,
+                    double* __restrict__ alpha, float* __restrict__ alpha_f32) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= n + k) return;
+  double a = c < n ? alpha[c] : 0.0;
+  for (int i = 0; i < k; ++i) a = fma(X[(size_t)(n + i) * ld + c], w[n + i], a);   // X[n+i][c] = 0 for c > n + i
+  alpha[c] = a;
+  if (alpha_f32) alpha_f32[c] = (float)a;
 }
 
 int32_t check_info(sbo_ctx* ctx, const char* what) {
@@ -829,7 +923,7 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
   double* T = K21;
   if (n > 0) {
     SBO_CUDA(ctx, cudaMemsetAsync(T, 0, sizeof(double) * (size_t)k * ld, st));
-    int splits = (ctx->sm_count * 4) / ((n + 127) / 128);
+    int splits = (ctx->sm_count * 16) / ((n + 127) / 128);   // ~2048 resident threads per SM: one load in flight each
     if (splits < 1) splits = 1;
     if (splits > 64) splits = 64;
     dim3 g((n + 127) / 128, splits);
@@ -841,7 +935,14 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
     append_rows_kernel<<<g, 256, 0, st>>>(ctx->d_Linv, ld, n, k, T, X22);
     SBO_LAUNCH_CHECK(ctx, "append_rows_kernel");
   }
-  SBO_TRY(compute_alpha(ctx, n + k));
+  if (n > 0) {   // alpha by the O(n k) update; the first fit of an empty context goes the general way
+    append_w_kernel<<<k, 256, 0, st>>>(ctx->d_Linv, ld, n, k, ctx->d_r, ctx->d_w);
+    SBO_LAUNCH_CHECK(ctx, "append_w_kernel");
+    append_alpha_kernel<<<(n + k + 255) / 256, 256, 0, st>>>(ctx->d_Linv, ld, n, k, ctx->d_w, ctx->d_alpha, ctx->d_alpha_f32);
+    SBO_LAUNCH_CHECK(ctx, "append_alpha_kernel");
+  } else {
+    SBO_TRY(compute_alpha(ctx, n + k));
+  }
   SBO_TRY(refresh_planes(ctx, n, n + k));
   return SBO_OK;
 }
