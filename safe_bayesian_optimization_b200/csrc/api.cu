@@ -412,8 +412,7 @@ int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y,
     if (ctx->tc_skip_plan == 0) ctx->tc_skip_plan = -1;  // a decision to skip survives appends; a decision not to is re-examined
     done += kk;
   }
-  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  return SBO_OK;
+  return SBO_OK;   // factor_append left the stream synchronised
 }
 
 // N4 -- observation ingestion.  One record per SpatialMeasurement message as the publisher fills it

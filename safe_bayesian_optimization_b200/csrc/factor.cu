@@ -919,7 +919,8 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
   }
   diag_chol_inv_kernel<<<1, kDiagThreads, kDiagSmem, st>>>(S, kMaxAppend, k, X22, kMaxAppend, n, ctx->d_info);
   SBO_LAUNCH_CHECK(ctx, "diag_chol_inv_kernel(append)");
-  SBO_TRY(check_info(ctx, "sbo_append_observations"));
+  // The positive-definiteness verdict is read once, at the end (one host synchronisation per append instead of two):
+  // until then only rows >= n of L^-1 (not part of the state) and alpha are written, and alpha is restored below.
   double* T = K21;
   if (n > 0) {
     SBO_CUDA(ctx, cudaMemsetAsync(T, 0, sizeof(double) * (size_t)k * ld, st));
@@ -944,7 +945,14 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
     SBO_TRY(compute_alpha(ctx, n + k));
   }
   SBO_TRY(refresh_planes(ctx, n, n + k));
-  return SBO_OK;
+  const int32_t verdict = check_info(ctx, "sbo_append_observations");   // synchronises the stream
+  if (verdict != SBO_OK) {   // not positive definite: the new rows were computed from garbage; put alpha back
+    SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_alpha + n, 0, sizeof(double) * (size_t)k, st));
+    if (ctx->d_alpha_f32) SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_alpha_f32 + n, 0, sizeof(float) * (size_t)k, st));
+    if (n > 0) SBO_TRY(compute_alpha(ctx, n));
+    SBO_CUDA(ctx, cudaStreamSynchronize(st));
+  }
+  return verdict;
 }
 
 }  // namespace sbo

@@ -86,7 +86,15 @@ def test_errors_and_state(pkg):
             ctx.set_observations(xy, np.zeros(3))
         assert e.value.status == -4 and "positive definite at row" in str(e.value)
         assert ctx.n_obs == 0
-        ctx.set_observations(xy[:2], np.zeros(2))                     # context still usable
+        ctx.set_observations(xy[:2], np.array([0.3, -0.2]))           # context still usable
+        ctx.set_grid(0.0, 0.0, 0.1, 0.1, 8, 8)
+        alpha0, linv0 = ctx.alpha(), ctx.linv()
+        before, _ = ctx.step(2.0, -10.0)
+        mu0 = ctx.mu()
         with pytest.raises(pkg.SboError) as e:
-            ctx.append_observations(xy[2:], np.zeros(1))
+            ctx.append_observations(xy[2:], np.array([0.3]))
         assert e.value.status == -4 and ctx.n_obs == 2
+        # the failed append leaves the last good state: same factor, alpha put back, a step gives the same posterior
+        assert np.array_equal(ctx.linv(), linv0) and np.allclose(ctx.alpha(), alpha0, rtol=1e-13, atol=0)
+        after, _ = ctx.step(2.0, -10.0)
+        assert np.allclose(ctx.mu(), mu0, rtol=1e-13, atol=1e-15) and after.safe_count == before.safe_count
