@@ -246,3 +246,32 @@ def test_full_size_c2_properties(pkg):
             ctx2.set_observations(np.concatenate([p.xy, xy2]), np.concatenate([p.y, y2]))
             ctx2.step(p.beta, p.f_min)
             assert (ctx2.sigma2() <= s2 + 2e-5).all()
+
+
+def test_full_size_c3_properties(pkg):
+    """BASELINE config C3 at full size (4096 observations x 16 Mi cells, block-sparse walk): size-independent
+    properties -- bounds, count = checksum of the mask, idempotence, a row band computed on its own equals the same
+    rows of the full grid bit for bit, sigma^2 does not depend on y, mu - prior is linear in y - prior."""
+    p = S.make_problem("C3")
+    with make_ctx(pkg, p) as ctx:
+        ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+        ctx.set_observations(p.xy, p.y)
+        a, mask = ctx.step(p.beta, p.f_min)
+        assert a.kernel_used == 2 and ctx.tc_plan()[1] is True            # the planner chose the block-sparse walk
+        s2, mu = ctx.sigma2(), ctx.mu()
+        assert np.isfinite(mu).all() and (s2 > 0).all() and (s2 <= p.sigma_f ** 2 * (1 + 1e-6)).all()
+        assert a.safe_count == int(np.count_nonzero(mask)) and 0 < a.safe_count < p.m and set(np.unique(mask)) <= {0, 255}
+        b, mask_b = ctx.step(p.beta, p.f_min)
+        assert np.array_equal(mask, mask_b) and a.argmax_ucb == b.argmax_ucb and a.argmax_width == b.argmax_width
+        # a band of rows on its own
+        r0, r1 = 1531, 1540
+        ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H, r0, r1)
+        c, mask_c = ctx.step(p.beta, p.f_min)
+        assert np.array_equal(ctx.sigma2(), s2[r0 * p.W:r1 * p.W]) and np.array_equal(ctx.mu(), mu[r0 * p.W:r1 * p.W])
+        assert np.array_equal(mask_c, mask[r0 * p.W:r1 * p.W])
+        # y' = prior + 2 (y - prior): alpha doubles exactly, sigma^2 is untouched
+        ctx.set_observations(p.xy, p.prior_mean + 2.0 * (p.y - p.prior_mean))
+        ctx.step(p.beta, p.f_min)
+        assert np.array_equal(ctx.sigma2(), s2[r0 * p.W:r1 * p.W])
+        d1 = mu[r0 * p.W:r1 * p.W] - p.prior_mean
+        assert np.abs((ctx.mu() - p.prior_mean) - 2.0 * d1).max() <= 2e-6 * max(1.0, np.abs(d1).max())
