@@ -250,7 +250,7 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
     }
   } else {
     switch (kr) {
-      case 1: launch_thin<double, 1, 1, 8>(ctx, p); break;
+      case 1: launch_thin<double, 1, 1, 16>(ctx, p); break;   // one exp per 16 cells: the fp64 exp is ~14 DFMA-equivalents
       case 2: launch_thin<double, 2, 1, 8>(ctx, p); break;
       case 4: launch_thin<double, 4, 1, 4>(ctx, p); break;
       default: launch_thin<double, 8, 1, 4>(ctx, p); break;
