@@ -34,6 +34,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 
 #include "common.cuh"
@@ -92,6 +93,8 @@ struct TcParams {
   float* dbg_v;            // debug: V of tile 0 ([128][n_cap]) when non-null
   const float4* bbox;      // [n_cap / 64] scaled bounding box (xmin, xmax, ymin, ymax) of every 64-observation chunk
   int skip;                // 1: chunks whose K* entries are all below 2^-kSkipBits sigma_f^2 for a tile are not contracted
+  long long* dbg_clk;      // SBO_TC_CLK=1: per-role cycle counters of cluster 0 (timing forensics)
+  int dbg;                 // SBO_TC_DBG (timing experiments only, results are wrong): 1 generators skip the K* math, 2 epilogue skips the TMEM reads, 4 one MMA pass instead of three
 };
 
 // ---- PTX wrappers ------------------------------------------------------------------------------
@@ -231,6 +234,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
 // Instruction descriptor: D=f32, A=B=f16 (format 0), both K-major, N=256, M=128 per CTA.
 template <int CG> __device__ __forceinline__ uint32_t idesc_f16(uint32_t n_cols) {
   return (1u << 4) | ((n_cols >> 3) << 17) | ((uint32_t)((BM * CG) >> 4) << 24);
+}
+
+// One lane of a CONVERGED warp (the lowest).  The single-thread tcgen05 / TMA instructions are issued under this
+// predicate from warp-uniform code: with operands in uniform registers ptxas emits them directly; inside an
+// `if (lane == 0)` region it wraps every one of them in an ELECT / R2UR.BROADCAST / BRA.U.ANY waterfall loop
+// (~20 instructions per MMA: the issuer, not the tensor pipe, then paces the kernel).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -458,81 +471,95 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = sh->tmem_base;
+  const long long ck_begin = clock64();
 
   if (warp == 0) {
-    // =============================== TMA producer ===============================
+    // =============================== TMA producer (converged warp, one elected lane issues) ===============================
     uint32_t it = 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
       if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
-      if (lane == 0) {
-        for (int jb = jb_lo; jb < jb_hi; ++jb) {
-          const int nch = chunks_of(jb, n_pad);
-          bool fresh = true;
-          ChunkIter<kSkip> ci;
-          ci.reset(cmask);
-          for (int kc = ci.next(); kc < nch; kc = ci.next(), ++it) {
-            const int s = it % kStages;
-            const uint32_t ph = (it / kStages) & 1u;
-            // chunk c = kc - 4 jb >= 0 of the diagonal block only meets rows >= 64 c of this row block (L^-1 is
-            // lower triangular): the tile starts there and the MMA narrows to N = 256 - 64 c (see the issuer).
-            // The first contracted chunk of a row block runs at full N: it initialises every accumulator column.
-            const int c = fresh ? 0 : max(kc - jb * (BN / BK), 0);
-            fresh = false;
-            const int row = jb * BN + c * BK + (int)rank * ((int)Cfg::kBRows - c * (BK / 2));
-            mbar_wait(&sh->empty[s], ph ^ 1u);
-            const uint32_t bar = CG == 1 ? smem_u32(&sh->full[s]) : mapa(smem_u32(&sh->full[s]), 0);
-            if (rank == 0) mbar_arrive_expect_tx(&sh->full[s], 2 * Cfg::kBBytes * CG);
-            tma_load_2d<CG>(&tmap, bar, b_hi(s), kc * BK, row);
-            tma_load_2d<CG>(&tmap, bar, b_lo(s), kc * BK, p.n_cap + row);
+      for (int jb = jb_lo; jb < jb_hi; ++jb) {
+        const int nch = chunks_of(jb, n_pad);
+        bool fresh = true;
+        ChunkIter<kSkip> ci;
+        ci.reset(cmask);
+        for (int kc = ci.next(); kc < nch; kc = ci.next(), ++it) {
+          const int s = it % kStages;
+          const uint32_t ph = (it / kStages) & 1u;
+          // chunk c = kc - 4 jb >= 0 of the diagonal block only meets rows >= 64 c of this row block (L^-1 is
+          // lower triangular): the tile starts there and the MMA narrows to N = 256 - 64 c (see the issuer).
+          // The first contracted chunk of a row block runs at full N: it initialises every accumulator column.
+          const int c = fresh ? 0 : max(kc - jb * (BN / BK), 0);
+          fresh = false;
+          const int row = jb * BN + c * BK + (int)rank * ((int)Cfg::kBRows - c * (BK / 2));
+          mbar_wait(&sh->empty[s], ph ^ 1u);
+          const uint32_t bar = CG == 1 ? smem_u32(&sh->full[s]) : mapa(smem_u32(&sh->full[s]), 0);
+          if (elect_one()) {
+            if (p.dbg & 64) {
+              if (rank == 0) mbar_arrive_local(&sh->full[s]);
+            } else {
+              if (rank == 0) mbar_arrive_expect_tx(&sh->full[s], 2 * Cfg::kBBytes * CG);
+              tma_load_2d<CG>(&tmap, bar, b_hi(s), kc * BK, row);
+              tma_load_2d<CG>(&tmap, bar, b_lo(s), kc * BK, p.n_cap + row);
+            }
           }
+          __syncwarp();
         }
       }
-      it = __shfl_sync(0xffffffffu, it, 0);
     }
   } else if (warp == 1) {
-    // =============================== MMA issuer (leader CTA) ===============================
+    // =============================== MMA issuer (leader CTA; converged warp, one elected lane issues) ===============================
     uint32_t it = 0, acc_it = 0;
+    long long ck_full = 0, ck_issue = 0, ck_acc = 0;
+    const bool clk_on = p.dbg_clk != nullptr && blockIdx.x == 0;
     for (long long gt = group; rank == 0 && gt < ngtiles; gt += ngroups) {
       if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
-      if (lane == 0) {
-        for (int jb = jb_lo; jb < jb_hi; ++jb) {
-          const int nch = chunks_of(jb, n_pad);
-          ChunkIter<kSkip> ci;
-          ci.reset(cmask);
-          int kc = ci.next();
-          if (kc >= nch) continue;  // no chunk of this row block matters for the tile: V = 0, nothing to do
-          const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
-          ++acc_it;
-          mbar_wait(&sh->tmem_empty[as], aph ^ 1u);  // epilogue has drained this accumulator
+      for (int jb = jb_lo; jb < jb_hi; ++jb) {
+        const int nch = chunks_of(jb, n_pad);
+        ChunkIter<kSkip> ci;
+        ci.reset(cmask);
+        int kc = ci.next();
+        if (kc >= nch) continue;  // no chunk of this row block matters for the tile: V = 0, nothing to do
+        const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
+        ++acc_it;
+        const long long cka = clk_on ? clock64() : 0;
+        mbar_wait(&sh->tmem_empty[as], aph ^ 1u);  // epilogue has drained this accumulator
+        if (clk_on) ck_acc += clock64() - cka;
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        bool fresh = true;
+        for (; kc < nch; kc = ci.next(), ++it) {
+          const int s = it % kStages;
+          const uint32_t ph = (it / kStages) & 1u;
+          const long long ckf = clk_on ? clock64() : 0;
+          mbar_wait(&sh->full[s], ph);  // TMA bytes landed and generators stored their planes
+          const long long ckg = clk_on ? clock64() : 0;
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + as * BN;
-          bool fresh = true;
-          for (; kc < nch; kc = ci.next(), ++it) {
-            const int s = it % kStages;
-            const uint32_t ph = (it / kStages) & 1u;
-            mbar_wait(&sh->full[s], ph);  // TMA bytes landed and generators stored their planes
-            tc_fence_after();
-            const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(s))), dal = umma_desc_sw128(smem_u32(a_lo(s)));
-            const uint64_t dbh = umma_desc_sw128(smem_u32(b_hi(s))), dbl = umma_desc_sw128(smem_u32(b_lo(s)));
-            // diagonal block, chunk c: columns < 64 c of the accumulator get no contribution (zeros of L^-1)
-            const uint32_t c = fresh ? 0u : (uint32_t)max(kc - jb * (BN / BK), 0);
-            const uint32_t idesc = idesc_f16<CG>(BN - c * BK), d_col = d_tmem + c * BK;
+          const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(s))), dal = umma_desc_sw128(smem_u32(a_lo(s)));
+          const uint64_t dbh = umma_desc_sw128(smem_u32(b_hi(s))), dbl = umma_desc_sw128(smem_u32(b_lo(s)));
+          // diagonal block, chunk c: columns < 64 c of the accumulator get no contribution (zeros of L^-1)
+          const uint32_t c = fresh ? 0u : (uint32_t)max(kc - jb * (BN / BK), 0);
+          const uint32_t idesc = idesc_f16<CG>(BN - c * BK), d_col = d_tmem + c * BK;
+          if (elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < BK / UK; ++ks) {
               const uint64_t adv = (uint64_t)((ks * UK * 2) >> 4);  // +32 bytes along K inside the swizzle row
               umma_f16<CG>(d_col, dal + adv, dbh + adv, idesc, (fresh && ks == 0) ? 0u : 1u);
+              if (p.dbg & 4) continue;
               umma_f16<CG>(d_col, dah + adv, dbl + adv, idesc, 1u);
               umma_f16<CG>(d_col, dah + adv, dbh + adv, idesc, 1u);
             }
-            fresh = false;
             umma_commit<CG>(&sh->empty[s]);  // stage reusable once these MMAs have read it
           }
-          umma_commit<CG>(&sh->tmem_full[as]);  // accumulator complete
+          __syncwarp();
+          fresh = false;
+          if (clk_on) { ck_full += ckg - ckf; ck_issue += clock64() - ckg; }
         }
+        if (elect_one()) umma_commit<CG>(&sh->tmem_full[as]);  // accumulator complete
+        __syncwarp();
       }
-      it = __shfl_sync(0xffffffffu, it, 0);
-      acc_it = __shfl_sync(0xffffffffu, acc_it, 0);
     }
+    if (clk_on && lane == 0) { p.dbg_clk[40] = ck_full; p.dbg_clk[41] = ck_issue; p.dbg_clk[42] = ck_acc; p.dbg_clk[43] = it; }
   } else if (warp >= 4 && warp < 8) {
     // =============================== epilogue ===============================
     const int q = warp & 3;
@@ -557,6 +584,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         for (int c = 0; c < BN / 32; ++c) {
           const int jc = j0 + c * 32;
           if (jc >= p.j_hi || jc + 32 <= p.j_lo) continue;  // columns outside the contracted rows (warp-uniform)
+          if (p.dbg & 2) continue;
           uint32_t v[32];
           tmem_ld32(taddr + c * 32, v);
           tmem_ld_wait();
@@ -619,6 +647,8 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     float4 o_next = make_float4(0.f, 0.f, 0.f, 0.f);
     float a_next = 0.f;
     int c_next = -1;
+    long long ck_math = 0, ck_wait = 0, ck_post = 0, ck_iters = 0;
+    const bool clk_on = p.dbg_clk != nullptr && blockIdx.x < 2 && (gw == 0 || gw == 15) && lane == 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups, tile_par ^= 1u) {
       const long long tile = min(gt * CG + (long long)rank, ntiles - 1);  // an odd last tile: the peer recomputes it, no store
       const bool live = gt * CG + rank < ntiles;
@@ -641,8 +671,9 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           kn = ci.next();  // the chunk after this one (one look-ahead serves the loop and the prefetch below)
           const int s = it % kStages;
           const uint32_t ph = (it / kStages) & 1u;
+          const long long ck0 = clk_on ? clock64() : 0;
           // per-observation terms of this quarter-chunk, one observation per lane (lanes 0-15)
-          if (lane < 16) {
+          if (lane < 16 && !(p.dbg & 16)) {
             const int k = kc * BK + kq * 16 + lane;
             if (c_next != kc) {  // warp-uniform
               o_next = p.obs[k];
@@ -659,10 +690,15 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           }
           __syncwarp();
           uint32_t hi[8], lo[8];
-          if (last) two_sum_acc(mu_hi, mu_lo, gen_chunk<true>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, hi, lo));
+          if (p.dbg & 1) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { hi[e] = 0x3c003c00u; lo[e] = 0u; }
+          } else if (last) two_sum_acc(mu_hi, mu_lo, gen_chunk<true>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, hi, lo));
           else gen_chunk<false>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, hi, lo);
+          const long long ck1 = clk_on ? clock64() : 0;
           mbar_wait(&sh->empty[s], ph ^ 1u);  // MMAs that read this stage have completed
-          {
+          const long long ck2 = clk_on ? clock64() : 0;
+          if (!(p.dbg & 8)) {
             uint8_t* pa_hi = a_hi(s) + row_off;
             uint8_t* pa_lo = a_lo(s) + row_off;
             const uint32_t off0 = (((uint32_t)kq * 2u) ^ swz) << 4, off1 = (((uint32_t)kq * 2u + 1u) ^ swz) << 4;
@@ -671,12 +707,13 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             *reinterpret_cast<uint4*>(pa_hi + off1) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
             *reinterpret_cast<uint4*>(pa_lo + off1) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
           }
-          fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+          if (!(p.dbg & 32)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
           __syncwarp();
           if (lane == 0) {
             if constexpr (CG == 1) mbar_arrive_local(&sh->full[s]);
             else mbar_arrive_cluster(mapa(smem_u32(&sh->full[s]), 0));
           }
+          if (clk_on) { const long long ck3 = clock64(); ck_math += ck1 - ck0; ck_wait += ck2 - ck1; ck_post += ck3 - ck2; ++ck_iters; }
         }
       }
       const double mu_acc = (double)mu_hi + (double)mu_lo;
@@ -692,10 +729,15 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         }
       }
     }
+    if (clk_on) {
+      long long* o = p.dbg_clk + 8 * (blockIdx.x * 2 + (gw == 15));
+      o[0] = ck_math; o[1] = ck_wait; o[2] = ck_post; o[3] = ck_iters;
+    }
   }
 
   tc_fence_before();
   if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
+  if (p.dbg_clk && blockIdx.x == 0 && threadIdx.x == 0) p.dbg_clk[63] = clock64() - ck_begin;
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<CG>(tmem_base, kTmemCols);
@@ -863,6 +905,16 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.dbg_v = g_dbg_v;
   p.bbox = reinterpret_cast<const float4*>(ctx->d_chunk_bbox);
   p.skip = tc_plan_skip(ctx) ? 1 : 0;
+  p.dbg = 0;
+  if (const char* s = std::getenv("SBO_TC_DBG")) p.dbg = std::atoi(s);
+  p.dbg_clk = nullptr;
+  static long long* d_clk = nullptr;
+  const bool want_clk = std::getenv("SBO_TC_CLK") != nullptr;
+  if (want_clk) {
+    if (!d_clk) cudaMalloc(&d_clk, 64 * sizeof(long long));
+    cudaMemsetAsync(d_clk, 0, 64 * sizeof(long long), ctx->stream);
+    p.dbg_clk = d_clk;
+  }
   if ((ctx->n + BK - 1) / BK > kMaskWords * 32)
     return fail(ctx, SBO_ERR_CAPACITY, "tcgen05 posterior kernel: more than 32 768 observations (chunk mask capacity)");
   SBO_TRY(tc_pack_observations(ctx));
@@ -892,6 +944,18 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
     if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_kernel<2> (cluster launch)");
   }
   SBO_LAUNCH_CHECK(ctx, "posterior_tc_kernel");
+  if (want_clk) {
+    long long h[64];
+    cudaMemcpyAsync(h, d_clk, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
+    std::fprintf(stderr, "[tc clk] total %lld clk\n", h[63]);
+    for (int g = 0; g < 4; ++g)
+      std::fprintf(stderr, "[tc clk] cta %d gen warp %2d: iters %lld  math %.0f  wait(empty) %.0f  post %.0f clk/iter\n", g / 2, (g & 1) * 15,
+                   h[8 * g + 3], (double)h[8 * g] / std::max(1LL, h[8 * g + 3]), (double)h[8 * g + 1] / std::max(1LL, h[8 * g + 3]),
+                   (double)h[8 * g + 2] / std::max(1LL, h[8 * g + 3]));
+    std::fprintf(stderr, "[tc clk] issuer: iters %lld  wait(full) %.0f  issue %.0f clk/iter, wait(tmem_empty) total %lld\n", h[43],
+                 (double)h[40] / std::max(1LL, h[43]), (double)h[41] / std::max(1LL, h[43]), h[42]);
+  }
   return SBO_OK;
 }
 
