@@ -67,9 +67,9 @@ struct __align__(16) TcShared {
   unsigned long long tmem_empty[2];// leader CTA's copy is the one in use
   uint32_t tmem_base;
   uint32_t pad[3];
-  float4 obs_x[kGenWarps][4];      // per generator warp: scaled x - tile origin of its 16 observations
-  float4 obs_y[kGenWarps][4];      //   y factor of K* (incl. sigma_f^2 and the A scale)
-  float4 obs_a[kGenWarps][4];      //   alpha
+  float4 obs_x[kGenWarps][8];      // per generator warp: scaled x - tile origin of its 32 observations
+  float4 obs_y[kGenWarps][8];      //   y factor of K* (incl. sigma_f^2 and the A scale)
+  float4 obs_a[kGenWarps][8];      //   alpha
   float mu_part[2][3][BM];         // partial mu of k-quarters 1..3, double-buffered by tile parity
   uint32_t cmask[kThreadsTc / 32][kMaskWords];  // per warp: bit c set = chunk c is contracted for the current tile (pair)
 };
@@ -336,6 +336,30 @@ template <bool kSkip> struct ChunkIter {
   }
 };
 
+// The (row block, chunk) visits of one cell tile in pipeline order -- every role walks this same sequence.
+template <bool kSkip> struct TileWalk {
+  ChunkIter<kSkip> ci;
+  const uint32_t* mask;
+  int jb, jb_hi, n_pad, nch;
+  __device__ __forceinline__ void start(const uint32_t* m, int jb_lo_, int jb_hi_, int n_pad_) {
+    mask = m; jb = jb_lo_; jb_hi = jb_hi_; n_pad = n_pad_;
+    nch = jb < jb_hi ? chunks_of(jb, n_pad) : 0;
+    ci.reset(mask);
+  }
+  // chunk of the next visit (its row block is `jb`), or -1 when the tile is done
+  __device__ __forceinline__ int next() {
+    while (jb < jb_hi) {
+      const int kc = ci.next();
+      if (kc < nch) return kc;
+      if (++jb < jb_hi) {
+        nch = chunks_of(jb, n_pad);
+        ci.reset(mask);
+      }
+    }
+    return -1;
+  }
+};
+
 // One thread's share of a K* chunk: cell r of the tile x 16 observations (2 groups of 8 = 2 16-byte
 // swizzle units of the row), written as fp16 hi / lo planes.  Returns sum_k K*[r,k] alpha[k] (scaled).
 //   K*[r,k] 2^shift_a = ex2(-(xs_k - cxs_r)^2) ey_k,   xs, cxs = x sqrt(log2(e) / 2 l^2),
@@ -383,6 +407,65 @@ __device__ __forceinline__ void two_sum_acc(float& hi, float& lo, float x) {
   const float z = t - hi;
   lo += (hi - (t - z)) + (x - z);
   hi = t;
+}
+
+// ---- packed fp32 pairs (sm_100: add/mul/fma.f32x2 -> FADD2 / FMUL2 / FFMA2, two results per issue slot) ----------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float a, float b) {
+  f32x2 r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+  f32x2 r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+  f32x2 r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+
+// One thread's share of HALF a K* chunk-half: cell r x 16 observations (two 16-byte swizzle units per plane), the
+// arithmetic of gen_chunk on packed fp32 pairs: per pair of entries  FADD2 (dx), FMUL2 (dx^2), 2 MUFU.EX2, FMUL2 (ey),
+// [FFMA2 (mu)], F2FP (hi), 2 HADD2.F32 (hi back to fp32), FADD2 (residual), F2FP (lo) = 5 issue slots per entry
+// instead of 7.  ncx2 = (-cxs, -cxs).  mu2 accumulates sum_k K*[r,k] alpha[k] in two fp32 lanes (even / odd k).
+template <bool kMu>
+__device__ __forceinline__ void gen16(const float4* ox4, const float4* oy4, const float4* oa4, f32x2 ncx2, uint32_t (&hi)[8],
+                                      uint32_t (&lo)[8], f32x2& mu2) {
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float4 xa = ox4[q], ya = oy4[q];  // warp-wide broadcast loads
+    float4 aa = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (kMu) aa = oa4[q];
+    const f32x2 xs[2] = {pack2(xa.x, xa.y), pack2(xa.z, xa.w)};
+    const f32x2 ey[2] = {pack2(ya.x, ya.y), pack2(ya.z, ya.w)};
+    const f32x2 al[2] = {pack2(aa.x, aa.y), pack2(aa.z, aa.w)};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const f32x2 d = add2(xs[h], ncx2);
+      float t0, t1;
+      unpack2(mul2(d, d), t0, t1);
+      // MUFU ex2 is accurate enough here (profiles/accuracy_r01.md); the error budget is set by the accumulator.
+      const f32x2 kv = mul2(pack2(ex2_approx(-t0), ex2_approx(-t1)), ey[h]);
+      if (kMu) mu2 = fma2(kv, al[h], mu2);
+      float k0, k1;
+      unpack2(kv, k0, k1);
+      const __half2 hh = __floats2half2_rn(k0, k1);
+      const float2 hf = __half22float2(hh);
+      float r0, r1;
+      unpack2(add2(kv, pack2(-hf.x, -hf.y)), r0, r1);
+      hi[2 * q + h] = h2_bits(hh);
+      lo[2 * q + h] = h2_bits(__floats2half2_rn(r0, r1));
+    }
+  }
 }
 
 // Observation coordinates for the generators: scaled by sqrt(log2(e) / 2 l^2) and split into fp32 (hi, lo)
@@ -457,7 +540,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(&sh->full[s], 1 + kGenWarps * CG);  // leader's TMA producer + every generator warp of the group
+      mbar_init(&sh->full[s], 1 + (kGenWarps / 2) * CG);  // leader's TMA producer + the 8 generator warps per CTA that own the visit
       mbar_init(&sh->empty[s], 1);          // tcgen05.commit
     }
     for (int s = 0; s < 2; ++s) {
@@ -631,8 +714,12 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     }
   } else if (warp >= 8) {
     // =============================== K* generators ===============================
-    const int gw = warp - 8;       // 0..15
-    const int kq = gw >> 2;        // which 16 of the chunk's 64 observations
+    // Two groups of 8 warps take alternate visits (grp = visit parity): a warp has two chunk times for its share,
+    // and the per-chunk fixed cost (observation staging, fence, barrier traffic) is paid once per 32 observations.
+    const int gw = warp - 8;          // 0..15
+    const int grp = gw >> 3;          // parity of the visits this warp generates
+    const int oh = (gw >> 2) & 1;     // which 32 of the chunk's 64 observations
+    const int pq = grp * 2 + oh;      // slot of this warp's partial mu
     const int r = (gw & 3) * 32 + lane;
     float* ox = reinterpret_cast<float*>(sh->obs_x[gw]);
     float* oy = reinterpret_cast<float*>(sh->obs_y[gw]);
@@ -640,14 +727,15 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     const uint32_t row_off = (uint32_t)r * 128u;
     const uint32_t swz = (uint32_t)(r & 7);
     const float cxs = (float)((double)r * p.rx * p.xscale);  // scaled offset of this thread's cell from the tile origin
+    const f32x2 ncx2 = pack2(-cxs, -cxs);
     uint32_t it = 0;
     uint32_t tile_par = 0;
-    // observation data of the NEXT contracted chunk is fetched while the current one is generated; the guess
-    // (next set bit, else the first one again) is wrong only across tiles with different masks: checked at use
+    // observation data of this warp's NEXT visit (two visits ahead) is fetched while the current one is generated;
+    // across tiles the guess is "the next tile starts like this one": checked at use (c_next != kc -> reload)
     float4 o_next = make_float4(0.f, 0.f, 0.f, 0.f);
     float a_next = 0.f;
     int c_next = -1;
-    long long ck_math = 0, ck_wait = 0, ck_post = 0, ck_iters = 0;
+    long long ck_math = 0, ck_wait = 0, ck_post = 0, ck_iters = 0, ck_stage = 0, ck_sync = 0, ck_h2 = 0, ck_fence = 0;
     const bool clk_on = p.dbg_clk != nullptr && blockIdx.x < 2 && (gw == 0 || gw == 15) && lane == 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups, tile_par ^= 1u) {
       const long long tile = min(gt * CG + (long long)rank, ntiles - 1);  // an odd last tile: the peer recomputes it, no store
@@ -657,70 +745,92 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       const double ox0 = cell_coord(p.x0, p.rx, col0) * p.xscale, oy0 = cell_coord(p.y0, p.ry, p.row0 + lrow) * p.xscale;
       const float oxh = (float)ox0, oxl = (float)(ox0 - (double)oxh);
       const float oyh = (float)oy0, oyl = (float)(oy0 - (double)oyh);
-      float mu_hi = 0.f, mu_lo = 0.f;  // fp32 inside a 16-observation quarter-chunk, double-word fp32 across chunks
+      float mu_hi = 0.f, mu_lo = 0.f;  // fp32 inside a 32-observation half-chunk, double-word fp32 across chunks
       if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
-      ChunkIter<kSkip> ci;
-      ci.reset(cmask);
-      const int first_chunk = ci.next();
-      for (int jb = jb_lo; jb < jb_hi; ++jb) {
-        const bool last = (jb == jb_hi - 1);
-        const int nch = chunks_of(jb, n_pad);
-        ci.reset(cmask);
-        int kc = ci.next();
-        for (int kn; kc < nch; kc = kn, ++it) {
-          kn = ci.next();  // the chunk after this one (one look-ahead serves the loop and the prefetch below)
-          const int s = it % kStages;
-          const uint32_t ph = (it / kStages) & 1u;
-          const long long ck0 = clk_on ? clock64() : 0;
-          // per-observation terms of this quarter-chunk, one observation per lane (lanes 0-15)
-          if (lane < 16 && !(p.dbg & 16)) {
-            const int k = kc * BK + kq * 16 + lane;
-            if (c_next != kc) {  // warp-uniform
-              o_next = p.obs[k];
-              a_next = p.alpha[k];
-            }
-            const float yr = (o_next.z - oyh) + (o_next.w - oyl);
-            ox[lane] = (o_next.x - oxh) + (o_next.y - oxl);  // (the previous chunk's readers passed the __syncwarp below)
-            oy[lane] = k < p.n ? ex2_approx(-yr * yr) * p.a_scale : 0.f;
-            oa[lane] = a_next;
-            c_next = kn < nch ? kn : first_chunk;  // (a tile without any chunk never gets here)
-            const int kp = c_next * BK + kq * 16 + lane;  // < n_cap: the buffers are padded
-            o_next = p.obs[kp];
-            a_next = p.alpha[kp];
+      TileWalk<kSkip> w, scout;
+      w.start(cmask, jb_lo, jb_hi, n_pad);
+      scout = w;
+      const int first0 = scout.next(), first1 = scout.next();  // visits 0 and 1 of this tile
+      // visit parity is counted per tile (vi), not along the pipeline (it): which warps sum which observations into mu
+      // must not depend on the tiles this CTA happened to process before (row-band shards agree bit for bit)
+      uint32_t vi = 0;
+      for (int kc = w.next(); kc >= 0; kc = w.next(), ++it, ++vi) {
+        int kn = scout.next();  // the chunk two visits ahead
+        if (kn < 0) kn = grp == 0 ? first0 : first1;  // next tile: this group's first visit there
+        if ((vi & 1u) != (uint32_t)grp) continue;
+        const bool last = (w.jb == jb_hi - 1);
+        const int s = it % kStages;
+        const uint32_t ph = (it / kStages) & 1u;
+        const long long ck0 = clk_on ? clock64() : 0;
+        // per-observation terms of this half-chunk, one observation per lane
+        if (!(p.dbg & 16)) {
+          const int k = kc * BK + oh * 32 + lane;
+          if (c_next != kc) {  // warp-uniform
+            o_next = p.obs[k];
+            a_next = p.alpha[k];
           }
-          __syncwarp();
+          const float yr = (o_next.z - oyh) + (o_next.w - oyl);
+          ox[lane] = (o_next.x - oxh) + (o_next.y - oxl);  // (the previous visit's readers passed the __syncwarp below)
+          oy[lane] = k < p.n ? ex2_approx(-yr * yr) * p.a_scale : 0.f;
+          oa[lane] = a_next;
+          c_next = kn >= 0 ? kn : kc;
+          const int kp = c_next * BK + oh * 32 + lane;  // < n_cap: the buffers are padded
+          o_next = p.obs[kp];
+          a_next = p.alpha[kp];
+        }
+        const long long ckA = clk_on ? clock64() : 0;
+        __syncwarp();
+        const long long ckB = clk_on ? clock64() : 0;
+        uint8_t* pa_hi = a_hi(s) + row_off;
+        uint8_t* pa_lo = a_lo(s) + row_off;
+        f32x2 mu2 = pack2(0.f, 0.f);
+        long long ck1 = 0, ck2 = 0;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
           uint32_t hi[8], lo[8];
           if (p.dbg & 1) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) { hi[e] = 0x3c003c00u; lo[e] = 0u; }
-          } else if (last) two_sum_acc(mu_hi, mu_lo, gen_chunk<true>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, hi, lo));
-          else gen_chunk<false>(sh->obs_x[gw], sh->obs_y[gw], sh->obs_a[gw], cxs, hi, lo);
-          const long long ck1 = clk_on ? clock64() : 0;
-          mbar_wait(&sh->empty[s], ph ^ 1u);  // MMAs that read this stage have completed
-          const long long ck2 = clk_on ? clock64() : 0;
+          } else if (last) gen16<true>(sh->obs_x[gw] + 4 * half, sh->obs_y[gw] + 4 * half, sh->obs_a[gw] + 4 * half, ncx2, hi, lo, mu2);
+          else gen16<false>(sh->obs_x[gw] + 4 * half, sh->obs_y[gw] + 4 * half, sh->obs_a[gw] + 4 * half, ncx2, hi, lo, mu2);
+          if (half == 0) {
+            ck1 = clk_on ? clock64() : 0;
+            mbar_wait(&sh->empty[s], ph ^ 1u);  // MMAs that read this stage have completed
+            ck2 = clk_on ? clock64() : 0;
+          }
           if (!(p.dbg & 8)) {
-            uint8_t* pa_hi = a_hi(s) + row_off;
-            uint8_t* pa_lo = a_lo(s) + row_off;
-            const uint32_t off0 = (((uint32_t)kq * 2u) ^ swz) << 4, off1 = (((uint32_t)kq * 2u + 1u) ^ swz) << 4;
+            const uint32_t u0 = (uint32_t)(oh * 4 + half * 2);
+            const uint32_t off0 = ((u0 ^ swz) << 4), off1 = (((u0 + 1u) ^ swz) << 4);
             *reinterpret_cast<uint4*>(pa_hi + off0) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
             *reinterpret_cast<uint4*>(pa_lo + off0) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
             *reinterpret_cast<uint4*>(pa_hi + off1) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
             *reinterpret_cast<uint4*>(pa_lo + off1) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
           }
-          if (!(p.dbg & 32)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
-          __syncwarp();
-          if (lane == 0) {
-            if constexpr (CG == 1) mbar_arrive_local(&sh->full[s]);
-            else mbar_arrive_cluster(mapa(smem_u32(&sh->full[s]), 0));
-          }
-          if (clk_on) { const long long ck3 = clock64(); ck_math += ck1 - ck0; ck_wait += ck2 - ck1; ck_post += ck3 - ck2; ++ck_iters; }
+        }
+        if (last) {
+          float m0, m1;
+          unpack2(mu2, m0, m1);
+          two_sum_acc(mu_hi, mu_lo, m0 + m1);
+        }
+        const long long ckD = clk_on ? clock64() : 0;
+        if (!(p.dbg & 32)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+        __syncwarp();
+        const long long ckE = clk_on ? clock64() : 0;
+        if (lane == 0) {
+          if constexpr (CG == 1) mbar_arrive_local(&sh->full[s]);
+          else mbar_arrive_cluster(mapa(smem_u32(&sh->full[s]), 0));
+        }
+        if (clk_on) {
+          const long long ck3 = clock64();
+          ck_math += ck1 - ck0; ck_wait += ck2 - ck1; ck_post += ck3 - ck2; ++ck_iters;
+          ck_stage += ckA - ck0; ck_sync += ckB - ckA; ck_h2 += ckD - ck2; ck_fence += ckE - ckD;
         }
       }
       const double mu_acc = (double)mu_hi + (double)mu_lo;
-      // combine the four k-quarters' partial mu and write it out
-      if (kq > 0) sh->mu_part[tile_par][kq - 1][r] = (float)mu_acc;
+      // combine the four partial mu (2 groups x 2 observation halves) and write it out
+      if (pq > 0) sh->mu_part[tile_par][pq - 1][r] = (float)mu_acc;
       named_bar_sync(1, kGenWarps * 32);
-      if (kq == 0 && live) {
+      if (pq == 0 && live) {
         const int col = col0 + r;
         if (col < p.W) {
           const double part = (double)sh->mu_part[tile_par][0][r] + (double)sh->mu_part[tile_par][1][r] +
@@ -731,7 +841,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     }
     if (clk_on) {
       long long* o = p.dbg_clk + 8 * (blockIdx.x * 2 + (gw == 15));
-      o[0] = ck_math; o[1] = ck_wait; o[2] = ck_post; o[3] = ck_iters;
+      o[0] = ck_math; o[1] = ck_wait; o[2] = ck_post; o[3] = ck_iters; o[4] = ck_stage; o[5] = ck_sync; o[6] = ck_h2; o[7] = ck_fence;
     }
   }
 
@@ -950,9 +1060,11 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
     cudaStreamSynchronize(ctx->stream);
     std::fprintf(stderr, "[tc clk] total %lld clk\n", h[63]);
     for (int g = 0; g < 4; ++g)
-      std::fprintf(stderr, "[tc clk] cta %d gen warp %2d: iters %lld  math %.0f  wait(empty) %.0f  post %.0f clk/iter\n", g / 2, (g & 1) * 15,
-                   h[8 * g + 3], (double)h[8 * g] / std::max(1LL, h[8 * g + 3]), (double)h[8 * g + 1] / std::max(1LL, h[8 * g + 3]),
-                   (double)h[8 * g + 2] / std::max(1LL, h[8 * g + 3]));
+      std::fprintf(stderr, "[tc clk] cta %d gen warp %2d: iters %lld  math %.0f (stage %.0f sync %.0f)  wait(empty) %.0f  post %.0f (sts1+gen2+sts2 %.0f fence %.0f) clk/iter\n", g / 2, (g & 1) * 15,
+                   h[8 * g + 3], (double)h[8 * g] / std::max(1LL, h[8 * g + 3]), (double)h[8 * g + 4] / std::max(1LL, h[8 * g + 3]),
+                   (double)h[8 * g + 5] / std::max(1LL, h[8 * g + 3]), (double)h[8 * g + 1] / std::max(1LL, h[8 * g + 3]),
+                   (double)h[8 * g + 2] / std::max(1LL, h[8 * g + 3]), (double)h[8 * g + 6] / std::max(1LL, h[8 * g + 3]),
+                   (double)h[8 * g + 7] / std::max(1LL, h[8 * g + 3]));
     std::fprintf(stderr, "[tc clk] issuer: iters %lld  wait(full) %.0f  issue %.0f clk/iter, wait(tmem_empty) total %lld\n", h[43],
                  (double)h[40] / std::max(1LL, h[43]), (double)h[41] / std::max(1LL, h[43]), h[42]);
   }
