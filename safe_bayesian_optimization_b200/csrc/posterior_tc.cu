@@ -42,6 +42,11 @@
 namespace sbo {
 namespace {
 
+// -DSBO_TC_CLOCKS=1 compiles the per-role cycle counters in (SBO_TC_CLK=1 prints them); off by default: they cost registers
+#ifndef SBO_TC_CLOCKS
+#define SBO_TC_CLOCKS 0
+#endif
+
 constexpr int BM = 128;          // cells per CTA tile (UMMA M per CTA)
 constexpr int BN = 256;          // rows of L^-1 per accumulator (UMMA N)
 constexpr int BK = 64;           // k per stage: 64 fp16 = one 128-byte swizzle row
@@ -554,7 +559,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
   tc_fence_after();
   const uint32_t tmem_base = sh->tmem_base;
-  const long long ck_begin = clock64();
+  const long long ck_begin = SBO_TC_CLOCKS ? clock64() : 0;
 
   if (warp == 0) {
     // =============================== TMA producer (converged warp, one elected lane issues) ===============================
@@ -594,7 +599,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     // =============================== MMA issuer (leader CTA; converged warp, one elected lane issues) ===============================
     uint32_t it = 0, acc_it = 0;
     long long ck_full = 0, ck_issue = 0, ck_acc = 0;
-    const bool clk_on = p.dbg_clk != nullptr && blockIdx.x == 0;
+    const bool clk_on = SBO_TC_CLOCKS && p.dbg_clk != nullptr && blockIdx.x == 0;
     for (long long gt = group; rank == 0 && gt < ngtiles; gt += ngroups) {
       if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
       for (int jb = jb_lo; jb < jb_hi; ++jb) {
@@ -736,7 +741,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     float a_next = 0.f;
     int c_next = -1;
     long long ck_math = 0, ck_wait = 0, ck_post = 0, ck_iters = 0, ck_stage = 0, ck_sync = 0, ck_h2 = 0, ck_fence = 0;
-    const bool clk_on = p.dbg_clk != nullptr && blockIdx.x < 2 && (gw == 0 || gw == 15) && lane == 0;
+    const bool clk_on = SBO_TC_CLOCKS && p.dbg_clk != nullptr && blockIdx.x < 2 && (gw == 0 || gw == 15) && lane == 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups, tile_par ^= 1u) {
       const long long tile = min(gt * CG + (long long)rank, ntiles - 1);  // an odd last tile: the peer recomputes it, no store
       const bool live = gt * CG + rank < ntiles;
@@ -847,7 +852,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
 
   tc_fence_before();
   if constexpr (CG == 1) __syncthreads(); else cluster_sync_all();
-  if (p.dbg_clk && blockIdx.x == 0 && threadIdx.x == 0) p.dbg_clk[63] = clock64() - ck_begin;
+  if (SBO_TC_CLOCKS && p.dbg_clk && blockIdx.x == 0 && threadIdx.x == 0) p.dbg_clk[63] = clock64() - ck_begin;
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<CG>(tmem_base, kTmemCols);
