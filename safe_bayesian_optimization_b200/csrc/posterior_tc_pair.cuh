@@ -16,8 +16,16 @@
 //   row block jb0 = 2 pi     takes part while kc < chunks_of(jb0)       (narrowed in its diagonal block)
 //   row block jb1 = 2 pi + 1 takes part in every visit                  (kc < chunks_of(jb1))
 
-constexpr int kPairStagesA = 3;
-constexpr int kPairStagesB = 3;
+#ifndef SBO_PAIR_SA
+#define SBO_PAIR_SA 3
+#define SBO_PAIR_SB 3
+#endif
+constexpr int kPairStagesA = SBO_PAIR_SA;
+constexpr int kPairStagesB = SBO_PAIR_SB;
+#ifndef SBO_PAIR_LAG
+#define SBO_PAIR_LAG 0
+#endif
+constexpr int kPairLag = SBO_PAIR_LAG;
 constexpr uint32_t kPairABytes = 2 * kABytes;              // hi + lo planes of one K* chunk: 32 KB
 constexpr uint32_t kPairBBytes = 2 * TcCfg<2>::kBBytes;    // hi + lo half-tiles of L^-1 held by one CTA: 32 KB
 
@@ -121,9 +129,10 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         const int jb0 = 2 * pi;
         const bool has1 = jb0 + 1 < nblocks;
         const int nch0 = chunks_of(jb0, n_pad), nchl = has1 ? chunks_of(jb0 + 1, n_pad) : nch0;
-        for (int kc = 0; kc < nchl; ++kc) {
-          if (kc < nch0) load_b(jb0, kc);
-          if (has1) load_b(jb0 + 1, kc);
+        const int lag = has1 ? kPairLag : 0;  // the second row block's MMAs trail the first one's by `lag` visits (see the issuer)
+        for (int t = 0; t < nchl + lag; ++t) {
+          if (t < nch0) load_b(jb0, t);
+          if (has1 && t >= lag) load_b(jb0 + 1, t - lag);
         }
       }
     }
@@ -135,15 +144,23 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         const int jb0 = 2 * pi;
         const bool has1 = jb0 + 1 < nblocks;
         const int nch0 = chunks_of(jb0, n_pad), nchl = has1 ? chunks_of(jb0 + 1, n_pad) : nch0;
-        for (int kc = 0; kc < nchl; ++kc, ++ita) {
-          const int sa = ita % kPairStagesA;
-          mbar_wait(&sh->full_a[sa], (ita / kPairStagesA) & 1u);  // generators stored their planes
-          tc_fence_after();
-          const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(sa))), dal = umma_desc_sw128(smem_u32(a_lo(sa)));
+        // Issue order inside a pair: (row block 0, visit t) then (row block 1, visit t - lag).  lag = 1 would hide the
+        // epilogue still draining the second accumulator when a pair begins (there is no spare one: 2 x 256 columns = all
+        // of TMEM); measured equal to lag = 0 at n = 1024 / 2048 (2.03 / 7.16 ms), lag = 2 starves the K* ring (+12 %).
+        const int lag = has1 ? kPairLag : 0;
+        for (int t = 0; t < nchl + lag; ++t) {
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
-            if (half == 0 ? kc >= nch0 : !has1) continue;
+            const int kc = half == 0 ? t : t - lag;
+            if (half == 0 ? kc >= nch0 : (!has1 || kc < 0)) continue;
             const int jb = jb0 + half;
+            const uint32_t va = ita + (uint32_t)kc;  // this visit's place in the A ring
+            const int sa = va % kPairStagesA;
+            if (half == 0 || kc >= nch0) {  // first use of the visit's K* stage
+              mbar_wait(&sh->full_a[sa], (va / kPairStagesA) & 1u);  // generators stored their planes
+              tc_fence_after();
+            }
+            const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(sa))), dal = umma_desc_sw128(smem_u32(a_lo(sa)));
             if (kc == 0) {  // first MMA into this accumulator: the epilogue must have drained its previous contents
               mbar_wait(&sh->tmem_empty[half], ((half == 0 ? use0 : use1) & 1u) ^ 1u);
               tc_fence_after();
@@ -164,17 +181,15 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
                 umma_f16<CG>(d_col, dah + adv, dbh + adv, idesc, 1u);
               }
               umma_commit<CG>(&sh->empty_b[sb]);
+              if (half == 1 || !has1) umma_commit<CG>(&sh->empty_a[sa]);  // last use: K* stage reusable once these MMAs have read it
               if (half == 0 && kc == nch0 - 1) umma_commit<CG>(&sh->tmem_full[0]);  // first row block complete
+              if (half == 1 && kc == nchl - 1) umma_commit<CG>(&sh->tmem_full[1]);
             }
             __syncwarp();
             ++itb;
           }
-          if (elect_one()) {
-            umma_commit<CG>(&sh->empty_a[sa]);  // K* stage reusable once these MMAs have read it
-            if (has1 && kc == nchl - 1) umma_commit<CG>(&sh->tmem_full[1]);
-          }
-          __syncwarp();
         }
+        ita += (uint32_t)nchl;
       }
     }
   } else if (warp >= 4 && warp < 8) {
