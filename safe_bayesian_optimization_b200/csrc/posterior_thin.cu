@@ -2,16 +2,19 @@
 //
 // After sbo_append_observations the factor gains k rows:  L^-1 = [[L11^-1, 0], [R, L22^-1]].  For every cell
 //   sigma^2_new = sigma^2_old - sum_r u_r^2,   u_r = rows_new[r] . k*      (sequential conditioning)
-//   mu_new      = prior_mean + k* . alpha_new                              (alpha changes everywhere)
-// so one pass over the n observations per cell yields both.  This is what the ROS node's steady state looks
+//   mu_new      = mu_old + sum_r w_r u_r,      w = L^-1 (y - prior_mean)   (alpha_new = [alpha_old; 0] + rows_new^T w_new,
+//                                                                           factor.cu append_alpha_kernel, so k* . alpha_new
+//                                                                           = k* . alpha_old + sum_r w_r (rows_new[r] . k*))
+// so the k projections u_r are all a cell needs: one pass over the n observations with k outputs (not 1 + k: the
+// mean needs no contraction of its own).  This is what the ROS node's steady state looks
 // like (one measurement per second, src/turtlesim_spatial_publisher.py:43) and what BASELINE configs C3/C5 time.
 // The contraction has N = k (<= 8) columns: far too thin for a tensor-core tile (the 256-row block kernel of
 // posterior_tc.cu spends 256/k times the necessary MMAs on it), and its cost is the K* entries themselves --
 // one ex2 (fp32) or exp (fp64) per cell and observation if done naively.  The RBF kernel on a grid is separable,
 //   k*(cell(ix, iy), obs j) = sigma_f^2 ex(ix, j) ey(iy, j),
 // so a thread that owns C columns x R rows of cells needs ex only once per (column, observation) and the row
-// factor arrives pre-multiplied:  the CTA stages, per observation, the tile-relative x and the R (1 + k) products
-// ey(r, j) alpha_j and ey(r, j) Linv[new row q][j]; the inner loop is then one FMA per (cell, observation, output)
+// factor arrives pre-multiplied:  the CTA stages, per observation, the tile-relative x and the R k products
+// ey(r, j) Linv[new row q][j]; the inner loop is then one FMA per (cell, observation, new row)
 // and 1/R exponentials per (cell, observation), with all staged values read as broadcast 16-byte vectors.
 //
 // Numerics: fp32 mode accumulates in fp32 over 64 observations and in fp64 across (an fp32 running sum over
@@ -32,7 +35,7 @@ struct ThinParams {
   const float4* obs_f32;   // fp32 mode: scaled (x_hi, x_lo, y_hi, y_lo)
   const double* xy;        // fp64 mode
   const double* Linv;      // [n_cap][ld] fp64
-  const double* alpha;     // [n] fp64
+  const double* w;         // [n] fp64: L^-1 (y - prior_mean); entries row_lo .. row_lo + k_new - 1 are read
   int n, ld;
   int row_lo, k_new;       // new rows [row_lo, row_lo + k_new)
   int W, rows_local, row0;
@@ -58,10 +61,10 @@ __device__ __forceinline__ void load4(const double* p, double (&v)[4]) {
 }
 
 // Tile = (kThinThreads * C) columns x R grid rows; thread = C columns x R rows.  NP products per observation:
-// slot r (1 + KR) is ey_r alpha, slots r (1 + KR) + 1 + q are ey_r Linv[new row q].
+// slot r KR + q is ey_r Linv[new row q].
 template <typename T, int KR, int C, int R>
 struct ThinCfg {
-  static constexpr int kNP = R * (1 + KR);
+  static constexpr int kNP = R * KR;
   static constexpr int kChunk = sizeof(T) == 4 ? 256 : 128;   // observations staged per pass (<= 48 KB static smem)
   static_assert(kNP % 4 == 0, "products are read as 4-vectors");
 };
@@ -89,6 +92,10 @@ posterior_thin_kernel(ThinParams p, T* __restrict__ mu_out, T* __restrict__ s2_o
   const int row_groups = (p.rows_local + R - 1) / R;
   const long long ntiles = (long long)row_groups * tiles_per_row;
 
+  double wq[KR];
+#pragma unroll
+  for (int q = 0; q < KR; ++q) wq[q] = q < p.k_new ? p.w[p.row_lo + q] : 0.0;
+
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int r0 = (int)(tile / tiles_per_row) * R, col0 = (int)(tile % tiles_per_row) * span;
     // tile origin; fp32 mode works in scaled units with (hi, lo) pairs, fp64 mode in plain coordinates
@@ -112,7 +119,7 @@ posterior_thin_kernel(ThinParams p, T* __restrict__ mu_out, T* __restrict__ s2_o
       if (tid < kChunk) {
         const int j = k0 + tid;
         const bool live = j < p.n;
-        T tx = (T)0, ta = (T)0, tl[KR];
+        T tx = (T)0, tl[KR];
         float4 of = make_float4(0.f, 0.f, 0.f, 0.f);
         double2 od = make_double2(0.0, 0.0);
 #pragma unroll
@@ -125,7 +132,6 @@ posterior_thin_kernel(ThinParams p, T* __restrict__ mu_out, T* __restrict__ s2_o
             od = *reinterpret_cast<const double2*>(p.xy + 2 * (size_t)j);
             tx = (T)(od.x - ox);
           }
-          ta = (T)p.alpha[j];
 #pragma unroll
           for (int q = 0; q < KR; ++q)
             if (q < p.k_new) tl[q] = (T)p.Linv[(size_t)(p.row_lo + q) * p.ld + j];
@@ -146,9 +152,8 @@ posterior_thin_kernel(ThinParams p, T* __restrict__ mu_out, T* __restrict__ s2_o
               e = (T)(p.sf2 * exp(-dy * dy * p.inv2l2));
             }
           }
-          sm.p[tid][r * (1 + KR)] = e * ta;
 #pragma unroll
-          for (int q = 0; q < KR; ++q) sm.p[tid][r * (1 + KR) + 1 + q] = e * tl[q];
+          for (int q = 0; q < KR; ++q) sm.p[tid][r * KR + q] = e * tl[q];
         }
       }
       __syncthreads();
@@ -201,11 +206,15 @@ posterior_thin_kernel(ThinParams p, T* __restrict__ mu_out, T* __restrict__ s2_o
       for (int r = 0; r < R; ++r) {
         if (col < p.W && r0 + r < p.rows_local) {
           const long long lc = (long long)(r0 + r) * p.W + col;
-          double red = 0.0;
+          double red = 0.0, dmu = 0.0;
 #pragma unroll
-          for (int t = 0; t < KR; ++t) red = fma(acc[q][r * (1 + KR) + 1 + t], acc[q][r * (1 + KR) + 1 + t], red);
+          for (int t = 0; t < KR; ++t) {
+            const double u = acc[q][r * KR + t];
+            red = fma(u, u, red);
+            dmu = fma(wq[t], u, dmu);
+          }
           s2_out[lc] = (T)((double)s2_out[lc] - red);
-          mu_out[lc] = (T)(p.prior_mean + acc[q][r * (1 + KR)]);
+          mu_out[lc] = (T)((double)mu_out[lc] + dmu);
         }
       }
     }
@@ -231,7 +240,7 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
   if (k_new < 0 || k_new > kThinMaxRows) return fail(ctx, SBO_ERR_STATE, "posterior_thin: more than 8 new rows");
   ThinParams p;
   p.obs_f32 = reinterpret_cast<const float4*>(ctx->d_obs_f32);
-  p.xy = ctx->d_xy; p.Linv = ctx->d_Linv; p.alpha = ctx->d_alpha;
+  p.xy = ctx->d_xy; p.Linv = ctx->d_Linv; p.w = ctx->d_w;
   p.n = ctx->n; p.ld = ctx->n_cap; p.row_lo = row_lo; p.k_new = k_new;
   p.W = ctx->W; p.rows_local = ctx->row1 - ctx->row0; p.row0 = ctx->row0;
   p.x0 = ctx->x0; p.y0 = ctx->y0; p.rx = ctx->rx; p.ry = ctx->ry;
@@ -243,16 +252,16 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
   if (ctx->cfg.precision == SBO_FP32) {
     SBO_TRY(tc_pack_observations(ctx));
     switch (kr) {
-      case 1: launch_thin<float, 1, 2, 8>(ctx, p); break;
-      case 2: launch_thin<float, 2, 2, 4>(ctx, p); break;
+      case 1: launch_thin<float, 1, 2, 16>(ctx, p); break;
+      case 2: launch_thin<float, 2, 2, 8>(ctx, p); break;
       case 4: launch_thin<float, 4, 1, 8>(ctx, p); break;
       default: launch_thin<float, 8, 1, 4>(ctx, p); break;
     }
   } else {
     switch (kr) {
-      case 1: launch_thin<double, 1, 1, 16>(ctx, p); break;   // one exp per 16 cells: the fp64 exp is ~14 DFMA-equivalents
-      case 2: launch_thin<double, 2, 1, 8>(ctx, p); break;
-      case 4: launch_thin<double, 4, 1, 4>(ctx, p); break;
+      case 1: launch_thin<double, 1, 1, 32>(ctx, p); break;   // one exp per 32 cells: the fp64 exp is ~14 DFMA-equivalents
+      case 2: launch_thin<double, 2, 1, 16>(ctx, p); break;
+      case 4: launch_thin<double, 4, 1, 8>(ctx, p); break;
       default: launch_thin<double, 8, 1, 4>(ctx, p); break;
     }
   }
