@@ -201,6 +201,46 @@ def test_single_cta_variant_matches_pair(pkg, oracle, coracle, monkeypatch):
     assert np.array_equal(out["1"][0], out["2"][0]) and np.array_equal(out["1"][1], out["2"][1])
 
 
+@pytest.mark.parametrize("n,W,H", [(700, 384, 9), (1100, 256, 7), (2304, 640, 3), (512, 130, 4)])
+def test_pair_kernel_matches_row_block_kernel(pkg, oracle, coracle, monkeypatch, n, W, H):
+    """The dense full refresh runs the K*-stationary pair kernel (one K* generation per two row blocks of L^-1;
+    odd row-block counts end in a single).  SBO_TC_PAIR=0 runs the one-row-block kernel instead: both meet the
+    oracle, and sigma^2 agrees bit for bit (same MMAs per accumulator in the same order, same epilogue sums)."""
+    p = S.make_problem("C2", n=n, W=W, H=H)
+    ref = reference(oracle, coracle, p)
+    out = {}
+    for pair in ("0", "1"):
+        monkeypatch.setenv("SBO_TC_PAIR", pair)
+        monkeypatch.setenv("SBO_TC_SKIP", "0")
+        with make_ctx(pkg, p, kernel="tcgen05") as ctx:
+            ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+            ctx.set_observations(p.xy, p.y)
+            res, mask = ctx.step(p.beta, p.f_min)
+            out[pair] = (ctx.mu(), ctx.sigma2())
+            check_step(p, ref, res, mask, out[pair][0], out[pair][1], "fp32", label=f"pair={pair}")
+    assert np.array_equal(out["0"][1], out["1"][1])
+    assert np.abs(out["0"][0] - out["1"][0]).max() <= 2e-6 * np.abs(out["0"][0]).max()
+
+
+@pytest.mark.parametrize("precision", ["fp32", "fp64"])
+def test_long_rank1_chain_stays_in_tolerance(pkg, oracle, coracle, precision):
+    """The node's steady state: one observation per step.  The thin kernel updates mu in place
+    (mu += w u) and sigma^2 (-= u^2), so rounding accumulates over the chain: 48 steps must still meet the oracle."""
+    n0, steps = 200, 48
+    p = S.make_problem("C3", n=n0 + steps, W=300, H=17)
+    with make_ctx(pkg, p, precision=precision, kernel="auto" if precision == "fp64" else "tcgen05", max_obs=n0 + steps) as ctx:
+        ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+        ctx.set_observations(p.xy[:n0], p.y[:n0])
+        ctx.step(p.beta, p.f_min)
+        for t in range(steps):
+            ctx.append_observations(p.xy[n0 + t:n0 + t + 1], p.y[n0 + t:n0 + t + 1])
+            res, mask = ctx.step(p.beta, p.f_min, incremental=True)
+            assert res.kernel_used == 3
+        ref = reference(oracle, coracle, p)
+        band = check_step(p, ref, res, mask, ctx.mu(), ctx.sigma2(), precision, label="chain48")
+        check_argmax(res, ref, band, mask)
+
+
 @pytest.mark.parametrize("spread", [1.0, 4.0, 12.0])
 def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, monkeypatch, spread):
     """The tcgen05 kernel leaves out 64-observation chunks whose K* entries are all < 2^-44 sigma_f^2 for a cell tile
