@@ -922,7 +922,9 @@ int32_t tc_init(sbo_ctx* ctx) {
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(posterior_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
   if (e == cudaSuccess)
-    e = cudaFuncSetAttribute(posterior_tc_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_pair_smem_bytes());
+    e = cudaFuncSetAttribute(posterior_tc_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_pair_smem_bytes());
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(posterior_tc_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_pair_smem_bytes());
   if (e != cudaSuccess) {
     delete map;
     return cuda_fail(ctx, e, "tc_init: cudaFuncSetAttribute(max dynamic smem)");
@@ -1058,11 +1060,12 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    // dense full refresh over at least two row blocks: the K*-stationary pair kernel (SBO_TC_PAIR=0: off)
-    bool pair = !p.skip && !p.accumulate && p.j_lo == 0 && p.j_hi == p.n && p.n > BN && p.dbg_v == nullptr;
+    // full refresh over at least two row blocks: the K*-stationary pair kernel (SBO_TC_PAIR=0: off)
+    bool pair = !p.accumulate && p.j_lo == 0 && p.j_hi == p.n && p.n > BN && p.dbg_v == nullptr;
     if (const char* s = std::getenv("SBO_TC_PAIR")) pair = pair && std::atoi(s) != 0;
     if (pair) cfg.dynamicSmemBytes = tc_pair_smem_bytes();
-    const cudaError_t e = pair     ? cudaLaunchKernelEx(&cfg, posterior_tc_pair_kernel, tmap, p)
+    const cudaError_t e = pair     ? (p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_pair_kernel<true>, tmap, p)
+                                             : cudaLaunchKernelEx(&cfg, posterior_tc_pair_kernel<false>, tmap, p))
                           : p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, true>, tmap, p)
                                    : cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, false>, tmap, p);
     if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_kernel<2> (cluster launch)");

@@ -1,7 +1,7 @@
 // posterior_tc_pair.cuh -- included by posterior_tc.cu (inside namespace sbo::{anonymous}).
 //
-// The "K*-stationary" form of the tcgen05 posterior kernel for the dense full refresh (every chunk of every row
-// block, all rows of L^-1, CTA pairs).  A generated K* chunk (128 cells x 64 observations, fp16 hi/lo planes) is
+// The "K*-stationary" form of the tcgen05 posterior kernel for the full refresh (all rows of L^-1, CTA pairs; dense or
+// block-sparse walk: kSkip as in posterior_tc_kernel, one chunk mask per tile serves both row blocks of a pair).  A generated K* chunk (128 cells x 64 observations, fp16 hi/lo planes) is
 // contracted against TWO row blocks of L^-1 -- 512 accumulator columns, the whole of TMEM -- before its stage is
 // released, so a tile visits chunk k once per PAIR of row blocks: 24 generations per tile at n = 1024 instead of 40,
 // half as many at large n.  The generators (issue slots, MUFU, shared-memory stores) were what paced the
@@ -22,10 +22,6 @@
 #endif
 constexpr int kPairStagesA = SBO_PAIR_SA;
 constexpr int kPairStagesB = SBO_PAIR_SB;
-#ifndef SBO_PAIR_LAG
-#define SBO_PAIR_LAG 0
-#endif
-constexpr int kPairLag = SBO_PAIR_LAG;
 constexpr uint32_t kPairABytes = 2 * kABytes;              // hi + lo planes of one K* chunk: 32 KB
 constexpr uint32_t kPairBBytes = 2 * TcCfg<2>::kBBytes;    // hi + lo half-tiles of L^-1 held by one CTA: 32 KB
 
@@ -42,29 +38,38 @@ struct __align__(16) TcPairShared {
   float4 obs_y[kGenWarps][8];
   float4 obs_a[kGenWarps][8];
   float mu_part[2][3][BM];
+  uint32_t cmask[kThreadsTc / 32][kMaskWords];  // per warp: bit c set = chunk c is contracted for the current tile pair
 };
 
 constexpr size_t tc_pair_smem_bytes() {
   return 1024 + (size_t)kPairStagesA * kPairABytes + (size_t)kPairStagesB * kPairBBytes + sizeof(TcPairShared);
 }
 
-// visits of one tile in pipeline order: for every pair, chunks 0 .. chunks_of(last row block of the pair) - 1
-struct PairWalk {
-  int pi, npairs, nblocks, n_pad, kc, nch;
+// visits of one tile in pipeline order: for every pair, the contracted chunks below chunks_of(last row block of the pair)
+template <bool kSkip> struct PairWalk {
+  ChunkIter<kSkip> ci;
+  const uint32_t* mask;
+  int pi, npairs, nblocks, n_pad, nch;
   __device__ __forceinline__ int nch_of(int pair) const { return chunks_of(min(2 * pair + 1, nblocks - 1), n_pad); }
-  __device__ __forceinline__ void start(int nblocks_, int n_pad_) {
-    nblocks = nblocks_; n_pad = n_pad_; npairs = (nblocks + 1) / 2; pi = 0; kc = 0; nch = nch_of(0);
+  __device__ __forceinline__ void start(const uint32_t* m, int nblocks_, int n_pad_) {
+    mask = m; nblocks = nblocks_; n_pad = n_pad_; npairs = (nblocks + 1) / 2; pi = 0; nch = nch_of(0);
+    ci.reset(mask);
   }
   // chunk of the next visit (it belongs to pair `pi`), or -1 when the tile is done
   __device__ __forceinline__ int next() {
     while (pi < npairs) {
-      if (kc < nch) return kc++;
-      if (++pi < npairs) { kc = 0; nch = nch_of(pi); }
+      const int kc = ci.next();
+      if (kc < nch) return kc;
+      if (++pi < npairs) {
+        nch = nch_of(pi);
+        ci.reset(mask);
+      }
     }
     return -1;
   }
 };
 
+template <bool kSkip>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   constexpr int CG = 2;
@@ -86,6 +91,9 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   const int n_pad = (p.n + BK - 1) / BK * BK;
   const int nblocks = (p.n + BN - 1) / BN;
   const int npairs = (nblocks + 1) / 2;
+  const int nchunks = n_pad / BK;
+  uint32_t* cmask = sh->cmask[warp];
+  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip};
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 4; ++s) {
@@ -109,10 +117,12 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   if (warp == 0) {
     // =============================== TMA producer: B stages in consumption order ===============================
     uint32_t itb = 0;
-    auto load_b = [&](int jb, int kc) {
+    auto load_b = [&](int jb, int kc, bool fresh) {
       const int s = itb % kPairStagesB;
       const uint32_t ph = (itb / kPairStagesB) & 1u;
-      const int c = max(kc - jb * (BN / BK), 0);  // diagonal block: rows < 64 c hold zeros, the tile starts below them
+      // diagonal block: rows < 64 c hold zeros, the tile starts below them.  An accumulator's first contracted chunk
+      // runs at full N (it initialises every column), so its tile starts at the row block's first row.
+      const int c = fresh ? 0 : max(kc - jb * (BN / BK), 0);
       const int row = jb * BN + c * BK + (int)rank * ((int)TcCfg<2>::kBRows - c * (BK / 2));
       mbar_wait(&sh->empty_b[s], ph ^ 1u);
       const uint32_t bar = mapa(smem_u32(&sh->full_b[s]), 0);
@@ -125,14 +135,17 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       ++itb;
     };
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
       for (int pi = 0; pi < npairs; ++pi) {
         const int jb0 = 2 * pi;
         const bool has1 = jb0 + 1 < nblocks;
         const int nch0 = chunks_of(jb0, n_pad), nchl = has1 ? chunks_of(jb0 + 1, n_pad) : nch0;
-        const int lag = has1 ? kPairLag : 0;  // the second row block's MMAs trail the first one's by `lag` visits (see the issuer)
-        for (int t = 0; t < nchl + lag; ++t) {
-          if (t < nch0) load_b(jb0, t);
-          if (has1 && t >= lag) load_b(jb0 + 1, t - lag);
+        bool fresh0 = true, fresh1 = true;
+        ChunkIter<kSkip> ci;
+        ci.reset(cmask);
+        for (int kc = ci.next(); kc < nchl; kc = ci.next()) {
+          if (kc < nch0) { load_b(jb0, kc, fresh0); fresh0 = false; }
+          if (has1) { load_b(jb0 + 1, kc, fresh1); fresh1 = false; }
         }
       }
     }
@@ -140,56 +153,55 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     // =============================== MMA issuer (leader CTA; converged warp, one elected lane issues) ===============================
     uint32_t ita = 0, itb = 0, use0 = 0, use1 = 0;
     for (long long gt = group; rank == 0 && gt < ngtiles; gt += ngroups) {
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
       for (int pi = 0; pi < npairs; ++pi) {
         const int jb0 = 2 * pi;
         const bool has1 = jb0 + 1 < nblocks;
         const int nch0 = chunks_of(jb0, n_pad), nchl = has1 ? chunks_of(jb0 + 1, n_pad) : nch0;
-        // Issue order inside a pair: (row block 0, visit t) then (row block 1, visit t - lag).  lag = 1 would hide the
-        // epilogue still draining the second accumulator when a pair begins (there is no spare one: 2 x 256 columns = all
-        // of TMEM); measured equal to lag = 0 at n = 1024 / 2048 (2.03 / 7.16 ms), lag = 2 starves the K* ring (+12 %).
-        const int lag = has1 ? kPairLag : 0;
-        for (int t = 0; t < nchl + lag; ++t) {
+        ChunkIter<kSkip> ci;
+        ci.reset(cmask);
+        int kc = ci.next();
+        bool fresh0 = true, fresh1 = true;
+        for (int kn; kc < nchl; kc = kn, ++ita) {
+          kn = ci.next();  // the next contracted chunk: tells whether this visit is an accumulator's last
+          const int sa = ita % kPairStagesA;
+          mbar_wait(&sh->full_a[sa], (ita / kPairStagesA) & 1u);  // generators stored their planes
+          tc_fence_after();
+          const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(sa))), dal = umma_desc_sw128(smem_u32(a_lo(sa)));
 #pragma unroll
           for (int half = 0; half < 2; ++half) {
-            const int kc = half == 0 ? t : t - lag;
-            if (half == 0 ? kc >= nch0 : (!has1 || kc < 0)) continue;
+            if (half == 0 ? kc >= nch0 : !has1) continue;
             const int jb = jb0 + half;
-            const uint32_t va = ita + (uint32_t)kc;  // this visit's place in the A ring
-            const int sa = va % kPairStagesA;
-            if (half == 0 || kc >= nch0) {  // first use of the visit's K* stage
-              mbar_wait(&sh->full_a[sa], (va / kPairStagesA) & 1u);  // generators stored their planes
-              tc_fence_after();
-            }
-            const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(sa))), dal = umma_desc_sw128(smem_u32(a_lo(sa)));
-            if (kc == 0) {  // first MMA into this accumulator: the epilogue must have drained its previous contents
+            const bool fresh = half == 0 ? fresh0 : fresh1;
+            if (fresh) {  // first MMA into this accumulator: the epilogue must have drained its previous contents
               mbar_wait(&sh->tmem_empty[half], ((half == 0 ? use0 : use1) & 1u) ^ 1u);
               tc_fence_after();
-              if (half == 0) ++use0; else ++use1;
+              if (half == 0) { ++use0; fresh0 = false; } else { ++use1; fresh1 = false; }
             }
             const int sb = itb % kPairStagesB;
             mbar_wait(&sh->full_b[sb], (itb / kPairStagesB) & 1u);  // TMA bytes of both CTAs landed
             tc_fence_after();
             const uint64_t dbh = umma_desc_sw128(smem_u32(b_hi(sb))), dbl = umma_desc_sw128(smem_u32(b_lo(sb)));
-            const uint32_t c = (uint32_t)max(kc - jb * (BN / BK), 0);
+            // diagonal block, chunk c: columns < 64 c of the accumulator get no contribution (zeros of L^-1)
+            const uint32_t c = fresh ? 0u : (uint32_t)max(kc - jb * (BN / BK), 0);
             const uint32_t idesc = idesc_f16<CG>(BN - c * BK), d_col = tmem_base + half * BN + c * BK;
             if (elect_one()) {
 #pragma unroll
               for (int ks = 0; ks < BK / UK; ++ks) {
                 const uint64_t adv = (uint64_t)((ks * UK * 2) >> 4);
-                umma_f16<CG>(d_col, dal + adv, dbh + adv, idesc, (kc == 0 && ks == 0) ? 0u : 1u);
+                umma_f16<CG>(d_col, dal + adv, dbh + adv, idesc, (fresh && ks == 0) ? 0u : 1u);
                 umma_f16<CG>(d_col, dah + adv, dbl + adv, idesc, 1u);
                 umma_f16<CG>(d_col, dah + adv, dbh + adv, idesc, 1u);
               }
               umma_commit<CG>(&sh->empty_b[sb]);
               if (half == 1 || !has1) umma_commit<CG>(&sh->empty_a[sa]);  // last use: K* stage reusable once these MMAs have read it
-              if (half == 0 && kc == nch0 - 1) umma_commit<CG>(&sh->tmem_full[0]);  // first row block complete
-              if (half == 1 && kc == nchl - 1) umma_commit<CG>(&sh->tmem_full[1]);
+              if (half == 0 && kn >= nch0) umma_commit<CG>(&sh->tmem_full[0]);  // first row block complete
+              if (half == 1 && kn >= nchl) umma_commit<CG>(&sh->tmem_full[1]);
             }
             __syncwarp();
             ++itb;
           }
         }
-        ita += (uint32_t)nchl;
       }
     }
   } else if (warp >= 4 && warp < 8) {
@@ -199,12 +211,17 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     uint32_t use0 = 0, use1 = 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
       const long long tile = gt * CG + rank;
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
       float rs_hi = 0.f, rs_lo = 0.f;  // sum of squares of this cell's row of V (scaled), double-word fp32
+      ChunkIter<kSkip> ci0;
+      ci0.reset(cmask);
+      const int first_chunk = ci0.next();
       for (int pi = 0; pi < npairs; ++pi) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           const int jb = 2 * pi + half;
           if (jb >= nblocks) continue;
+          if (first_chunk >= chunks_of(jb, n_pad)) continue;  // row block skipped by the issuer: V = 0
           const uint32_t use = half == 0 ? use0++ : use1++;
           mbar_wait(&sh->tmem_full[half], use & 1u);
           tc_fence_after();
@@ -267,8 +284,9 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       const float oxh = (float)ox0, oxl = (float)(ox0 - (double)oxh);
       const float oyh = (float)oy0, oyl = (float)(oy0 - (double)oyh);
       float mu_hi = 0.f, mu_lo = 0.f;
-      PairWalk w, scout;
-      w.start(nblocks, n_pad);
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      PairWalk<kSkip> w, scout;
+      w.start(cmask, nblocks, n_pad);
       scout = w;
       const int first0 = scout.next(), first1 = scout.next();
       uint32_t vi = 0;  // visit parity per tile: mu must not depend on the tiles processed before (see posterior_tc_kernel)
