@@ -306,13 +306,15 @@ def main():
         else:
             peak, peak_note = 75.0, "fp32 FMA pipe, nominal (the SIMT cross-check kernel; not the product path)"
         achieved = flops / (ms_post * 1e-3) / 1e12
+        kname = {1: "posterior_simt_kernel", 2: "posterior_tc_kernel", 3: "posterior_thin_kernel", 4: "posterior_f64_kernel"}.get(outs[-1].kernel_used, "?")
+        if outs[-1].kernel_used == 2 and p.n > 256 and ctx.tc_plan()[0] == 2 and os.environ.get("SBO_TC_PAIR", "1") != "0":
+            kname = "posterior_tc_pair_kernel"   # full refresh over >= 2 row blocks of L^-1: the K*-stationary form (posterior_tc_pair.cuh)
         traffic = None
         try:   # per-launch DRAM bytes of the dominant kernel from the committed ncu --set full capture of this workload
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic_r01.json")))
-            traffic = tj[{1: "posterior_simt_kernel", 2: "posterior_tc_kernel", 4: "posterior_f64_kernel"}[outs[-1].kernel_used]][args.workload]["dram_bytes_per_launch"]
+            traffic = tj[kname][args.workload]["dram_bytes_per_launch"]
         except Exception:
             traffic = None
-        kname = {1: "posterior_simt_kernel", 2: "posterior_tc_kernel", 3: "posterior_thin_kernel", 4: "posterior_f64_kernel"}.get(outs[-1].kernel_used, "?")
         roofline = {"bound": "tensor" if used_tc else ("fp64" if p.precision == "fp64" else "fp32"), "achieved": achieved, "peak": peak,
                     "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic, "kernel": kname,
                     "peak_source": peak_note, "ms_kernel": ms_post, "credited_flops_per_launch": flops,
