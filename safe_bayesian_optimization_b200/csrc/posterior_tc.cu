@@ -46,6 +46,9 @@ namespace {
 #ifndef SBO_TC_CLOCKS
 #define SBO_TC_CLOCKS 0
 #endif
+// SBO_TC_DBG bit flags switch parts of the kernel off for timing experiments (results are then wrong by design):
+// they only exist in -DSBO_TC_CLOCKS=1 builds.
+#define TC_DBG(p, bit) (SBO_TC_CLOCKS && ((p).dbg & (bit)))
 
 constexpr int BM = 128;          // cells per CTA tile (UMMA M per CTA)
 constexpr int BN = 256;          // rows of L^-1 per accumulator (UMMA N)
@@ -583,7 +586,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           mbar_wait(&sh->empty[s], ph ^ 1u);
           const uint32_t bar = CG == 1 ? smem_u32(&sh->full[s]) : mapa(smem_u32(&sh->full[s]), 0);
           if (elect_one()) {
-            if (p.dbg & 64) {
+            if TC_DBG(p, 64) {
               if (rank == 0) mbar_arrive_local(&sh->full[s]);
             } else {
               if (rank == 0) mbar_arrive_expect_tx(&sh->full[s], 2 * Cfg::kBBytes * CG);
@@ -633,7 +636,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             for (int ks = 0; ks < BK / UK; ++ks) {
               const uint64_t adv = (uint64_t)((ks * UK * 2) >> 4);  // +32 bytes along K inside the swizzle row
               umma_f16<CG>(d_col, dal + adv, dbh + adv, idesc, (fresh && ks == 0) ? 0u : 1u);
-              if (p.dbg & 4) continue;
+              if TC_DBG(p, 4) continue;
               umma_f16<CG>(d_col, dah + adv, dbl + adv, idesc, 1u);
               umma_f16<CG>(d_col, dah + adv, dbh + adv, idesc, 1u);
             }
@@ -672,7 +675,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         for (int c = 0; c < BN / 32; ++c) {
           const int jc = j0 + c * 32;
           if (jc >= p.j_hi || jc + 32 <= p.j_lo) continue;  // columns outside the contracted rows (warp-uniform)
-          if (p.dbg & 2) continue;
+          if TC_DBG(p, 2) continue;
           uint32_t v[32];
           tmem_ld32(taddr + c * 32, v);
           tmem_ld_wait();
@@ -768,7 +771,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         const uint32_t ph = (it / kStages) & 1u;
         const long long ck0 = clk_on ? clock64() : 0;
         // per-observation terms of this half-chunk, one observation per lane
-        if (!(p.dbg & 16)) {
+        if (!TC_DBG(p, 16)) {
           const int k = kc * BK + oh * 32 + lane;
           if (c_next != kc) {  // warp-uniform
             o_next = p.obs[k];
@@ -793,7 +796,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t hi[8], lo[8];
-          if (p.dbg & 1) {
+          if TC_DBG(p, 1) {
 #pragma unroll
             for (int e = 0; e < 8; ++e) { hi[e] = 0x3c003c00u; lo[e] = 0u; }
           } else if (last) gen16<true>(sh->obs_x[gw] + 4 * half, sh->obs_y[gw] + 4 * half, sh->obs_a[gw] + 4 * half, ncx2, hi, lo, mu2);
@@ -803,7 +806,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             mbar_wait(&sh->empty[s], ph ^ 1u);  // MMAs that read this stage have completed
             ck2 = clk_on ? clock64() : 0;
           }
-          if (!(p.dbg & 8)) {
+          if (!TC_DBG(p, 8)) {
             const uint32_t u0 = (uint32_t)(oh * 4 + half * 2);
             const uint32_t off0 = ((u0 ^ swz) << 4), off1 = (((u0 + 1u) ^ swz) << 4);
             *reinterpret_cast<uint4*>(pa_hi + off0) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
@@ -818,7 +821,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           two_sum_acc(mu_hi, mu_lo, m0 + m1);
         }
         const long long ckD = clk_on ? clock64() : 0;
-        if (!(p.dbg & 32)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
+        if (!TC_DBG(p, 32)) fence_proxy_async();  // generic-proxy stores -> visible to the tensor core (async proxy)
         __syncwarp();
         const long long ckE = clk_on ? clock64() : 0;
         if (lane == 0) {
