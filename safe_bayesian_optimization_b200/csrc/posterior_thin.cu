@@ -22,6 +22,7 @@
 // tcgen05 kernel.  fp64 mode is plain fp64.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -221,6 +222,105 @@ posterior_thin_kernel(ThinParams p, T* __restrict__ mu_out, T* __restrict__ s2_o
   }
 }
 
+// ---- fp64, one new row, large grids: two-dimensional register tile ------------------------------------------------
+// The kernel above reads R staged products per observation and thread as broadcast LDS.128 (two doubles each) for R
+// DFMAs: 16 LDS.128 per 32 DFMA at R = 32, and a warp-wide broadcast of 16 bytes still costs the shared-memory pipe
+// its four 8-lane phases -- it ran at 26 % of the DFMA rate, bound by those reads.  Here a thread owns 8 x 8 cells
+// (columns 2 tx + 32 i + {0,1}, rows 2 ty + 32 i + {0,1} of a 128 x 128-cell CTA tile), the CTA stages BOTH factors
+// per observation -- a[c] = ex(col c, j) and b[r] = sigma_f^2 ey(row r, j) Linv[new row][j] -- and the inner loop is
+// 8 LDS.128 for 64 DFMA: u[r][c] += b[r] a[c].  One exp per 64 cell-observations instead of one per 32.
+constexpr int kT2 = 128;      // cells per CTA tile edge
+constexpr int kT2Ld = kT2 + 8; // row stride of the staged factors (doubles): 16-byte aligned rows, staggered banks
+constexpr int kT2Chunk = 32;  // observations staged per pass: 2 x 32 x 136 doubles = 68 KB
+
+// Staging by recurrence: along a grid line with pitch s h the RBF factor obeys
+//   e(i+1) = e(i) g(i),  g(i) = exp(-(2 (X_i - x_j) s h + s^2 h^2) / 2 l^2),  g(i+1) = g(i) Q,  Q = exp(-s^2 h^2 / l^2),
+// so a thread that owns observation jj and the 16 cells sg, sg + 8, ..., sg + 120 of the tile edge pays two exp and
+// thirty multiplications instead of sixteen exp (the fp64 exp is ~45 DFMA-equivalents; with one exp per staged value the
+// staging cost 70 % of the inner loop).  Sixteen steps: relative error ~16 ulp, far inside the fp64 tolerance.  The
+// host only selects this kernel when a tile edge spans <= 4 length-scales: an anchor that underflows then sits >= 33
+// length-scales from every cell of its segment, whose true factors are < e^-560.
+__global__ void __launch_bounds__(kThinThreads, 1)
+posterior_thin2d_f64_kernel(ThinParams p, double* __restrict__ mu_out, double* __restrict__ s2_out) {
+  extern __shared__ __align__(16) double sm2[];
+  double* a_s = sm2;                        // [kT2Chunk][kT2Ld]
+  double* b_s = sm2 + kT2Chunk * kT2Ld;     // [kT2Chunk][kT2Ld]
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int sg = tid & 7, jj = tid >> 3;    // staging role: observation jj of the chunk, cells sg + 8 i of the tile edge
+  const int tiles_x = (p.W + kT2 - 1) / kT2, tiles_y = (p.rows_local + kT2 - 1) / kT2;
+  const long long ntiles = (long long)tiles_x * tiles_y;
+  const double w = p.w[p.row_lo];
+  const double* lrow = p.Linv + (size_t)p.row_lo * p.ld;
+  const double sx = 8.0 * p.rx, sy = 8.0 * p.ry;
+  const double qx = exp(-2.0 * sx * sx * p.inv2l2), qy = exp(-2.0 * sy * sy * p.inv2l2);
+
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int r0 = (int)(tile / tiles_x) * kT2, col0 = (int)(tile % tiles_x) * kT2;
+    const double cx0 = cell_coord(p.x0, p.rx, col0 + sg), cy0 = cell_coord(p.y0, p.ry, p.row0 + r0 + sg);
+    double acc[8][8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+#pragma unroll
+      for (int c = 0; c < 8; ++c) acc[r][c] = 0.0;
+
+    for (int k0 = 0; k0 < p.n; k0 += kT2Chunk) {
+      {
+        const int j = k0 + jj;
+        double ox = 0.0, oy = 0.0, ol = 0.0;  // observations beyond n: Linv = 0, so b = 0
+        if (j < p.n) {
+          const double2 od = *reinterpret_cast<const double2*>(p.xy + 2 * (size_t)j);
+          ox = od.x; oy = od.y; ol = p.sf2 * lrow[j];
+        }
+        const double dx = cx0 - ox, dy = cy0 - oy;
+        double ea = exp(-dx * dx * p.inv2l2), ga = exp(-(2.0 * dx * sx + sx * sx) * p.inv2l2);
+        double eb = exp(-dy * dy * p.inv2l2) * ol, gb = exp(-(2.0 * dy * sy + sy * sy) * p.inv2l2);
+        double* da = a_s + jj * kT2Ld + sg;
+        double* db = b_s + jj * kT2Ld + sg;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          da[8 * i] = ea;
+          db[8 * i] = eb;
+          ea *= ga; ga *= qx;
+          eb *= gb; gb *= qy;
+        }
+      }
+      __syncthreads();
+#pragma unroll 2
+      for (int q = 0; q < kT2Chunk; ++q) {
+        double a[8], b[8];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const double2 av = *reinterpret_cast<const double2*>(&a_s[q * kT2Ld + 2 * tx + 32 * i]);
+          const double2 bv = *reinterpret_cast<const double2*>(&b_s[q * kT2Ld + 2 * ty + 32 * i]);
+          a[2 * i] = av.x; a[2 * i + 1] = av.y;
+          b[2 * i] = bv.x; b[2 * i + 1] = bv.y;
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+          for (int c = 0; c < 8; ++c) acc[r][c] = fma(b[r], a[c], acc[r][c]);
+      }
+      __syncthreads();
+    }
+
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int row = r0 + 2 * ty + 32 * (r >> 1) + (r & 1);
+      if (row >= p.rows_local) continue;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const int col = col0 + 2 * tx + 32 * (c >> 1) + (c & 1);
+        if (col < p.W) {
+          const long long lc = (long long)row * p.W + col;
+          const double u = acc[r][c];
+          s2_out[lc] = s2_out[lc] - u * u;
+          mu_out[lc] = fma(w, u, mu_out[lc]);
+        }
+      }
+    }
+  }
+}
+
 template <typename T, int KR, int C, int R>
 void launch_thin(sbo_ctx* ctx, const ThinParams& p) {
   const int span = kThinThreads * C;
@@ -258,6 +358,21 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
       default: launch_thin<float, 8, 1, 4>(ctx, p); break;
     }
   } else {
+    const long long tiles2d = (long long)((p.W + kT2 - 1) / kT2) * ((p.rows_local + kT2 - 1) / kT2);
+    const char* e2d = std::getenv("SBO_THIN_2D");
+    const bool span_ok = kT2 * std::max(std::fabs(p.rx), std::fabs(p.ry)) <= 4.0 * ctx->cfg.length_scale;  // see the staging recurrence
+    if (kr == 1 && tiles2d >= ctx->sm_count && span_ok && !(e2d && std::atoi(e2d) == 0)) {   // enough 128 x 128 tiles for every SM
+      const size_t smem = (size_t)2 * kT2Chunk * kT2Ld * sizeof(double);
+      static bool attr_set = false;
+      if (!attr_set) {
+        cudaFuncSetAttribute(posterior_thin2d_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_set = true;
+      }
+      const unsigned grid = (unsigned)std::min<long long>(tiles2d, ctx->sm_count);
+      posterior_thin2d_f64_kernel<<<grid, kThinThreads, smem, ctx->stream>>>(p, static_cast<double*>(ctx->d_mu), static_cast<double*>(ctx->d_s2));
+      SBO_LAUNCH_CHECK(ctx, "posterior_thin2d_f64_kernel");
+      return SBO_OK;
+    }
     switch (kr) {
       case 1: launch_thin<double, 1, 1, 32>(ctx, p); break;   // one exp per 32 cells: the fp64 exp is ~14 DFMA-equivalents
       case 2: launch_thin<double, 2, 1, 16>(ctx, p); break;

@@ -241,6 +241,31 @@ def test_long_rank1_chain_stays_in_tolerance(pkg, oracle, coracle, precision):
         check_argmax(res, ref, band, mask)
 
 
+def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, monkeypatch):
+    """fp64, one new row, >= one 128 x 128 tile per SM: the 2-D register-tile kernel.  Same projections as the
+    column-strip kernel (SBO_THIN_2D=0), different summation order: agreement to fp64 rounding; ragged tile edges."""
+    n0 = 130
+    p = S.make_problem("C5", n=n0 + 2, W=1990, H=1250)
+    out = {}
+    for flag in ("0", "1"):
+        monkeypatch.setenv("SBO_THIN_2D", flag)
+        with make_ctx(pkg, p, precision="fp64", kernel="auto", max_obs=n0 + 2) as ctx:
+            ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+            ctx.set_observations(p.xy[:n0], p.y[:n0])
+            ctx.step(p.beta, p.f_min, want_mask=False)
+            for t in range(2):
+                ctx.append_observations(p.xy[n0 + t:n0 + t + 1], p.y[n0 + t:n0 + t + 1])
+                res, _ = ctx.step(p.beta, p.f_min, incremental=True, want_mask=False)
+                assert res.kernel_used == 3
+            out[flag] = (ctx.mu(), ctx.sigma2())
+            if flag == "1":   # and against a full refresh of the same observation set
+                full, _ = ctx.step(p.beta, p.f_min, want_mask=False)
+                mu_f, s2_f = ctx.mu(), ctx.sigma2()
+    scale = np.abs(mu_f).max()
+    assert np.abs(out["1"][0] - out["0"][0]).max() <= 1e-12 * scale and np.abs(out["1"][1] - out["0"][1]).max() <= 1e-12
+    assert np.abs(out["1"][0] - mu_f).max() <= 1e-10 * scale and np.abs(out["1"][1] - s2_f).max() <= 1e-10
+
+
 @pytest.mark.parametrize("spread", [1.0, 4.0, 12.0])
 def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, monkeypatch, spread):
     """The tcgen05 kernel leaves out 64-observation chunks whose K* entries are all < 2^-44 sigma_f^2 for a cell tile
