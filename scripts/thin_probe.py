@@ -27,3 +27,4 @@ run("C5", 8192, 4096, 256, "fp64", [1, 2, 4, 8])
 run("C5", 8192, 4096, 1024, "fp64", [1])   # >= one 128 x 128 tile per SM: the 2-D tile kernel
 os.environ["SBO_THIN_2D"] = "0"
 run("C5", 8192, 4096, 1024, "fp64", [1])
+run("C4", 16384, 8192, 512, "fp32", [1])

@@ -241,15 +241,17 @@ def test_long_rank1_chain_stays_in_tolerance(pkg, oracle, coracle, precision):
         check_argmax(res, ref, band, mask)
 
 
-def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, monkeypatch):
-    """fp64, one new row, >= one 128 x 128 tile per SM: the 2-D register-tile kernel.  Same projections as the
-    column-strip kernel (SBO_THIN_2D=0), different summation order: agreement to fp64 rounding; ragged tile edges."""
+@pytest.mark.parametrize("precision", ["fp64"])
+def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, monkeypatch, precision):
+    """One new row, >= one 128 x 128 tile per SM: the 2-D register-tile kernels.  Same projections as the column-strip
+    kernel (SBO_THIN_2D=0), different summation order: agreement to rounding; ragged tile edges; and against a full
+    refresh of the same observation set."""
     n0 = 130
     p = S.make_problem("C5", n=n0 + 2, W=1990, H=1250)
     out = {}
     for flag in ("0", "1"):
         monkeypatch.setenv("SBO_THIN_2D", flag)
-        with make_ctx(pkg, p, precision="fp64", kernel="auto", max_obs=n0 + 2) as ctx:
+        with make_ctx(pkg, p, precision=precision, kernel="auto" if precision == "fp64" else "tcgen05", max_obs=n0 + 2) as ctx:
             ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
             ctx.set_observations(p.xy[:n0], p.y[:n0])
             ctx.step(p.beta, p.f_min, want_mask=False)
@@ -257,13 +259,14 @@ def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, monkeypatch):
                 ctx.append_observations(p.xy[n0 + t:n0 + t + 1], p.y[n0 + t:n0 + t + 1])
                 res, _ = ctx.step(p.beta, p.f_min, incremental=True, want_mask=False)
                 assert res.kernel_used == 3
-            out[flag] = (ctx.mu(), ctx.sigma2())
-            if flag == "1":   # and against a full refresh of the same observation set
-                full, _ = ctx.step(p.beta, p.f_min, want_mask=False)
-                mu_f, s2_f = ctx.mu(), ctx.sigma2()
+            out[flag] = (ctx.mu().astype(np.float64), ctx.sigma2().astype(np.float64))
+            if flag == "1":
+                ctx.step(p.beta, p.f_min, want_mask=False)
+                mu_f, s2_f = ctx.mu().astype(np.float64), ctx.sigma2().astype(np.float64)
     scale = np.abs(mu_f).max()
-    assert np.abs(out["1"][0] - out["0"][0]).max() <= 1e-12 * scale and np.abs(out["1"][1] - out["0"][1]).max() <= 1e-12
-    assert np.abs(out["1"][0] - mu_f).max() <= 1e-10 * scale and np.abs(out["1"][1] - s2_f).max() <= 1e-10
+    tight, loose = (1e-12, 1e-10) if precision == "fp64" else (2e-6, 1e-5)
+    assert np.abs(out["1"][0] - out["0"][0]).max() <= tight * scale and np.abs(out["1"][1] - out["0"][1]).max() <= tight
+    assert np.abs(out["1"][0] - mu_f).max() <= loose * scale and np.abs(out["1"][1] - s2_f).max() <= loose
 
 
 @pytest.mark.parametrize("spread", [1.0, 4.0, 12.0])
