@@ -325,7 +325,7 @@ def main():
             if skipping:   # block-sparse K*: the credited (dense triangular) flops include work that is never executed
                 roofline["executed_over_credited"] *= kept
                 roofline["block_sparse"] = {"kept_fraction_estimate": kept,
-                                            "note": "chunks of 64 observations whose K* entries are all < 2^-44 sigma_f^2 for a "
+                                            "note": "chunks of 64 observations whose K* entries are all < 2^-b sigma_f^2 (b = 36..60, bound 1e-7 sigma_f^2 on sigma^2; DESIGN 3.1) for a "
                                                     "cell tile are skipped; frac counts the dense triangular flops, so it can "
                                                     "exceed 1/3 (SBO_TC_SKIP=0 runs the dense walk)"}
         cpu = None

@@ -59,7 +59,6 @@ constexpr int kGenWarps = 16;
 constexpr uint32_t kABytes = BM * BK * 2;   // 16 KB per plane
 constexpr uint32_t kTmemCols = 512;
 constexpr int kMaskWords = 16;         // chunk masks cover 512 chunks = 32 768 observations; beyond that: dense
-constexpr float kSkipBits = 44.f;      // K* < 2^-44 sigma_f^2 over a whole 128-cell x 64-observation tile: skipped
 
 template <int CG> struct TcCfg {
   static constexpr uint32_t kBRows = BN / CG;                    // rows of a B tile held by one CTA
@@ -100,7 +99,8 @@ struct TcParams {
   float sf2, prior_mean;
   float* dbg_v;            // debug: V of tile 0 ([128][n_cap]) when non-null
   const float4* bbox;      // [n_cap / 64] scaled bounding box (xmin, xmax, ymin, ymax) of every 64-observation chunk
-  int skip;                // 1: chunks whose K* entries are all below 2^-kSkipBits sigma_f^2 for a tile are not contracted
+  int skip;                // 1: chunks whose K* entries are all below 2^-skip_bits sigma_f^2 for a tile are not contracted
+  float skip_bits;         // tc_skip_bits(): chosen so that everything skipped moves sigma^2 by < 1e-7 sigma_f^2
   long long* dbg_clk;      // SBO_TC_CLK=1: per-role cycle counters of cluster 0 (timing forensics)
   int dbg;                 // SBO_TC_DBG (timing experiments only, results are wrong): 1 generators skip the K* math, 2 epilogue skips the TMEM reads, 4 one MMA pass instead of three
 };
@@ -271,7 +271,7 @@ __device__ __forceinline__ int chunks_of(int jb, int n_pad) { return min(n_pad, 
 // ---- block sparsity of K* ------------------------------------------------------------------------
 // The observations are stored in spatial order (sbo_set_observations), so a chunk of 64 consecutive ones
 // covers a small box, and K*[cell, k] = sigma_f^2 2^-(d^2) in the scaled coordinates.  A chunk whose box is
-// farther than sqrt(kSkipBits) from every cell of the tile (pair) contributes less than 2^-44 sigma_f^2 per
+// farther than sqrt(skip_bits) from every cell of the tile (pair) contributes less than 2^-skip_bits sigma_f^2 per
 // entry -- below the fp16 split's own resolution (2^-22) squared -- and is left out by every role alike:
 // each warp builds the same bit mask for itself (no cross-warp hand-over) and walks its set bits.
 __device__ __forceinline__ float box_dist2(const float4 b, float xlo, float xhi, float y) {
@@ -285,6 +285,7 @@ struct MaskGeom {  // by value: taking the address of the kernel parameter block
   double x0, y0, rx, ry, xscale;
   const float4* bbox;
   int row0, skip;
+  float skip_bits;
 };
 
 template <int CG>
@@ -313,7 +314,7 @@ __device__ __noinline__ void build_chunk_mask(uint32_t* mask, const MaskGeom p, 
         const float4 b = p.bbox[c];
         on = false;
 #pragma unroll
-        for (int t = 0; t < CG; ++t) on = on || box_dist2(b, xlo[t], xhi[t], yy[t]) <= kSkipBits + 0.5f;
+        for (int t = 0; t < CG; ++t) on = on || box_dist2(b, xlo[t], xhi[t], yy[t]) <= p.skip_bits + 0.5f;
       }
     }
     const uint32_t bits = __ballot_sync(0xffffffffu, on);
@@ -544,7 +545,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   const int jb_lo = p.j_lo / BN, jb_hi = (p.j_hi + BN - 1) / BN;
   const int nchunks = n_pad / BK;
   uint32_t* cmask = sh->cmask[warp];
-  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip};
+  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip, p.skip_bits};
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -962,6 +963,16 @@ int32_t tc_pack_observations(sbo_ctx* ctx) {
 // almost every chunk matters everywhere)?  Host-side estimate on a sample of cell tiles: the fraction of
 // (row block, chunk) visits that the box test keeps, with the same boxes and cut-off as the kernel.  Cached
 // until the grid or the observations change.
+// Cut-off of the block-sparse walk, in bits: a chunk is skipped for a tile when every K* entry in it is < 2^-bits sigma_f^2.
+// Skipped entries move a component of v = L^-1 k* by at most 2^-bits sigma_f^2 ||row of L^-1||_1 <= 2^-bits sigma_f^2 sqrt(n / noise_var)
+// (||L^-1||_2 <= noise_var^-1/2), hence sigma^2 = sigma_f^2 - |v|^2 by at most 2 sqrt(n) |v| max|dv| <= 2 n sqrt(sigma_f^2 / noise_var) 2^-bits
+// relative to sigma_f^2.  bits is the smallest integer that keeps this under 1e-7 (1 % of the fp32 tolerance), never below 36.
+float tc_skip_bits(const sbo_ctx* ctx) {
+  const double sf2 = ctx->cfg.sigma_f * ctx->cfg.sigma_f;
+  const double bound = 2.0 * std::max(ctx->n, 1) * std::sqrt(sf2 / std::max(ctx->cfg.noise_var, 1e-300)) * 1e7;
+  return (float)std::min(60.0, std::max(36.0, std::ceil(std::log2(bound))));
+}
+
 bool tc_plan_skip(sbo_ctx* ctx) {
   if (!ctx->tc_skip) return false;
   if (ctx->tc_skip_plan >= 0) return ctx->tc_skip_plan != 0;
@@ -981,6 +992,7 @@ bool tc_plan_skip(sbo_ctx* ctx) {
   }
   const int rows = ctx->row1 - ctx->row0, tiles_per_row = (ctx->W + BM - 1) / BM;
   const int nblocks = (n + BN - 1) / BN;
+  const double bits = tc_skip_bits(ctx);
   const int sr = std::min(rows, 24), sc = std::min(tiles_per_row, 24);
   double kept = 0.0, total = 0.0;
   for (int a = 0; a < sr; ++a)
@@ -993,7 +1005,7 @@ bool tc_plan_skip(sbo_ctx* ctx) {
         const double dx = std::max(std::max(box[4 * c] - xhi, xlo - box[4 * c + 1]), 0.0);
         const double dy = std::max(std::max(box[4 * c + 2] - y, y - box[4 * c + 3]), 0.0);
         total += wgt;
-        if (dx * dx + dy * dy <= kSkipBits + 0.5) kept += wgt;
+        if (dx * dx + dy * dy <= bits + 0.5) kept += wgt;
       }
     }
   ctx->tc_kept_frac = total > 0.0 ? kept / total : 1.0;
@@ -1029,6 +1041,7 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.dbg_v = g_dbg_v;
   p.bbox = reinterpret_cast<const float4*>(ctx->d_chunk_bbox);
   p.skip = tc_plan_skip(ctx) ? 1 : 0;
+  p.skip_bits = tc_skip_bits(ctx);
   p.dbg = 0;
   if (const char* s = std::getenv("SBO_TC_DBG")) p.dbg = std::atoi(s);
   p.dbg_clk = nullptr;

@@ -93,7 +93,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   const int npairs = (nblocks + 1) / 2;
   const int nchunks = n_pad / BK;
   uint32_t* cmask = sh->cmask[warp];
-  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip};
+  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip, p.skip_bits};
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 4; ++s) {

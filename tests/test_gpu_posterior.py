@@ -271,7 +271,7 @@ def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, monkeypatch, precision):
 
 @pytest.mark.parametrize("spread", [1.0, 4.0, 12.0])
 def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, monkeypatch, spread):
-    """The tcgen05 kernel leaves out 64-observation chunks whose K* entries are all < 2^-44 sigma_f^2 for a cell tile
+    """The tcgen05 kernel leaves out 64-observation chunks whose K* entries are all < 2^-b sigma_f^2 for a cell tile (b from tc_skip_bits: sigma^2 moves by < 1e-7 sigma_f^2)
     (posterior_tc.cu, block sparsity of K*).  Stretching the domain (spread) makes most chunks, whole row blocks and
     for some tiles everything skippable; results must still meet the oracle and agree with the dense walk
     (SBO_TC_SKIP=0) far below the tolerance."""
