@@ -20,3 +20,21 @@ for prec in ("fp32", "fp64"):
         idx, cnt = ctx.compact_cells(border=True)
         cell = ctx.select_subgoal(idx[:50], p.goal) if cnt else -1
         print(prec, res.kernel_used, res.safe_count, cnt, cell)
+# fp64, one new row, >= one 128 x 128 tile per SM: the 2-D register-tile kernel; fp32 block-sparse pair kernel (spread-out domain)
+p = S.make_problem("C5", n=41, W=1990, H=1250)
+with pkg.SboContext(sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean,
+                    precision="fp64", max_obs=64, max_cells=p.m) as ctx:
+    ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+    ctx.set_observations(p.xy[:40], p.y[:40])
+    ctx.step(p.beta, p.f_min, want_mask=False)
+    ctx.append_observations(p.xy[40:41], p.y[40:41])
+    res, _ = ctx.step(p.beta, p.f_min, incremental=True, want_mask=False)
+    print("fp64 2-D tile", res.kernel_used, res.safe_count)
+p = S.make_problem("C3", n=1100, W=384, H=6)
+p.xy = p.xy * 6.0; p.rx *= 6.0; p.ry *= 6.0   # 6x wider domain: most chunks are out of reach of a tile
+with pkg.SboContext(sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean,
+                    precision="fp32", max_obs=1100, max_cells=p.m) as ctx:
+    ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+    ctx.set_observations(p.xy, p.y)
+    res, _ = ctx.step(p.beta, p.f_min, want_mask=False)
+    print("fp32 block-sparse", res.kernel_used, ctx.tc_plan(), res.safe_count)
