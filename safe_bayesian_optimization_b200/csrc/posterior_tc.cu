@@ -1043,10 +1043,11 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.skip = tc_plan_skip(ctx) ? 1 : 0;
   p.skip_bits = tc_skip_bits(ctx);
   p.dbg = 0;
-  if (const char* s = std::getenv("SBO_TC_DBG")) p.dbg = std::atoi(s);
+  if (SBO_TC_CLOCKS)
+    if (const char* s = std::getenv("SBO_TC_DBG")) p.dbg = std::atoi(s);
   p.dbg_clk = nullptr;
   static long long* d_clk = nullptr;
-  const bool want_clk = std::getenv("SBO_TC_CLK") != nullptr;
+  const bool want_clk = SBO_TC_CLOCKS && std::getenv("SBO_TC_CLK") != nullptr;
   if (want_clk) {
     if (!d_clk) cudaMalloc(&d_clk, 64 * sizeof(long long));
     cudaMemsetAsync(d_clk, 0, 64 * sizeof(long long), ctx->stream);

@@ -367,11 +367,9 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
     const bool span_ok = kT2 * std::max(std::fabs(p.rx), std::fabs(p.ry)) <= 4.0 * ctx->cfg.length_scale;  // see the staging recurrence
     if (kr == 1 && tiles2d >= ctx->sm_count && span_ok && !(e2d && std::atoi(e2d) == 0)) {   // enough 128 x 128 tiles for every SM
       const size_t smem = (size_t)2 * kT2Chunk * kT2Ld * sizeof(double);
-      static bool attr_set = false;
-      if (!attr_set) {
-        cudaFuncSetAttribute(posterior_thin2d_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = true;
-      }
+      // per device, so not cached in a process-wide flag (a process may hold contexts on several GPUs); a few microseconds
+      const cudaError_t ea = cudaFuncSetAttribute(posterior_thin2d_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (ea != cudaSuccess) return cuda_fail(ctx, ea, "posterior_thin2d_f64_kernel: cudaFuncSetAttribute(max dynamic smem)");
       const unsigned grid = (unsigned)std::min<long long>(tiles2d, ctx->sm_count);
       posterior_thin2d_f64_kernel<<<grid, kThinThreads, smem, ctx->stream>>>(p, static_cast<double*>(ctx->d_mu), static_cast<double*>(ctx->d_s2));
       SBO_LAUNCH_CHECK(ctx, "posterior_thin2d_f64_kernel");
