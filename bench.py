@@ -59,14 +59,50 @@ def credited_flops(m, n):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    """SM clock and clock-event reasons sampled DURING the timed region.  In-process NVML thread (every 2 ms: a C2 step
+    lasts 2 ms and the whole timed region tens of ms, which a 200 ms nvidia-smi loop sees once at best); nvidia-smi -lms 200
+    as the fallback when pynvml is missing."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASON_BITS = {0x4: "sw_power_cap", 0x8: "hw_slowdown", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown"}
 
     def __init__(self, device_index):
         self.idx, self.proc, self.file = device_index, None, None
+        self.thread, self.stop_flag, self.samples, self.nvml, self.handle = None, False, [], None, None
+
+    def _nvml_open(self):
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            import torch
+            uuid = str(torch.cuda.get_device_properties(self.idx).uuid)
+            uuid = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+            h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode() if hasattr(uuid, "encode") else uuid)
+        except Exception:
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.idx)
+        self.nvml, self.handle = pynvml, h
+
+    def _loop(self):
+        nv, h = self.nvml, self.handle
+        reasons_fn = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            try:
+                self.samples.append((nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM), int(reasons_fn(h)),
+                                     nv.nvmlDeviceGetPowerUsage(h) / 1000.0))
+            except Exception:
+                break
+            time.sleep(0.002)
 
     def start(self):
+        try:
+            import threading
+            self._nvml_open()
+            self.stop_flag, self.samples = False, []
+            self.thread = threading.Thread(target=self._loop, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.thread = None
         try:
             self.file = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
@@ -75,6 +111,22 @@ class ClockSampler:
             self.proc = None
 
     def stop(self):
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+            if not self.samples:
+                return None
+            sm = [x[0] for x in self.samples]
+            bits = 0
+            for x in self.samples:
+                bits |= x[1]
+            try:
+                mx = float(self.nvml.nvmlDeviceGetMaxClockInfo(self.handle, self.nvml.NVML_CLOCK_SM))
+            except Exception:
+                mx = float(max(sm))
+            return {"sm_mhz": float(np.median(sm)), "sm_min_mhz": float(min(sm)), "sm_max_mhz": mx,
+                    "reasons": sorted(n for b, n in self.REASON_BITS.items() if bits & b), "samples": len(sm),
+                    "power_w_max": float(max(x[2] for x in self.samples)), "how": "NVML, every 2 ms, during warm-up + timed steps"}
         if not self.proc:
             return None
         self.proc.terminate()
@@ -98,7 +150,8 @@ class ClockSampler:
                     reasons.add(name)
         if not sm:
             return None
-        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm),
+                "how": "nvidia-smi -lms 200"}
 
 
 def cpu_posterior_sample(p, seconds, prefer=None):
