@@ -269,13 +269,13 @@ def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, monkeypatch, precision):
     assert np.abs(out["1"][0] - mu_f).max() <= loose * scale and np.abs(out["1"][1] - s2_f).max() <= loose
 
 
-@pytest.mark.parametrize("spread", [1.0, 4.0, 12.0])
-def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, monkeypatch, spread):
+@pytest.mark.parametrize("spread,n", [(1.0, 1500), (4.0, 1500), (12.0, 1500), (4.0, 1100), (12.0, 2100)])  # 6, 5 and 9 row blocks
+def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, monkeypatch, spread, n):
     """The tcgen05 kernel leaves out 64-observation chunks whose K* entries are all < 2^-b sigma_f^2 for a cell tile (b from tc_skip_bits: sigma^2 moves by < 1e-7 sigma_f^2)
     (posterior_tc.cu, block sparsity of K*).  Stretching the domain (spread) makes most chunks, whole row blocks and
     for some tiles everything skippable; results must still meet the oracle and agree with the dense walk
     (SBO_TC_SKIP=0) far below the tolerance."""
-    p = S.make_problem("C3", n=1500, W=384, H=7)
+    p = S.make_problem("C3", n=n, W=384, H=7)
     p.xy = p.xy * spread
     p.rx, p.ry = p.rx * spread, p.ry * spread * 9.0        # a tall grid: rows far from each other
     ref = reference(oracle, coracle, p)
