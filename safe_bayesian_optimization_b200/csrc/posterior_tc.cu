@@ -581,9 +581,13 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           // chunk c = kc - 4 jb >= 0 of the diagonal block only meets rows >= 64 c of this row block (L^-1 is
           // lower triangular): the tile starts there and the MMA narrows to N = 256 - 64 c (see the issuer).
           // The first contracted chunk of a row block runs at full N: it initialises every accumulator column.
-          const int c = fresh ? 0 : max(kc - jb * (BN / BK), 0);
+          // Only rows j_lo .. j_hi of L^-1 count (the incremental step: the new rows; a full refresh: rows < n), so the
+          // tile and the MMA are also cut to the 64-row groups [c_min, c_end) of the row block that hold them.
+          const int c_min = min(max(p.j_lo - jb * BN, 0) / BK, BN / BK - 1);
+          const int c_end = max(min((p.j_hi - jb * BN + BK - 1) / BK, BN / BK), c_min + 1);
+          const int c = min(max(fresh ? 0 : kc - jb * (BN / BK), c_min), c_end - 1);
           fresh = false;
-          const int row = jb * BN + c * BK + (int)rank * ((int)Cfg::kBRows - c * (BK / 2));
+          const int row = jb * BN + c * BK + (int)rank * ((c_end - c) * (BK / CG));
           mbar_wait(&sh->empty[s], ph ^ 1u);
           const uint32_t bar = CG == 1 ? smem_u32(&sh->full[s]) : mapa(smem_u32(&sh->full[s]), 0);
           if (elect_one()) {
@@ -630,8 +634,11 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(s))), dal = umma_desc_sw128(smem_u32(a_lo(s)));
           const uint64_t dbh = umma_desc_sw128(smem_u32(b_hi(s))), dbl = umma_desc_sw128(smem_u32(b_lo(s)));
           // diagonal block, chunk c: columns < 64 c of the accumulator get no contribution (zeros of L^-1)
-          const uint32_t c = fresh ? 0u : (uint32_t)max(kc - jb * (BN / BK), 0);
-          const uint32_t idesc = idesc_f16<CG>(BN - c * BK), d_col = d_tmem + c * BK;
+          // ... and groups outside [c_min, c_end) hold no row in j_lo .. j_hi (see the producer)
+          const int c_min = min(max(p.j_lo - jb * BN, 0) / BK, BN / BK - 1);
+          const int c_end = max(min((p.j_hi - jb * BN + BK - 1) / BK, BN / BK), c_min + 1);
+          const uint32_t c = (uint32_t)min(max(fresh ? 0 : kc - jb * (BN / BK), c_min), c_end - 1);
+          const uint32_t idesc = idesc_f16<CG>((c_end - c) * BK), d_col = d_tmem + c * BK;
           if (elect_one()) {
 #pragma unroll
             for (int ks = 0; ks < BK / UK; ++ks) {
