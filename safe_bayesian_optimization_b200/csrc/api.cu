@@ -292,6 +292,8 @@ int32_t sbo_set_grid(sbo_ctx* ctx, double x0, double y0, double rx, double ry, i
   ctx->W = W; ctx->H = H; ctx->row0 = row0; ctx->row1 = row1;
   ctx->cell0 = (int64_t)row0 * W;
   ctx->m_local = m_local;
+  tc_eager_cancel(ctx);
+  ++ctx->grid_epoch;
   ctx->grid_set = true;
   ctx->tc_skip_plan = -1;
   ctx->posterior_valid = false;
@@ -333,6 +335,7 @@ int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, in
   if (!all_finite(xy, 2 * (size_t)n) || !all_finite(y, (size_t)n))
     return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_observations: NaN/Inf in the observations");
   SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  tc_eager_cancel(ctx);
   // spatial order: bands of two length-scales in y, by x inside a band (see sbo_copy_order)
   std::vector<int32_t> order((size_t)n);
   for (int i = 0; i < n; ++i) order[i] = i;
@@ -370,6 +373,7 @@ int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, in
   ctx->n_at_fit = n;
   const int32_t st = factor_full(ctx);
   if (st != SBO_OK) {
+    tc_eager_cancel(ctx);
     ctx->n = 0;  // the factor buffers were overwritten: no observations until the next successful fit
     ctx->order.clear();
     ctx->h_xy_sorted.clear();
@@ -394,6 +398,7 @@ int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y,
   if (!all_finite(xy, 2 * (size_t)k) || !all_finite(y, (size_t)k))
     return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_append_observations: NaN/Inf in the observations");
   SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+  tc_eager_cancel(ctx);
   std::vector<double> r((size_t)k);
   for (int i = 0; i < k; ++i) r[i] = y[i] - ctx->cfg.prior_mean;
   for (int done = 0; done < k;) {

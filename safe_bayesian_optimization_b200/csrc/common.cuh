@@ -79,6 +79,14 @@ struct sbo_ctx {
   float* d_obs_f32 = nullptr;    // [n_cap] float4: scaled observation coordinates as fp32 (hi, lo) pairs (posterior_tc.cu)
   void* tmap_planes = nullptr;   // host copy of the CUtensorMap (128 B), 256-row box
   bool planes_valid = false;
+  // eager first pairs of the posterior, launched by factor_full on a side stream (posterior_tc.cu)
+  cudaStream_t eager_stream = nullptr;
+  cudaEvent_t ev_eager_done = nullptr;
+  void* d_rs_part = nullptr;     // [rs_cap] float2 running row sums of the partial launch
+  int64_t rs_cap = 0;
+  bool eager_inflight = false;   // a partial result exists (or is being computed) for eager_n observations on grid eager_grid_epoch
+  int eager_pairs = 0, eager_n = 0;
+  uint64_t grid_epoch = 0, eager_grid_epoch = 0;
 
   // posterior of the last step (this shard)
   void* d_mu = nullptr;      // [max_cells] float or double
@@ -160,7 +168,7 @@ int32_t launch_select(sbo_ctx* ctx, const int32_t* d_frontier, int64_t F, double
 // factor.cu
 int32_t factor_full(sbo_ctx* ctx);                 // d_xy, d_r, n -> d_A (L), d_Linv, d_alpha, planes
 int32_t factor_append(sbo_ctx* ctx, int k);        // rows [n, n+k) already in d_xy / d_r
-int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end);
+int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end, cudaStream_t stream = nullptr);   // nullptr: ctx->stream
 
 // posterior_simt.cu
 int32_t launch_posterior_simt(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
@@ -171,7 +179,10 @@ void tc_plane_shifts(const sbo_config& cfg, int* shift_a, int* shift_b);
 int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
 void tc_destroy(sbo_ctx* ctx);
 bool tc_plan_skip(sbo_ctx* ctx);                   // worth walking chunk masks on this grid / observation set?
-int32_t tc_pack_observations(sbo_ctx* ctx);       // d_xy -> d_obs_f32 (scaled fp32 hi/lo pairs)
+int tc_eager_pairs(sbo_ctx* ctx);                   // row-block pairs factor_full may launch early (0: none)
+int32_t tc_eager_launch(sbo_ctx* ctx, int pairs, cudaEvent_t ready);
+void tc_eager_cancel(sbo_ctx* ctx);                 // waits for an eager launch in flight and drops its partial result
+int32_t tc_pack_observations(sbo_ctx* ctx, cudaStream_t stream = nullptr);       // d_xy -> d_obs_f32 (scaled fp32 hi/lo pairs)
 
 // posterior_thin.cu
 int32_t launch_posterior_f64(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);   // fp64 mode, DMMA

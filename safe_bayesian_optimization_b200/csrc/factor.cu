@@ -795,11 +795,12 @@ static int32_t ensure_factor_streams(sbo_ctx* ctx, int nblk) {
   return SBO_OK;
 }
 
-int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end) {
+int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end, cudaStream_t stream) {
   if (!ctx->d_planes || row_end <= row_begin) return SBO_OK;
+  if (!stream) stream = ctx->stream;
   const int ld = ctx->n_cap;
   dim3 grid((ld + 255) / 256, row_end - row_begin);
-  planes_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d_Linv, ld, row_begin, row_end, ld,
+  planes_kernel<<<grid, 256, 0, stream>>>(ctx->d_Linv, ld, row_begin, row_end, ld,
                                                reinterpret_cast<__half*>(ctx->d_planes), (size_t)ld * ld,
                                                std::ldexp(1.0, ctx->shift_b));
   SBO_LAUNCH_CHECK(ctx, "planes_kernel");
@@ -845,6 +846,10 @@ int32_t factor_full(sbo_ctx* ctx) {
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev_factor[0], st));
   SBO_CUDA(ctx, cudaStreamWaitEvent(sb, ctx->ev_factor[0], 0));
   const dim3 sub(1, 1, small ? 4 : 1);
+  // the first row-block pairs of the posterior start as soon as their rows of L^-1 are final (posterior_tc.cu)
+  const int eager_pairs = tc_eager_pairs(ctx);
+  const int eager_rows = eager_pairs * 512;
+  int planes_done = 0;
   for (int k = 0; k < nblk; ++k) {
     double* Dk = ctx->d_Dinv + (size_t)k * NB * NB;
     cudaEvent_t ev_d = ctx->ev_factor[1 + 2 * k], ev_t = ctx->ev_factor[2 + 2 * k];
@@ -879,6 +884,13 @@ int32_t factor_full(sbo_ctx* ctx) {
       trtri_row_kernel<128><<<k + 1, kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, k, Dk, ctx->d_Linv + (size_t)k * NB * ld, ld);
       SBO_LAUNCH_CHECK(ctx, "trtri_row_kernel");
     }
+    if (eager_rows > 0 && (k + 1) * NB == eager_rows) {   // rows [0, eager_rows) of L^-1 are final on sb
+      SBO_TRY(refresh_planes(ctx, 0, eager_rows, sb));
+      cudaEvent_t ev_ready = ctx->ev_factor[2 + 2 * (nblk - 1)];   // the last block has no panel: its "panel done" event is free
+      SBO_CUDA(ctx, cudaEventRecord(ev_ready, sb));
+      SBO_TRY(tc_eager_launch(ctx, eager_pairs, ev_ready));
+      planes_done = eager_rows;
+    }
     if (rem > 0) {
       SBO_CUDA(ctx, cudaStreamWaitEvent(sb, ev_t, 0));
       if (small) trtri_update_kernel<64><<<dim3(k + 1, rem, 4), kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, ctx->d_A, k);
@@ -894,7 +906,7 @@ int32_t factor_full(sbo_ctx* ctx) {
   }
   SBO_TRY(check_info(ctx, "sbo_set_observations"));
   SBO_TRY(compute_alpha(ctx, n));
-  SBO_TRY(refresh_planes(ctx, 0, ld));
+  SBO_TRY(refresh_planes(ctx, planes_done, ld));   // (rows the eager launch is reading were converted for it above)
   return SBO_OK;
 }
 

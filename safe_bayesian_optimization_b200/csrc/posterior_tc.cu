@@ -101,6 +101,9 @@ struct TcParams {
   const float4* bbox;      // [n_cap / 64] scaled bounding box (xmin, xmax, ymin, ymax) of every 64-observation chunk
   int skip;                // 1: chunks whose K* entries are all below 2^-skip_bits sigma_f^2 for a tile are not contracted
   float skip_bits;         // tc_skip_bits(): chosen so that everything skipped moves sigma^2 by < 1e-7 sigma_f^2
+  int pi_lo, pi_hi;        // pair kernel: row-block pairs [pi_lo, pi_hi) of this launch
+  int rs_mode;             // pair kernel: 0 whole job; 1 partial (store the running row sums in rs_part, no sigma^2 / mu); 2 resume from rs_part
+  float2* rs_part;         // [m_local] double-word fp32 running sums of a partial launch
   long long* dbg_clk;      // SBO_TC_CLK=1: per-role cycle counters of cluster 0 (timing forensics)
   int dbg;                 // SBO_TC_DBG (timing experiments only, results are wrong): 1 generators skip the K* math, 2 epilogue skips the TMEM reads, 4 one MMA pass instead of three
 };
@@ -946,6 +949,16 @@ int32_t tc_init(sbo_ctx* ctx) {
 }
 
 void tc_destroy(sbo_ctx* ctx) {
+  if (ctx->eager_stream) {
+    cudaStreamSynchronize(ctx->eager_stream);
+    cudaStreamDestroy(ctx->eager_stream);
+    cudaEventDestroy(ctx->ev_eager_done);
+    ctx->eager_stream = nullptr;
+  }
+  if (ctx->d_rs_part) cudaFree(ctx->d_rs_part);
+  ctx->d_rs_part = nullptr;
+  ctx->rs_cap = 0;
+  ctx->eager_inflight = false;
   if (ctx->tmap_planes) delete static_cast<CUtensorMap*>(ctx->tmap_planes);
   ctx->tmap_planes = nullptr;
   ctx->tc_ok = false;
@@ -953,14 +966,15 @@ void tc_destroy(sbo_ctx* ctx) {
 
 static float* g_dbg_v = nullptr;
 
-int32_t tc_pack_observations(sbo_ctx* ctx) {
+int32_t tc_pack_observations(sbo_ctx* ctx, cudaStream_t stream) {
+  if (!stream) stream = ctx->stream;
   if (!ctx->d_obs_f32) return fail(ctx, SBO_ERR_STATE, "packed observation buffer missing (fp32 mode only)");
   const double xscale = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
-  pack_obs_kernel<<<(ctx->n_cap + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_xy, ctx->n, ctx->n_cap, xscale,
+  pack_obs_kernel<<<(ctx->n_cap + 255) / 256, 256, 0, stream>>>(ctx->d_xy, ctx->n, ctx->n_cap, xscale,
                                                                      reinterpret_cast<float4*>(ctx->d_obs_f32));
   SBO_LAUNCH_CHECK(ctx, "pack_obs_kernel");
   const int nchunks = ctx->n_cap / BK;
-  chunk_bbox_kernel<<<(nchunks * 32 + 255) / 256, 256, 0, ctx->stream>>>(reinterpret_cast<const float4*>(ctx->d_obs_f32), ctx->n,
+  chunk_bbox_kernel<<<(nchunks * 32 + 255) / 256, 256, 0, stream>>>(reinterpret_cast<const float4*>(ctx->d_obs_f32), ctx->n,
                                                                          nchunks, reinterpret_cast<float4*>(ctx->d_chunk_bbox));
   SBO_LAUNCH_CHECK(ctx, "chunk_bbox_kernel");
   return SBO_OK;
@@ -1020,10 +1034,7 @@ bool tc_plan_skip(sbo_ctx* ctx) {
   return ctx->tc_skip_plan != 0;
 }
 
-int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
-  if (!ctx->tc_ok) return fail(ctx, SBO_ERR_STATE, "tcgen05 kernel not initialised");
-  if (ctx->m_local == 0) return SBO_OK;
-  TcParams p;
+static void tc_fill_params(sbo_ctx* ctx, TcParams& p, int j_lo, int j_hi, bool accumulate) {
   p.obs = reinterpret_cast<const float4*>(ctx->d_obs_f32);
   p.alpha = ctx->d_alpha_f32;
   p.mu = static_cast<float*>(ctx->d_mu);
@@ -1049,6 +1060,122 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   p.bbox = reinterpret_cast<const float4*>(ctx->d_chunk_bbox);
   p.skip = tc_plan_skip(ctx) ? 1 : 0;
   p.skip_bits = tc_skip_bits(ctx);
+  p.pi_lo = 0;
+  p.pi_hi = ((ctx->n + BN - 1) / BN + 1) / 2;
+  p.rs_mode = 0;
+  p.rs_part = nullptr;
+  p.dbg = 0;
+  p.dbg_clk = nullptr;
+}
+
+static cudaError_t tc_launch_pair(sbo_ctx* ctx, const TcParams& p, cudaStream_t stream, long long clusters) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(2 * clusters));
+  cfg.blockDim = dim3(kThreadsTc);
+  cfg.dynamicSmemBytes = tc_pair_smem_bytes();
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  const CUtensorMap& tmap = *static_cast<CUtensorMap*>(ctx->tmap_planes);
+  return p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_pair_kernel<true>, tmap, p)
+                : cudaLaunchKernelEx(&cfg, posterior_tc_pair_kernel<false>, tmap, p);
+}
+
+// ---- eager first pairs ------------------------------------------------------------------------------------------------
+// sbo_set_observations followed by sbo_step is the end-to-end step, and at n ~ 1000 a third of it is the fp64
+// factorisation: a chain of small kernels that keeps one or two SMs busy.  Rows 0 .. 512 P - 1 of L^-1 are final when the
+// chain is about half way, and the first P row-block pairs of the posterior need nothing else (no alpha: mu is summed in
+// the last pair).  So factor_full launches those pairs on a side stream as soon as their rows (and fp16 planes) exist,
+// on fewer CTAs than SMs so that the factor kernels keep finding free ones; the launch stores only the running row
+// sums (rs_mode 1).  The next full posterior on the same grid and observation set resumes from them (rs_mode 2: the
+// same sums in the same order, so sigma^2 and mu are bit-identical to the one-launch result).  Anything else that
+// touches the grid or the observations first waits for the side stream and drops the partial result.
+int tc_eager_pairs(sbo_ctx* ctx) {
+  static const bool off = std::getenv("SBO_TC_EAGER") && std::atoi(std::getenv("SBO_TC_EAGER")) == 0;
+  static const bool pair_off = std::getenv("SBO_TC_PAIR") && std::atoi(std::getenv("SBO_TC_PAIR")) == 0;
+  if (off || pair_off || !ctx->tc_ok || ctx->tc_cg != 2 || ctx->cfg.precision != SBO_FP32 || !ctx->grid_set || ctx->m_local == 0)
+    return 0;
+  if (ctx->cfg.kernel != SBO_KERNEL_AUTO && ctx->cfg.kernel != SBO_KERNEL_TCGEN05) return 0;
+  if (ctx->n < 2 * BN || ctx->n > 4096 || g_dbg_v) return 0;   // beyond ~4k observations the factorisation is a few % of the step
+  const long long ntiles = (long long)(ctx->row1 - ctx->row0) * ((ctx->W + BM - 1) / BM);
+  if (ntiles < 2 * ctx->sm_count) return 0;                    // a grid that small is latency, not throughput
+  if (tc_plan_skip(ctx)) return 0;                             // dense walk only
+  const int npairs = ((ctx->n + BN - 1) / BN + 1) / 2;
+  return npairs / 2;
+}
+
+void tc_eager_cancel(sbo_ctx* ctx) {
+  if (ctx->eager_inflight) {
+    cudaStreamSynchronize(ctx->eager_stream);
+    ctx->eager_inflight = false;
+  }
+}
+
+// called by factor_full once rows [0, 2 BN pairs) of L^-1 and their planes are final (event `ready`)
+int32_t tc_eager_launch(sbo_ctx* ctx, int pairs, cudaEvent_t ready) {
+  if (!ctx->eager_stream) {
+    SBO_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->eager_stream, cudaStreamNonBlocking));
+    SBO_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_eager_done, cudaEventDisableTiming));
+  }
+  if (ctx->rs_cap < ctx->m_local) {
+    if (ctx->d_rs_part) cudaFree(ctx->d_rs_part);
+    ctx->d_rs_part = nullptr;
+    ctx->rs_cap = 0;
+    SBO_CUDA(ctx, cudaMalloc(&ctx->d_rs_part, sizeof(float2) * (size_t)ctx->m_local));
+    ctx->rs_cap = ctx->m_local;
+  }
+  cudaStream_t se = ctx->eager_stream;
+  SBO_CUDA(ctx, cudaStreamWaitEvent(se, ready, 0));
+  SBO_TRY(tc_pack_observations(ctx, se));
+  TcParams p;
+  tc_fill_params(ctx, p, 0, ctx->n, false);
+  p.pi_lo = 0;
+  p.pi_hi = pairs;
+  p.rs_mode = 1;
+  p.rs_part = reinterpret_cast<float2*>(ctx->d_rs_part);
+  const long long ntiles = (long long)p.rows_local * ((p.W + BM - 1) / BM);
+  // leave ~1/8 of the SMs to the factorisation's own kernels
+  const long long clusters =
+      std::max<long long>(1, std::min<long long>((ntiles + 1) / 2, ctx->sm_count / 2 - std::max(2, ctx->sm_count / 16)));
+  const cudaError_t e = tc_launch_pair(ctx, p, se, clusters);
+  if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_pair_kernel (eager first pairs)");
+  ++ctx->launches;
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev_eager_done, se));
+  ctx->eager_inflight = true;
+  ctx->eager_pairs = pairs;
+  ctx->eager_n = ctx->n;
+  ctx->eager_grid_epoch = ctx->grid_epoch;
+  return SBO_OK;
+}
+
+int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
+  if (!ctx->tc_ok) return fail(ctx, SBO_ERR_STATE, "tcgen05 kernel not initialised");
+  if (ctx->m_local == 0) return SBO_OK;
+  // a partial result of the eager first pairs: usable by a full refresh of the same grid and observation set, once
+  bool resume = false;
+  if (ctx->eager_inflight) {
+    resume = !accumulate && j_lo == 0 && j_hi == ctx->n && ctx->eager_n == ctx->n && ctx->eager_grid_epoch == ctx->grid_epoch;
+    if (resume) {
+      SBO_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_eager_done, 0));  // also orders the re-pack below behind its reads
+      ctx->eager_inflight = false;
+    } else {
+      tc_eager_cancel(ctx);
+    }
+  }
+  TcParams p;
+  tc_fill_params(ctx, p, j_lo, j_hi, accumulate);
+  if (resume && !p.skip) {
+    p.pi_lo = ctx->eager_pairs;
+    p.rs_mode = 2;
+    p.rs_part = reinterpret_cast<float2*>(ctx->d_rs_part);
+  } else {
+    resume = false;
+  }
   p.dbg = 0;
   if (SBO_TC_CLOCKS)
     if (const char* s = std::getenv("SBO_TC_DBG")) p.dbg = std::atoi(s);
@@ -1062,7 +1189,7 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   }
   if ((ctx->n + BK - 1) / BK > kMaskWords * 32)
     return fail(ctx, SBO_ERR_CAPACITY, "tcgen05 posterior kernel: more than 32 768 observations (chunk mask capacity)");
-  SBO_TRY(tc_pack_observations(ctx));
+  SBO_TRY(tc_pack_observations(ctx, ctx->stream));
   const long long ntiles = (long long)p.rows_local * ((p.W + BM - 1) / BM);
   const CUtensorMap& tmap = *static_cast<CUtensorMap*>(ctx->tmap_planes);
   if (ctx->tc_cg == 1) {
@@ -1087,9 +1214,8 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
     // full refresh over at least two row blocks: the K*-stationary pair kernel (SBO_TC_PAIR=0: off)
     bool pair = !p.accumulate && p.j_lo == 0 && p.j_hi == p.n && p.n > BN && p.dbg_v == nullptr;
     if (const char* s = std::getenv("SBO_TC_PAIR")) pair = pair && std::atoi(s) != 0;
-    if (pair) cfg.dynamicSmemBytes = tc_pair_smem_bytes();
-    const cudaError_t e = pair     ? (p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_pair_kernel<true>, tmap, p)
-                                             : cudaLaunchKernelEx(&cfg, posterior_tc_pair_kernel<false>, tmap, p))
+    if (resume && !pair) return fail(ctx, SBO_ERR_STATE, "eager first pairs without the pair kernel");
+    const cudaError_t e = pair     ? tc_launch_pair(ctx, p, ctx->stream, pairs)
                           : p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, true>, tmap, p)
                                    : cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, false>, tmap, p);
     if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_kernel<2> (cluster launch)");

@@ -51,8 +51,9 @@ template <bool kSkip> struct PairWalk {
   const uint32_t* mask;
   int pi, npairs, nblocks, n_pad, nch;
   __device__ __forceinline__ int nch_of(int pair) const { return chunks_of(min(2 * pair + 1, nblocks - 1), n_pad); }
-  __device__ __forceinline__ void start(const uint32_t* m, int nblocks_, int n_pad_) {
-    mask = m; nblocks = nblocks_; n_pad = n_pad_; npairs = (nblocks + 1) / 2; pi = 0; nch = nch_of(0);
+  // pairs [pi_lo, pi_hi): `npairs` is the END of the walk, not the pair count of the observation set
+  __device__ __forceinline__ void start(const uint32_t* m, int nblocks_, int n_pad_, int pi_lo, int pi_hi) {
+    mask = m; nblocks = nblocks_; n_pad = n_pad_; npairs = pi_hi; pi = pi_lo; nch = pi < npairs ? nch_of(pi) : 0;
     ci.reset(mask);
   }
   // chunk of the next visit (it belongs to pair `pi`), or -1 when the tile is done
@@ -136,7 +137,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     };
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
       if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
-      for (int pi = 0; pi < npairs; ++pi) {
+      for (int pi = p.pi_lo; pi < p.pi_hi; ++pi) {
         const int jb0 = 2 * pi;
         const bool has1 = jb0 + 1 < nblocks;
         const int nch0 = chunks_of(jb0, n_pad), nchl = has1 ? chunks_of(jb0 + 1, n_pad) : nch0;
@@ -154,7 +155,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     uint32_t ita = 0, itb = 0, use0 = 0, use1 = 0;
     for (long long gt = group; rank == 0 && gt < ngtiles; gt += ngroups) {
       if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
-      for (int pi = 0; pi < npairs; ++pi) {
+      for (int pi = p.pi_lo; pi < p.pi_hi; ++pi) {
         const int jb0 = 2 * pi;
         const bool has1 = jb0 + 1 < nblocks;
         const int nch0 = chunks_of(jb0, n_pad), nchl = has1 ? chunks_of(jb0 + 1, n_pad) : nch0;
@@ -213,10 +214,18 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       const long long tile = gt * CG + rank;
       if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
       float rs_hi = 0.f, rs_lo = 0.f;  // sum of squares of this cell's row of V (scaled), double-word fp32
+      const long long e_tile = min(tile, ntiles - 1);
+      const int e_lrow = (int)(e_tile / tiles_per_row), e_col = (int)(e_tile % tiles_per_row) * BM + r;
+      const bool e_live = tile < ntiles && e_col < p.W;
+      const long long e_lc = (long long)e_lrow * p.W + e_col;
+      if (p.rs_mode == 2 && e_live) {  // resume: pairs < pi_lo were contracted by an earlier launch (same sums, same order)
+        const float2 v0 = p.rs_part[e_lc];
+        rs_hi = v0.x; rs_lo = v0.y;
+      }
       ChunkIter<kSkip> ci0;
       ci0.reset(cmask);
       const int first_chunk = ci0.next();
-      for (int pi = 0; pi < npairs; ++pi) {
+      for (int pi = p.pi_lo; pi < p.pi_hi; ++pi) {
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           const int jb = 2 * pi + half;
@@ -252,9 +261,9 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           if (lane == 0) mbar_arrive_cluster(mapa(smem_u32(&sh->tmem_empty[half]), 0));
         }
       }
-      if (tile < ntiles) {
-        const int lrow = (int)(tile / tiles_per_row), col = (int)(tile % tiles_per_row) * BM + r;
-        if (col < p.W) p.s2[(long long)lrow * p.W + col] = (float)((double)p.sf2 - ((double)rs_hi + (double)rs_lo) * p.v_unscale2);
+      if (e_live) {
+        if (p.rs_mode == 1) p.rs_part[e_lc] = make_float2(rs_hi, rs_lo);  // partial launch: the running sum, nothing else
+        else p.s2[e_lc] = (float)((double)p.sf2 - ((double)rs_hi + (double)rs_lo) * p.v_unscale2);
       }
     }
   } else if (warp >= 8) {
@@ -286,7 +295,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       float mu_hi = 0.f, mu_lo = 0.f;
       if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
       PairWalk<kSkip> w, scout;
-      w.start(cmask, nblocks, n_pad);
+      w.start(cmask, nblocks, n_pad, p.pi_lo, p.pi_hi);
       scout = w;
       const int first0 = scout.next(), first1 = scout.next();
       uint32_t vi = 0;  // visit parity per tile: mu must not depend on the tiles processed before (see posterior_tc_kernel)
@@ -341,7 +350,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       const double mu_acc = (double)mu_hi + (double)mu_lo;
       if (pq > 0) sh->mu_part[tile_par][pq - 1][r] = (float)mu_acc;
       named_bar_sync(1, kGenWarps * 32);
-      if (pq == 0 && live) {
+      if (pq == 0 && live && p.pi_hi == npairs) {  // (a partial launch that stops before the last pair has no mu)
         const int col = col0 + r;
         if (col < p.W) {
           const double part = (double)sh->mu_part[tile_par][0][r] + (double)sh->mu_part[tile_par][1][r] +

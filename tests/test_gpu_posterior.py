@@ -241,6 +241,60 @@ def test_long_rank1_chain_stays_in_tolerance(pkg, oracle, coracle, precision):
         check_argmax(res, ref, band, mask)
 
 
+_EAGER_SCRIPT = """
+import sys, numpy as np
+sys.path.insert(0, {root!r})
+import safe_bayesian_optimization_b200 as pkg
+from safe_bayesian_optimization_b200 import synthetic as S
+p = S.make_problem('C2', n={n}, W={W}, H={H})
+out = sys.argv[1]
+ctx = pkg.SboContext(sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean,
+                     precision='fp32', max_obs=p.n + 8, max_cells=p.m)
+ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+for rep in range(3):                                   # fit (+ eager first pairs) then step, three times over
+    ctx.set_observations(p.xy, p.y)
+    res, mask = ctx.step(p.beta, p.f_min)
+np.save(out + '_mu.npy', ctx.mu()); np.save(out + '_s2.npy', ctx.sigma2()); np.save(out + '_mask.npy', mask)
+res2, mask2 = ctx.step(p.beta, p.f_min)                # a second step on the same fit: nothing eager left to resume from
+np.save(out + '_again_mu.npy', ctx.mu()); np.save(out + '_again_s2.npy', ctx.sigma2())
+ctx.set_observations(p.xy, p.y)                        # eager launched ...
+ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H, 4, p.H - 2)   # ... and dropped: another shard
+res, mask = ctx.step(p.beta, p.f_min)
+np.save(out + '_band_mu.npy', ctx.mu()); np.save(out + '_band_s2.npy', ctx.sigma2())
+ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+xy2, y2 = S.extra_observations(p, 3, 0)
+ctx.set_observations(p.xy, p.y); ctx.append_observations(xy2, y2)   # eager launched, then an append: dropped
+res, mask = ctx.step(p.beta, p.f_min)
+np.save(out + '_app_mu.npy', ctx.mu()); np.save(out + '_app_s2.npy', ctx.sigma2())
+ctx.close()
+"""
+
+
+@pytest.mark.parametrize("n,W,H", [(1024, 1024, 64), (700, 512, 96), (1600, 640, 80), (2304, 1024, 40)])
+def test_eager_first_pairs_bit_identical(pkg, oracle, coracle, n, W, H):
+    """sbo_set_observations launches the first row-block pairs of the posterior on a side stream while the factorisation
+    is still running (>= 2 tiles per SM, dense walk, 512 <= n <= 4096); the next sbo_step resumes from their running sums.
+    Same sums in the same order: mu, sigma^2 and the mask equal the one-launch result (SBO_TC_EAGER=0) bit for bit, also
+    when a grid change or an append drops the partial result.  The switch is read once per process: one process each."""
+    import subprocess, sys, tempfile
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = _EAGER_SCRIPT.format(root=root, n=n, W=W, H=H)
+    keys = ("mu", "s2", "mask", "again_mu", "again_s2", "band_mu", "band_s2", "app_mu", "app_s2")
+    res = {}
+    with tempfile.TemporaryDirectory() as td:
+        for flag in ("1", "0"):
+            subprocess.run([sys.executable, "-c", script, os.path.join(td, "e" + flag)], check=True,
+                           env=dict(os.environ, SBO_TC_EAGER=flag), timeout=600)
+            res[flag] = {k: np.load(os.path.join(td, "e" + flag + "_" + k + ".npy")) for k in keys}
+    for k in keys:
+        assert np.array_equal(res["1"][k], res["0"][k]), k
+    assert np.array_equal(res["1"]["again_mu"], res["1"]["mu"]) and np.array_equal(res["1"]["again_s2"], res["1"]["s2"])
+    p = S.make_problem("C2", n=n, W=W, H=H)
+    ref = reference(oracle, coracle, p)
+    assert np.abs(res["1"]["mu"] - ref["mu"]).max() <= TOL["fp32"] * np.abs(ref["mu"]).max()
+    assert np.abs(res["1"]["s2"] - ref["s2"]).max() <= TOL["fp32"] * p.sigma_f ** 2
+
+
 @pytest.mark.parametrize("precision", ["fp64"])
 def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, monkeypatch, precision):
     """One new row, >= one 128 x 128 tile per SM: the 2-D register-tile kernels.  Same projections as the column-strip
