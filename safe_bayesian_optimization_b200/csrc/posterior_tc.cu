@@ -1104,9 +1104,23 @@ int tc_eager_pairs(sbo_ctx* ctx) {
   if (ctx->n < 2 * BN || ctx->n > 4096 || g_dbg_v) return 0;   // beyond ~4k observations the factorisation is a few % of the step
   const long long ntiles = (long long)(ctx->row1 - ctx->row0) * ((ctx->W + BM - 1) / BM);
   if (ntiles < 2 * ctx->sm_count) return 0;                    // a grid that small is latency, not throughput
-  if (tc_plan_skip(ctx)) return 0;                             // dense walk only
+  // How many pairs: as many as finish about when the factorisation does.  While they run the factor kernels share the SMs
+  // that were left free, so a partial launch that outlasts the fit only delays it (measured at n = 4096 on a 4096^2 grid: four
+  // eager pairs = 50 ms of posterior turned a 7 ms fit into 57 ms).  Estimates: fit ~ 1.1 ms (n / 1024)^1.35 (measured 1.1 / 2.6 /
+  // 7.2 ms at 1024 / 2048 / 4096), of which the share 1 - 512 P / n is left when rows < 512 P are final; P pairs execute
+  // ~ 3.2 m (512 P)^2 kept flops at ~ 1.3e15 flop/s on 7/8 of the GPU.  Not worth a launch below 5 % of the whole posterior.
   const int npairs = ((ctx->n + BN - 1) / BN + 1) / 2;
-  return npairs / 2;
+  const double kept = tc_plan_skip(ctx) ? ctx->tc_kept_frac : 1.0;
+  const double fit_ms = 1.1 * std::pow((double)ctx->n / 1024.0, 1.35);
+  const double m = (double)ctx->m_local;
+  for (int P = npairs / 2; P >= 1; --P) {
+    const double rows = 512.0 * P;
+    const double ms = 3.2 * m * rows * rows * kept / 1.3e15 * 1e3;
+    const double all_ms = 3.2 * m * (double)ctx->n * ctx->n * kept / 1.5e15 * 1e3;
+    const double left_ms = fit_ms * (1.0 - rows / (double)ctx->n);   // the chain advances about linearly in the rows
+    if (ms <= 1.3 * left_ms) return ms >= 0.05 * all_ms ? P : 0;
+  }
+  return 0;
 }
 
 void tc_eager_cancel(sbo_ctx* ctx) {
@@ -1169,12 +1183,10 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   }
   TcParams p;
   tc_fill_params(ctx, p, j_lo, j_hi, accumulate);
-  if (resume && !p.skip) {
+  if (resume) {
     p.pi_lo = ctx->eager_pairs;
     p.rs_mode = 2;
     p.rs_part = reinterpret_cast<float2*>(ctx->d_rs_part);
-  } else {
-    resume = false;
   }
   p.dbg = 0;
   if (SBO_TC_CLOCKS)

@@ -298,8 +298,14 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       w.start(cmask, nblocks, n_pad, p.pi_lo, p.pi_hi);
       scout = w;
       const int first0 = scout.next(), first1 = scout.next();
-      uint32_t vi = 0;  // visit parity per tile: mu must not depend on the tiles processed before (see posterior_tc_kernel)
+      // Visit parity (which group of warps generates a visit, hence how the observations are grouped in the partial sums
+      // of mu) restarts with every pair: it must depend neither on the tiles this CTA processed before (row-band shards)
+      // nor on how many visits the pairs before had, which a launch that resumes at pair pi_lo does not see (block-sparse
+      // walk: any count).  The look-ahead below then guesses wrong across a pair of odd length: checked at use.
+      uint32_t vi = 0;
+      int pi_seen = -1;
       for (int kc = w.next(); kc >= 0; kc = w.next(), ++ita, ++vi) {
+        if (w.pi != pi_seen) { pi_seen = w.pi; vi = 0; }
         int kn = scout.next();  // the chunk two visits ahead
         if (kn < 0) kn = grp == 0 ? first0 : first1;
         if ((vi & 1u) != (uint32_t)grp) continue;
