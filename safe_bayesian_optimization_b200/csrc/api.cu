@@ -105,7 +105,10 @@ int32_t run_step(sbo_ctx* ctx, double beta, double f_min, bool incremental, int*
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
   // a few new rows: the thin SIMT kernel (O(m n k)); otherwise the row blocks that hold them
   static const bool thin_off = std::getenv("SBO_THIN") && std::atoi(std::getenv("SBO_THIN")) == 0;
-  if (incremental && !thin_off && j_hi - j_lo <= kThinMaxRows) {
+  if (incremental && which == SBO_KERNEL_TCGEN05 && tc_inc_applicable(ctx, j_hi - j_lo)) {
+    // large grid, fp32: the k projections as a tensor-core GEMM through the separable kernel (posterior_tc_inc.cuh)
+    SBO_TRY(launch_posterior_tc_inc(ctx, j_lo));
+  } else if (incremental && !thin_off && j_hi - j_lo <= kThinMaxRows) {
     SBO_TRY(launch_posterior_thin(ctx, j_lo));
     which = SBO_KERNEL_THIN;
   } else if (which == SBO_KERNEL_TCGEN05) {

@@ -83,6 +83,8 @@ struct sbo_ctx {
   cudaStream_t eager_stream = nullptr;
   cudaEvent_t ev_eager_done = nullptr;
   void* d_rs_part = nullptr;     // [rs_cap] float2 running row sums of the partial launch
+  void* d_pplanes = nullptr;     // fp16 hi/lo planes of P, the row operand of the incremental GEMM (posterior_tc_inc.cuh), lazy
+  size_t pplanes_cap = 0;        // bytes
   int64_t rs_cap = 0;
   bool eager_inflight = false;   // a partial result exists (or is being computed) for eager_n observations on grid eager_grid_epoch
   int eager_pairs = 0, eager_n = 0;
@@ -179,6 +181,8 @@ void tc_plane_shifts(const sbo_config& cfg, int* shift_a, int* shift_b);
 int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
 void tc_destroy(sbo_ctx* ctx);
 bool tc_plan_skip(sbo_ctx* ctx);                   // worth walking chunk masks on this grid / observation set?
+bool tc_inc_applicable(sbo_ctx* ctx, int k);       // incremental step with k new rows through the GEMM kernel?
+int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo);
 int tc_eager_pairs(sbo_ctx* ctx);                   // row-block pairs factor_full may launch early (0: none)
 int32_t tc_eager_launch(sbo_ctx* ctx, int pairs, cudaEvent_t ready);
 void tc_eager_cancel(sbo_ctx* ctx);                 // waits for an eager launch in flight and drops its partial result

@@ -874,6 +874,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
 }
 
 #include "posterior_tc_pair.cuh"
+#include "posterior_tc_inc.cuh"
 
 }  // namespace
 
@@ -883,6 +884,8 @@ namespace {
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn g_encode_tiled = nullptr;   // cuTensorMapEncodeTiled, resolved by tc_init
 
 template <int CG> constexpr size_t tc_smem_bytes() {
   return 1024 /*align slack*/ + (size_t)TcCfg<CG>::kStages * TcCfg<CG>::kStageBytes + sizeof(TcShared);
@@ -915,6 +918,7 @@ int32_t tc_init(sbo_ctx* ctx) {
   ctx->tc_skip = true;   // SBO_TC_SKIP=0: contract every chunk (dense), for A/B measurements
   if (const char* s = std::getenv("SBO_TC_SKIP")) ctx->tc_skip = std::atoi(s) != 0;
   tc_plane_shifts(ctx->cfg, &ctx->shift_a, &ctx->shift_b);
+  g_encode_tiled = reinterpret_cast<EncodeTiledFn>(fn);
   CUtensorMap* map = new CUtensorMap;
   const cuuint64_t nc = (cuuint64_t)ctx->n_cap;
   const cuuint64_t gdim[2] = {nc, 2 * nc};                 // inner: k (columns of L^-1), outer: hi rows then lo rows
@@ -935,6 +939,11 @@ int32_t tc_init(sbo_ctx* ctx) {
     e = cudaFuncSetAttribute(posterior_tc_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(posterior_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(posterior_tc_inc_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(posterior_tc_inc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(posterior_tc_inc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(posterior_tc_inc_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(posterior_tc_inc_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<2>());
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(posterior_tc_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_pair_smem_bytes());
   if (e == cudaSuccess)
@@ -955,6 +964,9 @@ void tc_destroy(sbo_ctx* ctx) {
     cudaEventDestroy(ctx->ev_eager_done);
     ctx->eager_stream = nullptr;
   }
+  if (ctx->d_pplanes) cudaFree(ctx->d_pplanes);
+  ctx->d_pplanes = nullptr;
+  ctx->pplanes_cap = 0;
   if (ctx->d_rs_part) cudaFree(ctx->d_rs_part);
   ctx->d_rs_part = nullptr;
   ctx->rs_cap = 0;
@@ -1164,6 +1176,97 @@ int32_t tc_eager_launch(sbo_ctx* ctx, int pairs, cudaEvent_t ready) {
   ctx->eager_pairs = pairs;
   ctx->eager_n = ctx->n;
   ctx->eager_grid_epoch = ctx->grid_epoch;
+  return SBO_OK;
+}
+
+// ---- incremental step as a GEMM (posterior_tc_inc.cuh) ---------------------------------------------------------------
+static void tc_inc_shape(const sbo_ctx* ctx, int k, int* lq, int* nslabs, long long* nitems, size_t* bytes) {
+  int l = 0;
+  while ((1 << l) < k) ++l;
+  const int rows = ctx->row1 - ctx->row0, slab_rows = BN >> l;
+  *lq = l;
+  *nslabs = (rows + slab_rows - 1) / slab_rows;
+  *nitems = (long long)*nslabs * (((ctx->W + BM - 1) / BM + 1) / 2);
+  *bytes = (size_t)2 * *nslabs * BN * ctx->n_cap * sizeof(__half);
+}
+
+bool tc_inc_applicable(sbo_ctx* ctx, int k) {
+  const char* env = std::getenv("SBO_TC_INC");
+  const bool off = env && std::atoi(env) == 0;
+  if (off || !ctx->tc_ok || ctx->tc_cg != 2 || ctx->cfg.precision != SBO_FP32 || !g_encode_tiled) return false;
+  if (k < 1 || k > 16 || ctx->m_local == 0 || ctx->n < 1) return false;
+  int lq, nslabs;
+  long long nitems;
+  size_t bytes;
+  tc_inc_shape(ctx, k, &lq, &nslabs, &nitems, &bytes);
+  // enough (slab, column pair) items for every CTA pair, and the planes of P within 2 GiB
+  return nitems >= ctx->sm_count / 2 && bytes <= ((size_t)2 << 30);
+}
+
+int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo) {
+  const int k = ctx->n - row_lo;
+  int lq, nslabs;
+  long long nitems;
+  size_t bytes;
+  tc_inc_shape(ctx, k, &lq, &nslabs, &nitems, &bytes);
+  tc_eager_cancel(ctx);
+  if (ctx->pplanes_cap < bytes) {
+    if (ctx->d_pplanes) cudaFree(ctx->d_pplanes);
+    ctx->d_pplanes = nullptr;
+    ctx->pplanes_cap = 0;
+    SBO_CUDA(ctx, cudaMalloc(&ctx->d_pplanes, bytes));
+    ctx->pplanes_cap = bytes;
+  }
+  SBO_TRY(tc_pack_observations(ctx, ctx->stream));
+  const int rp = nslabs * BN, ld = ctx->n_cap;
+  const double inv2l2 = 1.0 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale);
+  pplanes_kernel<<<dim3((unsigned)(rp >> lq), (unsigned)((ld + 255) / 256)), 256, 0, ctx->stream>>>(
+      ctx->d_xy, ctx->d_Linv, ld, ctx->n, row_lo, k, lq, ctx->row1 - ctx->row0, ctx->row0, ctx->y0, ctx->ry, inv2l2,
+      std::ldexp(1.0, ctx->shift_b), rp, reinterpret_cast<__half*>(ctx->d_pplanes));
+  SBO_LAUNCH_CHECK(ctx, "pplanes_kernel");
+  CUtensorMap tmap;
+  const cuuint64_t gdim[2] = {(cuuint64_t)ld, (cuuint64_t)2 * rp};
+  const cuuint64_t gstride[1] = {(cuuint64_t)ld * sizeof(__half)};
+  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)(BN / 2)};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = g_encode_tiled(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, ctx->d_pplanes, gdim, gstride, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(ctx, SBO_ERR_CUDA, "launch_posterior_tc_inc: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+  IncParams p;
+  p.obs = reinterpret_cast<const float4*>(ctx->d_obs_f32);
+  p.w = ctx->d_w;
+  p.mu = static_cast<float*>(ctx->d_mu);
+  p.s2 = static_cast<float*>(ctx->d_s2);
+  p.n = ctx->n; p.row_lo = row_lo; p.k = k;
+  p.W = ctx->W; p.rows_local = ctx->row1 - ctx->row0;
+  p.x0 = ctx->x0; p.rx = ctx->rx;
+  p.xscale = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
+  p.a_scale = (float)std::ldexp(ctx->cfg.sigma_f * ctx->cfg.sigma_f, ctx->shift_a);
+  p.u_unscale = std::ldexp(1.0, -(ctx->shift_a + ctx->shift_b));
+  p.nslabs = nslabs; p.tiles_x = (ctx->W + BM - 1) / BM; p.rp = rp;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)(2 * std::min<long long>(nitems, ctx->sm_count / 2)));
+  cfg.blockDim = dim3(kThreadsTc);
+  cfg.dynamicSmemBytes = tc_smem_bytes<2>();
+  cfg.stream = ctx->stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e;
+  switch (lq) {
+    case 0: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<0>, tmap, p); break;
+    case 1: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<1>, tmap, p); break;
+    case 2: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<2>, tmap, p); break;
+    case 3: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<3>, tmap, p); break;
+    default: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<4>, tmap, p); break;
+  }
+  if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_inc_kernel (cluster launch)");
+  SBO_LAUNCH_CHECK(ctx, "posterior_tc_inc_kernel");
   return SBO_OK;
 }
 

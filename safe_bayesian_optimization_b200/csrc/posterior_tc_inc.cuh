@@ -1,0 +1,253 @@
+// posterior_tc_inc.cuh -- included by posterior_tc.cu (inside namespace sbo::{anonymous}).
+//
+// The incremental step (k new rows of L^-1 after a rank-k append) as a tensor-core GEMM.  On a grid the RBF factorises,
+//   k*(cell(r, c), j) = sigma_f^2 ex(c, j) ey(r, j),
+// so the projection of new row q onto a cell is
+//   u_q(r, c) = sum_j ex(c, j) * [sigma_f^2 ey(r, j) Linv[q][j]] = (A P^T)(c, (r, q)),   A = ex (W x n),  P = (H k) x n,
+// a dense contraction over the observations whose operands cost (W + H k) n exponentials, not m n.  Both updates follow
+// from u:  sigma^2 -= sum_q u_q^2,  mu += sum_q w_q u_q  (w = L^-1 (y - prior_mean), see posterior_thin.cu).
+//
+// Mapping onto the pipeline of posterior_tc_kernel<2>:  the generators produce A tiles (128 columns x 64 observations of
+// ex, fp16 hi/lo) exactly as they produce K*, with the row factor left out; P takes the place of L^-1 -- its fp16 hi/lo
+// planes are written by pplanes_kernel once per step (row rho = local_row * KP + q, KP = k rounded up to a power of two)
+// and arrive by TMA; one accumulator holds 128 columns x 256 rows of P = 256 / KP grid rows; the epilogue applies the
+// two updates per element instead of summing squares.  No triangular structure: every chunk at full N.
+// 3 x 2 m n KP executed flops: C4 with one new row ~5 ms instead of the FMA strip kernel's 60.
+
+struct IncParams {
+  const float4* obs;   // [n_cap] scaled observation coordinates (x_hi, x_lo, y_hi, y_lo)
+  const double* w;     // [n] L^-1 (y - prior_mean); entries row_lo .. row_lo + k - 1 are read
+  float* mu;           // [m_local]
+  float* s2;           // [m_local]
+  int n, row_lo, k;
+  int W, rows_local;
+  double x0, rx, xscale;
+  float a_scale;       // sigma_f^2 2^shift_a
+  double u_unscale;    // 2^-(shift_a + shift_b)
+  int nslabs;          // slabs of 256 rows of P
+  int tiles_x;         // 128-column tiles per grid row
+  int rp;              // rows of P (multiple of 256); the lo plane starts at row rp of the tensor map
+};
+
+// fp16 hi/lo planes of P: row rho = lr * KP + q holds 2^shift_b ey(lr, j) Linv[row_lo + q][j]  (sigma_f^2 rides on A).
+// One thread per (grid row, observation): the fp64 exp is computed once and serves the KP rows of that grid row.
+__global__ void __launch_bounds__(256)
+pplanes_kernel(const double* __restrict__ xy, const double* __restrict__ Linv, int ld, int n, int row_lo, int k, int lq,
+               int rows_local, int row0, double y0, double ry, double inv2l2, double scale, int rp,
+               __half* __restrict__ planes) {
+  const int j = blockIdx.y * 256 + threadIdx.x;
+  const int lr = blockIdx.x;   // grid rows incl. the padding up to a whole slab
+  if (j >= ld) return;
+  double e = 0.0;
+  if (j < n && lr < rows_local) {
+    const double dy = xy[2 * (size_t)j + 1] - cell_coord(y0, ry, row0 + lr);
+    e = exp(-dy * dy * inv2l2) * scale;
+  }
+  const int kp = 1 << lq;
+  for (int q = 0; q < kp; ++q) {
+    const double x = (q < k && e != 0.0) ? e * Linv[(size_t)(row_lo + q) * ld + j] : 0.0;
+    const __half hi = __float2half_rn((float)x);
+    const __half lo = __float2half_rn((float)(x - (double)__half2float(hi)));
+    const size_t rho = (size_t)lr * kp + q;
+    planes[rho * ld + j] = hi;
+    planes[((size_t)rp + rho) * ld + j] = lo;
+  }
+}
+
+template <int LQ>
+__global__ void __launch_bounds__(kThreadsTc, 1)
+posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
+  constexpr int CG = 2;
+  constexpr int KP = 1 << LQ;
+  using Cfg = TcCfg<CG>;
+  constexpr int kStages = Cfg::kStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* tiles = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  TcShared* sh = reinterpret_cast<TcShared*>(tiles + (size_t)kStages * Cfg::kStageBytes);
+  auto a_hi = [&](int s) { return tiles + (size_t)s * Cfg::kStageBytes; };
+  auto a_lo = [&](int s) { return tiles + (size_t)s * Cfg::kStageBytes + kABytes; };
+  auto b_hi = [&](int s) { return tiles + (size_t)s * Cfg::kStageBytes + 2 * kABytes; };
+  auto b_lo = [&](int s) { return tiles + (size_t)s * Cfg::kStageBytes + 2 * kABytes + Cfg::kBBytes; };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int ncp = (p.tiles_x + 1) / 2;                       // column-tile pairs per slab
+  const long long nitems = (long long)p.nslabs * ncp;        // item = slab * ncp + column pair: neighbours share the slab's P tiles
+  const long long group = blockIdx.x / CG, ngroups = gridDim.x / CG;
+  const int nchunks = (p.n + BK - 1) / BK;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&sh->full[s], 1 + (kGenWarps / 2) * CG);
+      mbar_init(&sh->empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&sh->tmem_full[s], 1);
+      mbar_init(&sh->tmem_empty[s], 4 * CG);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc<CG>(&sh->tmem_base, kTmemCols);
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = sh->tmem_base;
+
+  if (warp == 0) {
+    // =============================== TMA producer: P tiles ===============================
+    uint32_t it = 0;
+    for (long long item = group; item < nitems; item += ngroups) {
+      const int sb = (int)(item / ncp);
+      const int row = sb * BN + (int)rank * (int)Cfg::kBRows;
+      for (int kc = 0; kc < nchunks; ++kc, ++it) {
+        const int s = it % kStages;
+        const uint32_t ph = (it / kStages) & 1u;
+        mbar_wait(&sh->empty[s], ph ^ 1u);
+        const uint32_t bar = mapa(smem_u32(&sh->full[s]), 0);
+        if (elect_one()) {
+          if (rank == 0) mbar_arrive_expect_tx(&sh->full[s], 2 * Cfg::kBBytes * CG);
+          tma_load_2d<CG>(&tmap, bar, b_hi(s), kc * BK, row);
+          tma_load_2d<CG>(&tmap, bar, b_lo(s), kc * BK, p.rp + row);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // =============================== MMA issuer (leader CTA) ===============================
+    uint32_t it = 0, acc_it = 0;
+    for (long long item = group; rank == 0 && item < nitems; item += ngroups) {
+      const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
+      ++acc_it;
+      mbar_wait(&sh->tmem_empty[as], aph ^ 1u);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + as * BN;
+      const uint32_t idesc = idesc_f16<CG>(BN);
+      for (int kc = 0; kc < nchunks; ++kc, ++it) {
+        const int s = it % kStages;
+        mbar_wait(&sh->full[s], (it / kStages) & 1u);
+        tc_fence_after();
+        const uint64_t dah = umma_desc_sw128(smem_u32(a_hi(s))), dal = umma_desc_sw128(smem_u32(a_lo(s)));
+        const uint64_t dbh = umma_desc_sw128(smem_u32(b_hi(s))), dbl = umma_desc_sw128(smem_u32(b_lo(s)));
+        if (elect_one()) {
+#pragma unroll
+          for (int ks = 0; ks < BK / UK; ++ks) {
+            const uint64_t adv = (uint64_t)((ks * UK * 2) >> 4);
+            umma_f16<CG>(d_tmem, dal + adv, dbh + adv, idesc, (kc == 0 && ks == 0) ? 0u : 1u);
+            umma_f16<CG>(d_tmem, dah + adv, dbl + adv, idesc, 1u);
+            umma_f16<CG>(d_tmem, dah + adv, dbh + adv, idesc, 1u);
+          }
+          umma_commit<CG>(&sh->empty[s]);
+          if (kc == nchunks - 1) umma_commit<CG>(&sh->tmem_full[as]);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // =============================== epilogue: sigma^2 -= sum_q u_q^2, mu += sum_q w_q u_q ===============================
+    const int q4 = warp & 3;
+    const int c = q4 * 32 + lane;  // TMEM lane == column of the tile
+    double wq[KP];
+#pragma unroll
+    for (int q = 0; q < KP; ++q) wq[q] = q < p.k ? p.w[p.row_lo + q] * p.u_unscale : 0.0;
+    const float uu = (float)p.u_unscale;
+    uint32_t acc_it = 0;
+    for (long long item = group; item < nitems; item += ngroups) {
+      const int sb = (int)(item / ncp), ct = 2 * (int)(item % ncp) + (int)rank;
+      const int col = ct * BM + c;
+      const bool live = ct < p.tiles_x && col < p.W;
+      const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
+      ++acc_it;
+      mbar_wait(&sh->tmem_full[as], aph);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + as * BN;
+#pragma unroll 1
+      for (int g = 0; g < BN / 32; ++g) {
+        uint32_t v[32];
+        tmem_ld32(taddr + g * 32, v);
+        tmem_ld_wait();
+        const int lr0 = (sb * BN + g * 32) >> LQ;  // first grid row of this group of 32 rows of P
+#pragma unroll
+        for (int t = 0; t < (32 >> LQ); ++t) {
+          float usq = 0.f;
+          double dmu = 0.0;
+#pragma unroll
+          for (int q = 0; q < KP; ++q) {
+            const float d = __uint_as_float(v[(t << LQ) + q]);
+            const float u = d * uu;
+            usq = fmaf(u, u, usq);
+            dmu = fma(wq[q], (double)d, dmu);
+          }
+          const int lr = lr0 + t;
+          if (live && lr < p.rows_local) {
+            const long long lc = (long long)lr * p.W + col;
+            p.s2[lc] = (float)((double)p.s2[lc] - (double)usq);
+            p.mu[lc] = (float)((double)p.mu[lc] + dmu);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa(smem_u32(&sh->tmem_empty[as]), 0));
+    }
+  } else if (warp >= 8) {
+    // =============================== generators: A = ex(column, observation), the K* generator without the row factor ===============================
+    const int gw = warp - 8;
+    const int grp = gw >> 3;
+    const int oh = (gw >> 2) & 1;
+    const int r = (gw & 3) * 32 + lane;
+    float* ox = reinterpret_cast<float*>(sh->obs_x[gw]);
+    float* oy = reinterpret_cast<float*>(sh->obs_y[gw]);
+    const uint32_t row_off = (uint32_t)r * 128u;
+    const uint32_t swz = (uint32_t)(r & 7);
+    const float cxs = (float)((double)r * p.rx * p.xscale);
+    const f32x2 ncx2 = pack2(-cxs, -cxs);
+    uint32_t it = 0;
+    float4 o_next = make_float4(0.f, 0.f, 0.f, 0.f);
+    int c_next = -1;
+    for (long long item = group; item < nitems; item += ngroups) {
+      const int ct = min(2 * (int)(item % ncp) + (int)rank, p.tiles_x - 1);  // an odd last column tile: the peer regenerates it
+      const double ox0 = cell_coord(p.x0, p.rx, ct * BM) * p.xscale;
+      const float oxh = (float)ox0, oxl = (float)(ox0 - (double)oxh);
+      for (int kc = 0; kc < nchunks; ++kc, ++it) {
+        if ((it & 1u) != (uint32_t)grp) continue;
+        const int s = it % kStages;
+        const uint32_t ph = (it / kStages) & 1u;
+        {
+          const int kobs = kc * BK + oh * 32 + lane;
+          if (c_next != kc) o_next = p.obs[kobs];
+          ox[lane] = (o_next.x - oxh) + (o_next.y - oxl);
+          oy[lane] = kobs < p.n ? p.a_scale : 0.f;
+          c_next = kc + 2 < nchunks ? kc + 2 : kc + 2 - nchunks;   // this warp's next visit (the next item starts at chunk 0 again)
+          if (c_next >= nchunks) c_next = 0;                        // (a single chunk)
+          o_next = p.obs[c_next * BK + oh * 32 + lane];
+        }
+        __syncwarp();
+        uint8_t* pa_hi = a_hi(s) + row_off;
+        uint8_t* pa_lo = a_lo(s) + row_off;
+        f32x2 mu2 = pack2(0.f, 0.f);
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t hi[8], lo[8];
+          gen16<false>(sh->obs_x[gw] + 4 * half, sh->obs_y[gw] + 4 * half, sh->obs_a[gw] + 4 * half, ncx2, hi, lo, mu2);
+          if (half == 0) mbar_wait(&sh->empty[s], ph ^ 1u);
+          const uint32_t u0 = (uint32_t)(oh * 4 + half * 2);
+          const uint32_t off0 = ((u0 ^ swz) << 4), off1 = (((u0 + 1u) ^ swz) << 4);
+          *reinterpret_cast<uint4*>(pa_hi + off0) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+          *reinterpret_cast<uint4*>(pa_lo + off0) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          *reinterpret_cast<uint4*>(pa_hi + off1) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+          *reinterpret_cast<uint4*>(pa_lo + off1) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(mapa(smem_u32(&sh->full[s]), 0));
+      }
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<CG>(tmem_base, kTmemCols);
+  }
+}

@@ -21,10 +21,13 @@ def run(name, n, W, H, precision, ks):
             print(f"{precision} n={n} grid {W}x{H} k={k}: incremental posterior {inc.ms_posterior:8.3f} ms "
                   f"({p.m * float(n) / inc.ms_posterior / 1e6:.1f} G cell-obs/s) kernel={inc.kernel_used}", flush=True)
 
+run("C3", 4096, 4096, 4096, "fp32", [1, 16])   # incremental GEMM kernel (>= one item per CTA pair)
 run("C2", 1024, 1024, 1024, "fp32", [1, 2, 4, 8])
 run("C4", 16384, 8192, 512, "fp32", [1])
+run("C4", 16384, 8192, 2048, "fp32", [1, 4, 16])
 run("C5", 8192, 4096, 256, "fp64", [1, 2, 4, 8])
 run("C5", 8192, 4096, 1024, "fp64", [1])   # >= one 128 x 128 tile per SM: the 2-D tile kernel
 os.environ["SBO_THIN_2D"] = "0"
 run("C5", 8192, 4096, 1024, "fp64", [1])
 run("C4", 16384, 8192, 512, "fp32", [1])
+run("C4", 16384, 8192, 2048, "fp32", [1, 4, 16])

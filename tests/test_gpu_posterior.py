@@ -241,6 +241,39 @@ def test_long_rank1_chain_stays_in_tolerance(pkg, oracle, coracle, precision):
         check_argmax(res, ref, band, mask)
 
 
+@pytest.mark.parametrize("ks", [[1, 3], [8, 16], [2, 5, 1]])
+def test_incremental_gemm_kernel(pkg, monkeypatch, ks):
+    """fp32, a grid with at least one (256-row slab, column pair) item per CTA pair: the incremental step runs as a
+    tensor-core GEMM through the separable RBF (posterior_tc_inc.cuh; kernel_used = 2 for any k <= 16).  Checked against a
+    full refresh of the same observations and against the FMA kernels (SBO_TC_INC=0) on the same chain; ragged edges."""
+    n0 = 130
+    total = n0 + sum(ks)
+    p = S.make_problem("C3", n=total, W=1990, H=2400)
+    out = {}
+    for flag in ("1", "0"):
+        monkeypatch.setenv("SBO_TC_INC", flag)
+        with make_ctx(pkg, p, precision="fp32", kernel="tcgen05", max_obs=total) as ctx:
+            ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+            ctx.set_observations(p.xy[:n0], p.y[:n0])
+            ctx.step(p.beta, p.f_min, want_mask=False)
+            n = n0
+            for k in ks:
+                ctx.append_observations(p.xy[n:n + k], p.y[n:n + k])
+                n += k
+                res, _ = ctx.step(p.beta, p.f_min, incremental=True, want_mask=False)
+                assert res.kernel_used == (2 if flag == "1" or k > 8 else 3)
+            out[flag] = (ctx.mu().astype(np.float64), ctx.sigma2().astype(np.float64))
+            if flag == "1":
+                ctx.set_observations(p.xy[:n], p.y[:n])
+                ctx.step(p.beta, p.f_min, want_mask=False)
+                mu_f, s2_f = ctx.mu().astype(np.float64), ctx.sigma2().astype(np.float64)
+    scale = np.abs(mu_f).max()
+    for flag in ("1", "0"):
+        assert np.abs(out[flag][0] - mu_f).max() <= TOL["fp32"] * scale, flag
+        assert np.abs(out[flag][1] - s2_f).max() <= TOL["fp32"] * p.sigma_f ** 2, flag
+    assert np.abs(out["1"][0] - out["0"][0]).max() <= 1e-5 * scale and np.abs(out["1"][1] - out["0"][1]).max() <= 1e-5
+
+
 _EAGER_SCRIPT = """
 import sys, numpy as np
 sys.path.insert(0, {root!r})
