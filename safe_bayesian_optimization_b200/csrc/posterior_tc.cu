@@ -1180,14 +1180,15 @@ int32_t tc_eager_launch(sbo_ctx* ctx, int pairs, cudaEvent_t ready) {
 }
 
 // ---- incremental step as a GEMM (posterior_tc_inc.cuh) ---------------------------------------------------------------
-static void tc_inc_shape(const sbo_ctx* ctx, int k, int* lq, int* nslabs, long long* nitems, size_t* bytes) {
+constexpr size_t kIncBandBytes = (size_t)1 << 30;   // planes of P are generated and contracted in bands of at most this size
+
+static void tc_inc_shape(const sbo_ctx* ctx, int k, int* lq, int* nslabs, long long* nitems) {
   int l = 0;
   while ((1 << l) < k) ++l;
   const int rows = ctx->row1 - ctx->row0, slab_rows = BN >> l;
   *lq = l;
   *nslabs = (rows + slab_rows - 1) / slab_rows;
   *nitems = (long long)*nslabs * (((ctx->W + BM - 1) / BM + 1) / 2);
-  *bytes = (size_t)2 * *nslabs * BN * ctx->n_cap * sizeof(__half);
 }
 
 bool tc_inc_applicable(sbo_ctx* ctx, int k) {
@@ -1197,19 +1198,26 @@ bool tc_inc_applicable(sbo_ctx* ctx, int k) {
   if (k < 1 || k > 16 || ctx->m_local == 0 || ctx->n < 1) return false;
   int lq, nslabs;
   long long nitems;
-  size_t bytes;
-  tc_inc_shape(ctx, k, &lq, &nslabs, &nitems, &bytes);
-  // enough (slab, column pair) items for every CTA pair, and the planes of P within 2 GiB
-  return nitems >= ctx->sm_count / 2 && bytes <= ((size_t)2 << 30);
+  tc_inc_shape(ctx, k, &lq, &nslabs, &nitems);
+  // Worth it when the GEMM (waves of (slab, column pair) items over the CTA pairs, ~1 us per 64-observation chunk, plus
+  // ~100 us of plane generation, launches, pipeline fill and the last epilogue: measured 0.15 ms at C2 with one new row
+  // against 0.116 ms for the strip kernel, 0.10 vs 0.19 ms with two) beats the FMA kernels (~1.2e13 cell-observations/s per row).
+  const int clusters = ctx->sm_count / 2, nchunks = (ctx->n + BK - 1) / BK;
+  const double gemm_us = (double)((nitems + clusters - 1) / clusters) * nchunks * 1.0 + 100.0;
+  const double fma_us = (double)ctx->m_local * ctx->n * k / 1.2e13 * 1e6;
+  return gemm_us < fma_us;
 }
 
 int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo) {
   const int k = ctx->n - row_lo;
   int lq, nslabs;
   long long nitems;
-  size_t bytes;
-  tc_inc_shape(ctx, k, &lq, &nslabs, &nitems, &bytes);
+  tc_inc_shape(ctx, k, &lq, &nslabs, &nitems);
   tc_eager_cancel(ctx);
+  const int ld = ctx->n_cap;
+  const size_t slab_bytes = (size_t)2 * BN * ld * sizeof(__half);                       // hi + lo rows of one slab
+  const int band_slabs = (int)std::max<size_t>(1, std::min<size_t>((size_t)nslabs, kIncBandBytes / slab_bytes));
+  const size_t bytes = (size_t)band_slabs * slab_bytes;
   if (ctx->pplanes_cap < bytes) {
     if (ctx->d_pplanes) cudaFree(ctx->d_pplanes);
     ctx->d_pplanes = nullptr;
@@ -1218,21 +1226,7 @@ int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo) {
     ctx->pplanes_cap = bytes;
   }
   SBO_TRY(tc_pack_observations(ctx, ctx->stream));
-  const int rp = nslabs * BN, ld = ctx->n_cap;
   const double inv2l2 = 1.0 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale);
-  pplanes_kernel<<<dim3((unsigned)(rp >> lq), (unsigned)((ld + 255) / 256)), 256, 0, ctx->stream>>>(
-      ctx->d_xy, ctx->d_Linv, ld, ctx->n, row_lo, k, lq, ctx->row1 - ctx->row0, ctx->row0, ctx->y0, ctx->ry, inv2l2,
-      std::ldexp(1.0, ctx->shift_b), rp, reinterpret_cast<__half*>(ctx->d_pplanes));
-  SBO_LAUNCH_CHECK(ctx, "pplanes_kernel");
-  CUtensorMap tmap;
-  const cuuint64_t gdim[2] = {(cuuint64_t)ld, (cuuint64_t)2 * rp};
-  const cuuint64_t gstride[1] = {(cuuint64_t)ld * sizeof(__half)};
-  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)(BN / 2)};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = g_encode_tiled(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, ctx->d_pplanes, gdim, gstride, box, estr,
-                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return fail(ctx, SBO_ERR_CUDA, "launch_posterior_tc_inc: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
   IncParams p;
   p.obs = reinterpret_cast<const float4*>(ctx->d_obs_f32);
   p.w = ctx->d_w;
@@ -1244,29 +1238,49 @@ int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo) {
   p.xscale = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
   p.a_scale = (float)std::ldexp(ctx->cfg.sigma_f * ctx->cfg.sigma_f, ctx->shift_a);
   p.u_unscale = std::ldexp(1.0, -(ctx->shift_a + ctx->shift_b));
-  p.nslabs = nslabs; p.tiles_x = (ctx->W + BM - 1) / BM; p.rp = rp;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)(2 * std::min<long long>(nitems, ctx->sm_count / 2)));
-  cfg.blockDim = dim3(kThreadsTc);
-  cfg.dynamicSmemBytes = tc_smem_bytes<2>();
-  cfg.stream = ctx->stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 2;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  cudaError_t e;
-  switch (lq) {
-    case 0: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<0>, tmap, p); break;
-    case 1: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<1>, tmap, p); break;
-    case 2: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<2>, tmap, p); break;
-    case 3: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<3>, tmap, p); break;
-    default: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<4>, tmap, p); break;
+  p.tiles_x = (ctx->W + BM - 1) / BM;
+  const int ncp = (p.tiles_x + 1) / 2;
+  for (int s0 = 0; s0 < nslabs; s0 += band_slabs) {   // bands run back to back on the stream and reuse the planes buffer
+    const int bs = std::min(band_slabs, nslabs - s0), rp = bs * BN;
+    p.nslabs = bs; p.rp = rp; p.lr_base = (s0 * BN) >> lq;
+    pplanes_kernel<<<dim3((unsigned)(rp >> lq), (unsigned)((ld + 255) / 256)), 256, 0, ctx->stream>>>(
+        ctx->d_xy, ctx->d_Linv, ld, ctx->n, row_lo, k, lq, p.rows_local, ctx->row0, ctx->y0, ctx->ry, inv2l2,
+        std::ldexp(1.0, ctx->shift_b), rp, p.lr_base, reinterpret_cast<__half*>(ctx->d_pplanes));
+    SBO_LAUNCH_CHECK(ctx, "pplanes_kernel");
+    CUtensorMap tmap;
+    const cuuint64_t gdim[2] = {(cuuint64_t)ld, (cuuint64_t)2 * rp};
+    const cuuint64_t gstride[1] = {(cuuint64_t)ld * sizeof(__half)};
+    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)(BN / 2)};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = g_encode_tiled(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, ctx->d_pplanes, gdim, gstride, box, estr,
+                                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+      return fail(ctx, SBO_ERR_CUDA, "launch_posterior_tc_inc: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+    const long long items = (long long)bs * ncp;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * std::min<long long>(items, ctx->sm_count / 2)));
+    cfg.blockDim = dim3(kThreadsTc);
+    cfg.dynamicSmemBytes = tc_smem_bytes<2>();
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e;
+    switch (lq) {
+      case 0: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<0>, tmap, p); break;
+      case 1: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<1>, tmap, p); break;
+      case 2: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<2>, tmap, p); break;
+      case 3: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<3>, tmap, p); break;
+      default: e = cudaLaunchKernelEx(&cfg, posterior_tc_inc_kernel<4>, tmap, p); break;
+    }
+    if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_inc_kernel (cluster launch)");
+    SBO_LAUNCH_CHECK(ctx, "posterior_tc_inc_kernel");
   }
-  if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_inc_kernel (cluster launch)");
-  SBO_LAUNCH_CHECK(ctx, "posterior_tc_inc_kernel");
   return SBO_OK;
 }
 

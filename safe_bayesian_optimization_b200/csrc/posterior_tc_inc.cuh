@@ -27,16 +27,18 @@ struct IncParams {
   int nslabs;          // slabs of 256 rows of P
   int tiles_x;         // 128-column tiles per grid row
   int rp;              // rows of P (multiple of 256); the lo plane starts at row rp of the tensor map
+  int lr_base;         // first (local) grid row of this band: P is generated and contracted band by band to bound its size
 };
 
 // fp16 hi/lo planes of P: row rho = lr * KP + q holds 2^shift_b ey(lr, j) Linv[row_lo + q][j]  (sigma_f^2 rides on A).
 // One thread per (grid row, observation): the fp64 exp is computed once and serves the KP rows of that grid row.
 __global__ void __launch_bounds__(256)
 pplanes_kernel(const double* __restrict__ xy, const double* __restrict__ Linv, int ld, int n, int row_lo, int k, int lq,
-               int rows_local, int row0, double y0, double ry, double inv2l2, double scale, int rp,
+               int rows_local, int row0, double y0, double ry, double inv2l2, double scale, int rp, int lr_base,
                __half* __restrict__ planes) {
   const int j = blockIdx.y * 256 + threadIdx.x;
-  const int lr = blockIdx.x;   // grid rows incl. the padding up to a whole slab
+  const int lb = blockIdx.x;   // row of the band, incl. the padding up to a whole slab
+  const int lr = lr_base + lb;
   if (j >= ld) return;
   double e = 0.0;
   if (j < n && lr < rows_local) {
@@ -48,7 +50,7 @@ pplanes_kernel(const double* __restrict__ xy, const double* __restrict__ Linv, i
     const double x = (q < k && e != 0.0) ? e * Linv[(size_t)(row_lo + q) * ld + j] : 0.0;
     const __half hi = __float2half_rn((float)x);
     const __half lo = __float2half_rn((float)(x - (double)__half2float(hi)));
-    const size_t rho = (size_t)lr * kp + q;
+    const size_t rho = (size_t)lb * kp + q;
     planes[rho * ld + j] = hi;
     planes[((size_t)rp + rho) * ld + j] = lo;
   }
@@ -165,7 +167,7 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
         uint32_t v[32];
         tmem_ld32(taddr + g * 32, v);
         tmem_ld_wait();
-        const int lr0 = (sb * BN + g * 32) >> LQ;  // first grid row of this group of 32 rows of P
+        const int lr0 = p.lr_base + ((sb * BN + g * 32) >> LQ);  // first grid row of this group of 32 rows of P
 #pragma unroll
         for (int t = 0; t < (32 >> LQ); ++t) {
           float usq = 0.f;

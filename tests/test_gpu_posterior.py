@@ -246,7 +246,7 @@ def test_incremental_gemm_kernel(pkg, monkeypatch, ks):
     """fp32, a grid with at least one (256-row slab, column pair) item per CTA pair: the incremental step runs as a
     tensor-core GEMM through the separable RBF (posterior_tc_inc.cuh; kernel_used = 2 for any k <= 16).  Checked against a
     full refresh of the same observations and against the FMA kernels (SBO_TC_INC=0) on the same chain; ragged edges."""
-    n0 = 130
+    n0 = 600   # enough observations for the library's cost model to prefer the GEMM at k = 1 on this grid
     total = n0 + sum(ks)
     p = S.make_problem("C3", n=total, W=1990, H=2400)
     out = {}
