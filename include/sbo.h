@@ -57,7 +57,8 @@ typedef enum {
   SBO_KERNEL_AUTO = 0,     /* tcgen05 path for SBO_FP32, the DMMA kernel for SBO_FP64 */
   SBO_KERNEL_SIMT = 1,     /* force the SIMT kernel (any precision)             */
   SBO_KERNEL_TCGEN05 = 2,  /* force the tcgen05 kernel (SBO_FP32 only)          */
-  SBO_KERNEL_THIN = 3,     /* reported only: the O(m n k) kernel of sbo_step_incremental after <= 8 new rows */
+  SBO_KERNEL_THIN = 3,     /* reported only: the O(m n k) FMA kernel of sbo_step_incremental after <= 8 new rows
+                              (fp32 steps on large grids run as a tensor-core GEMM instead and report SBO_KERNEL_TCGEN05) */
   SBO_KERNEL_DMMA = 4      /* reported only: the fp64 mma.sync kernel that SBO_KERNEL_AUTO selects for SBO_FP64 */
 } sbo_kernel_choice;
 

@@ -24,11 +24,14 @@
 // (profiles/ncu_posterior_tc_r01.md).  CG = 1 is the single-CTA form of the same code.
 //
 // Warp roles (768 threads, 1 CTA/SM, persistent over cell tiles):
-//   0      TMA producer (one lane)     1  MMA issuer (one lane, leader CTA)    2  TMEM alloc/dealloc
+//   0      TMA producer (converged warp, elect.sync)     1  MMA issuer (same, leader CTA)     2  TMEM alloc/dealloc
 //   4-7    epilogue (TMEM lane quarter = warp % 4)
-//   8-23   K* generators: warp w -> cells 32 (w & 3) .. +31, observations 16 ((w - 8) >> 2) .. +15 of the chunk
-// (16 generator warps, 4 per scheduler: with 8 the serial latency of one warp's share of a chunk, not any
-// pipe, paced the tensor core -- profiles/ncu_posterior_tc_r01b.md)
+//   8-23   K* generators in two groups of 8 on alternate visits: warp w -> cells 32 (w & 3) .. +31, observations
+//          32 (((w - 8) >> 2) & 1) .. +31 of the chunk
+// The full refresh over >= 2 row blocks runs posterior_tc_pair.cuh (one K* generation per pair of row blocks), large-grid
+// incremental steps posterior_tc_inc.cuh (a GEMM through the separable RBF); this kernel serves the rest: the
+// incremental rank-k step on the rows that hold the new observations, n <= 256, cta_group::1.
+// (profiles/ncu_posterior_tc_r01d.md has the measurements behind this organisation.)
 #include <cuda.h>
 #include <cuda_fp16.h>
 
