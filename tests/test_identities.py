@@ -1,0 +1,69 @@
+"""The algebra the incremental kernels rely on, checked in fp64 on the CPU against the oracle's full refit
+(oracle/oracle.py: textbook GP regression, Rasmussen & Williams Alg. 2.1).  No GPU.
+
+  after appending k observations, with rows_new = the k new rows of L^-1 and w = L^-1 (y - prior_mean):
+    alpha_new   = [alpha_old; 0] + rows_new^T w_new                       (factor.cu append_alpha_kernel)
+    u_q(cell)   = rows_new[q] . k*(cell)                                  (posterior_thin.cu, posterior_tc_inc.cuh)
+    sigma^2_new = sigma^2_old - sum_q u_q^2,   mu_new = mu_old + sum_q w_q u_q
+  and on a grid, with the separable RBF k*(cell(r, c), j) = sigma_f^2 ex(c, j) ey(r, j):
+    U_q = A P_q^T,  A = ex (W x n),  P_q[r, j] = sigma_f^2 ey(r, j) rows_new[q][j]          (the incremental GEMM)
+"""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from safe_bayesian_optimization_b200 import synthetic as S
+
+
+@pytest.mark.parametrize("n0,k", [(40, 1), (57, 3), (100, 16)])
+def test_incremental_identities(n0, k):
+    p = S.make_problem("C3", n=n0 + k, W=37, H=23)
+    hp = O.Hyper(p.sigma_f, p.length, p.noise_var, p.prior_mean)
+    g = O.Grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+    _, Linv0, alpha0 = O.gp_fit_scipy(p.xy[:n0], p.y[:n0], hp)
+    _, Linv1, alpha1 = O.gp_fit_scipy(p.xy, p.y, hp)
+    mu0, s20 = O.gp_posterior_scipy(p.xy[:n0], hp, Linv0, alpha0, g)
+    mu1, s21 = O.gp_posterior_scipy(p.xy, hp, Linv1, alpha1, g)
+    n = n0 + k
+    # L^-1 only gains rows
+    assert np.abs(Linv1[:n0, :n0] - Linv0).max() < 1e-9
+    rows_new = Linv1[n0:, :]                       # k x n
+    w = Linv1 @ (p.y - hp.prior_mean)
+    alpha_upd = np.concatenate([alpha0, np.zeros(k)]) + rows_new.T @ w[n0:]
+    assert np.abs(alpha_upd - alpha1).max() < 1e-8 * max(1.0, np.abs(alpha1).max())
+    cx, cy = g.cell_xy(np.arange(g.m))
+    Ks = O.rbf_np(np.stack([cx, cy], axis=1), p.xy, hp)          # m x n
+    U = Ks @ rows_new.T                                          # m x k
+    assert np.abs((s20 - (U ** 2).sum(axis=1)) - s21).max() < 1e-9
+    assert np.abs((mu0 + U @ w[n0:]) - mu1).max() < 1e-8 * max(1.0, np.abs(mu1).max())
+    # separability: U_q as a (rows x columns) GEMM over the observations
+    xs = p.x0 + p.rx * np.arange(p.W)
+    ys = p.y0 + p.ry * np.arange(p.H)
+    A = np.exp(-(xs[:, None] - p.xy[None, :, 0]) ** 2 / (2.0 * hp.length ** 2))          # W x n
+    E = np.exp(-(ys[:, None] - p.xy[None, :, 1]) ** 2 / (2.0 * hp.length ** 2))          # H x n
+    for q in range(k):
+        Pq = hp.sigma_f ** 2 * E * rows_new[q][None, :]                                   # H x n
+        Uq = Pq @ A.T                                                                     # H x W, row-major like the grid
+        assert np.abs(Uq.reshape(-1) - U[:, q]).max() < 1e-10
+
+
+def test_skip_bound_is_conservative():
+    """The block-sparse cut-off (posterior_tc.cu tc_skip_bits): dropping every K* entry below 2^-b sigma_f^2 moves sigma^2 by
+    less than 2 n sqrt(sigma_f^2 / noise_var) 2^-b sigma_f^2.  Checked on a spread-out problem with b small enough to bite."""
+    p = S.make_problem("C3", n=300, W=41, H=29)
+    p.xy = p.xy * 5.0
+    p.rx, p.ry = p.rx * 5.0, p.ry * 5.0
+    hp = O.Hyper(p.sigma_f, p.length, p.noise_var, p.prior_mean)
+    g = O.Grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+    _, Linv, alpha = O.gp_fit_scipy(p.xy, p.y, hp)
+    cx, cy = g.cell_xy(np.arange(g.m))
+    Ks = O.rbf_np(np.stack([cx, cy], axis=1), p.xy, hp)
+    V = Ks @ Linv.T
+    s2 = hp.sigma_f ** 2 - (V ** 2).sum(axis=1)
+    for b in (10, 16, 24):
+        Kc = np.where(Ks < 2.0 ** -b * hp.sigma_f ** 2, 0.0, Ks)
+        assert (Kc != Ks).any()
+        Vc = Kc @ Linv.T
+        s2c = hp.sigma_f ** 2 - (Vc ** 2).sum(axis=1)
+        bound = 2.0 * p.n * np.sqrt(hp.sigma_f ** 2 / hp.noise_var) * 2.0 ** -b * hp.sigma_f ** 2
+        assert np.abs(s2c - s2).max() <= bound
