@@ -888,8 +888,11 @@ int32_t factor_full(sbo_ctx* ctx) {
       SBO_TRY(refresh_planes(ctx, 0, eager_rows, sb));
       cudaEvent_t ev_ready = ctx->ev_factor[2 + 2 * (nblk - 1)];   // the last block has no panel: its "panel done" event is free
       SBO_CUDA(ctx, cudaEventRecord(ev_ready, sb));
-      SBO_TRY(tc_eager_launch(ctx, eager_pairs, ev_ready));
-      planes_done = eager_rows;
+      if (tc_eager_launch(ctx, eager_pairs, ev_ready) != SBO_OK) {   // best effort: the fit does not depend on it
+        cudaGetLastError();
+        ctx->eager_inflight = false;
+      }
+      planes_done = eager_rows;   // converted above either way
     }
     if (rem > 0) {
       SBO_CUDA(ctx, cudaStreamWaitEvent(sb, ev_t, 0));
