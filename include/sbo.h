@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define SBO_ABI_VERSION 1
+#define SBO_ABI_VERSION 2   /* 2: sbo_step_out gained low_sigma2 / refreshed / drift; options; row-band planner; device groups */
 
 typedef enum {
   SBO_OK = 0,
@@ -49,8 +49,14 @@ typedef enum {
 } sbo_status;
 
 typedef enum {
-  SBO_FP32 = 0,   /* mu, sigma^2 stored fp32; contraction on tcgen05 (3xTF32, fp32 accum in TMEM) */
-  SBO_FP64 = 1    /* mu, sigma^2 stored fp64; contraction in fp64 FMA                             */
+  SBO_FP32 = 0,   /* mu, sigma^2 stored fp32; contraction on tcgen05: 3xFP16 split (hi.hi + hi.lo + lo.hi, kind::f16,
+                     fp32 accumulators in TMEM) -- the fp32-grade split, 2^-22 per product.  Achieved accuracy (measured at
+                     C2-C4, profiles/parity_*): |d mu| <= 3e-6 max|mu|, |d sigma^2| <= 2e-6 sigma_f^2.  Relative to sigma^2
+                     ITSELF that is 1e-5 only where sigma^2 >= 0.2 sigma_f^2: next to observations (sigma^2 down to ~0.008
+                     sigma_f^2) fp32 storage of |v|^2 ~ 0.99 sigma_f^2 alone is 6e-8 = 7e-6 sigma^2, and the measured figure
+                     is 2.4e-4.  sbo_step_out.low_sigma2 counts the cells with sigma^2 < 0.02 sigma_f^2; use SBO_FP64 when
+                     those need 1e-5 of sigma^2. */
+  SBO_FP64 = 1    /* mu, sigma^2 stored fp64; contraction on the fp64 pipe (DMMA m8n8k4 / DFMA), 1e-10 */
 } sbo_precision;
 
 typedef enum {
@@ -100,6 +106,11 @@ typedef struct {
   float ms_sets;              /* GPU time: CI + mask + argmax kernel                          */
   float ms_comm;              /* GPU time: collective                                         */
   float ms_total;             /* GPU time: whole step on the stream                           */
+  /* ---- ABI 2 ---- */
+  int64_t low_sigma2;         /* cells with sigma^2 < 0.02 sigma_f^2 (where fp32 mode cannot hold 1e-5 of sigma^2 itself) */
+  int32_t refreshed;          /* sbo_step_incremental: 1 = the refresh policy ran a full posterior instead          */
+  float drift;                /* sbo_step_incremental: max |sigma^2 - exact| / sigma_f^2 and |mu - exact| / max(1,|mu|)
+                                 over the re-evaluated sample rows of this step's drift check; -1 = no check this step */
 } sbo_step_out;
 
 /* ---- life cycle --------------------------------------------------------- */
@@ -116,6 +127,28 @@ const char* sbo_status_string(int32_t status);
  * context's own; NULL restores the own stream. */
 int32_t sbo_set_stream(sbo_ctx* ctx, void* cuda_stream);
 int32_t sbo_synchronize(sbo_ctx* ctx);
+
+/* Tuning / A-B switches.  The defaults are the product path; nothing here is read from the environment, so a
+ * shipped libsbo.so computes the same thing whatever the caller's environment holds. */
+typedef enum {
+  SBO_OPT_TC_CTA_GROUP = 1,      /* 2 (default): CTA pairs, tcgen05 cta_group::2; 1: single CTAs                         */
+  SBO_OPT_TC_SKIP = 2,           /* 1 (default): block-sparse walk of K* where the planner finds enough to skip; 0: dense  */
+  SBO_OPT_TC_PAIR = 3,           /* 1 (default): K*-stationary pair kernel for the full refresh; 0: row-block kernel      */
+  SBO_OPT_TC_EAGER = 4,          /* 1 (default): first row-block pairs start inside the factorisation                    */
+  SBO_OPT_TC_INC = 5,            /* 1 (default): incremental steps on large grids as a tensor-core GEMM                  */
+  SBO_OPT_THIN = 6,              /* 1 (default): <= 8 new rows through the O(m n k) FMA kernel                            */
+  SBO_OPT_THIN_2D = 7,           /* 1 (default): fp64 one-new-row step through the 2-D register tile                      */
+  SBO_OPT_TC_GRADED = 8,         /* 1 (default): distance-graded split depth -- (tile, chunk) visits whose K* entries are
+                                    all < 2^-(b-10) sigma_f^2 issue hi.hi only (same error bound as the skipped chunks)   */
+  SBO_OPT_TC_STRIP = 9,          /* tile pairs per strip of the strip-major tile order (default 4; 0 = raster order)       */
+  SBO_OPT_REFRESH_EVERY = 10,    /* sbo_step_incremental runs a full refresh after this many incremental steps
+                                    (default 256 in SBO_FP32, 0 = never in SBO_FP64)                                        */
+  SBO_OPT_DRIFT_CHECK_EVERY = 11,/* every this many incremental steps, re-evaluate SBO_OPT_DRIFT_ROWS grid rows exactly
+                                    and refresh when the deviation exceeds tol / 4 (default 16; 0 = never)                  */
+  SBO_OPT_DRIFT_ROWS = 12        /* grid rows of the drift sample (default 2, spread over the shard)                       */
+} sbo_option;
+int32_t sbo_set_option(sbo_ctx* ctx, int32_t option, int32_t value);
+int32_t sbo_get_option(const sbo_ctx* ctx, int32_t option, int32_t* value);
 
 /* ---- grid --------------------------------------------------------------- */
 
@@ -279,6 +312,13 @@ int32_t sbo_compute_sets_device(sbo_ctx* ctx, const double* mu_dev, const double
 int32_t sbo_comm_unique_id(uint8_t id_out[128]);
 int32_t sbo_comm_init(sbo_ctx* ctx, const uint8_t id[128], int32_t rank, int32_t world);
 int32_t sbo_comm_destroy(sbo_ctx* ctx);
+/* Bands of grid rows of equal estimated WORK for `parts` GPUs (SURVEY 8(e) G1 shards cells by contiguous row bands;
+ * under the block-sparse walk of K* equal row counts are not equal work).  A pure host function of its arguments -- no
+ * GPU, no context -- so every rank of a multi-process job derives the same cuts without a collective.  row_cuts
+ * [parts + 1]: rank g owns rows [row_cuts[g], row_cuts[g + 1]).  max_rows > 0 caps the rows of one band (a shard's
+ * max_cells / W).  cost_share (may be NULL) [parts]: estimated share of the work per band. */
+int32_t sbo_plan_row_bands(const sbo_config* cfg, const double* xy, int32_t n, double x0, double y0, double rx, double ry,
+                           int32_t W, int32_t H, int32_t parts, int32_t max_rows, int32_t* row_cuts, double* cost_share);
 /* Host-side merge of per-shard results with the library's total order
  * (value desc, index asc); used when the host does its own transport. */
 int32_t sbo_merge_step_out(const sbo_step_out* parts, int32_t count, sbo_step_out* merged);
@@ -289,9 +329,14 @@ int32_t sbo_merge_step_out(const sbo_step_out* parts, int32_t count, sbo_step_ou
 int64_t sbo_launch_count(const sbo_ctx* ctx);
 /* How the tcgen05 posterior kernel will run on the current grid and observations: CTAs per MMA group (2 = CTA
  * pair), whether it walks block-sparsity masks of K* (chunks of 64 observations farther than the kernel's reach
- * from a whole cell tile are left out: every skipped entry is < 2^-44 sigma_f^2), and the planner's estimate of the
+ * from a whole cell tile are left out: every skipped entry is < 2^-b sigma_f^2, b from the error budget, see sbo_tc_plan_detail), and the planner's estimate of the
  * share of (row block, chunk) visits that remain (1.0 when dense). */
 int32_t sbo_tc_plan(sbo_ctx* ctx, int32_t* cta_group, int32_t* skipping, double* kept_fraction);
+/* The same plan in full: [0] cut-off in bits (chunks below 2^-bits sigma_f^2 are skipped), [1] ring cut-off (visits below
+ * 2^-ring issue hi.hi only; = [0] when graded split depth is off), [2] kept share of the (row block, chunk) visits,
+ * [3] share of the dense walk's MMA passes that are issued (executed tensor flops / dense 3-product flops), [4] measured
+ * max row 1-norm of L^-1 (0 = a-priori bound in use), [5] tiles per strip of the tile order (0 = raster). */
+int32_t sbo_tc_plan_detail(sbo_ctx* ctx, double out[6]);
 /* Device properties the library sees: SM count, and 1 if tcgen05 path usable. */
 int32_t sbo_device_info(const sbo_ctx* ctx, int32_t* sm_count, int32_t* tcgen05_ok);
 

@@ -16,6 +16,10 @@ LIB_PATH = os.path.join(CSRC, "libsbo.so")
 SBO_FP32, SBO_FP64 = 0, 1
 SBO_KERNEL_AUTO, SBO_KERNEL_SIMT, SBO_KERNEL_TCGEN05 = 0, 1, 2
 
+# sbo_option
+OPTIONS = {"tc_cta_group": 1, "tc_skip": 2, "tc_pair": 3, "tc_eager": 4, "tc_inc": 5, "thin": 6, "thin_2d": 7, "tc_graded": 8,
+           "tc_strip": 9, "refresh_every": 10, "drift_check_every": 11, "drift_rows": 12}
+
 SBO_OK = 0
 SBO_ERR_INVALID_ARG, SBO_ERR_NO_DEVICE, SBO_ERR_CUDA, SBO_ERR_NOT_POSDEF = -1, -2, -3, -4
 SBO_ERR_CAPACITY, SBO_ERR_STATE, SBO_ERR_COMM = -5, -6, -7
@@ -36,7 +40,8 @@ class SboStepOut(C.Structure):
     _fields_ = [("n_cells", C.c_int64), ("safe_count", C.c_int64), ("argmax_ucb", SboArgmax),
                 ("argmax_width", SboArgmax), ("clamped_sigma2", C.c_int64), ("n_obs", C.c_int32),
                 ("kernel_used", C.c_int32), ("ms_posterior", C.c_float), ("ms_sets", C.c_float),
-                ("ms_comm", C.c_float), ("ms_total", C.c_float)]
+                ("ms_comm", C.c_float), ("ms_total", C.c_float),
+                ("low_sigma2", C.c_int64), ("refreshed", C.c_int32), ("drift", C.c_float)]
 
 
 class SboMeasurement(C.Structure):
@@ -84,6 +89,11 @@ SYMBOLS = {
     "sbo_ingest_measurements": (C.c_int32, [_P, C.POINTER(SboMeasurement), C.c_int32, C.POINTER(C.c_int32),
                                             C.POINTER(C.c_int32)]),
     "sbo_tc_plan": (C.c_int32, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double)]),
+    "sbo_tc_plan_detail": (C.c_int32, [_P, _D]),
+    "sbo_set_option": (C.c_int32, [_P, C.c_int32, C.c_int32]),
+    "sbo_get_option": (C.c_int32, [_P, C.c_int32, C.POINTER(C.c_int32)]),
+    "sbo_plan_row_bands": (C.c_int32, [C.POINTER(SboConfig), _D, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double,
+                                       C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32), _D]),
     "sbo_copy_mu": (C.c_int32, [_P, _P]),
     "sbo_copy_sigma2": (C.c_int32, [_P, _P]),
     "sbo_copy_mu_f64": (C.c_int32, [_P, _D]),

@@ -40,7 +40,7 @@ void free_all(sbo_ctx* c) {
   void* dev[] = {c->d_xy, c->d_r, c->d_A, c->d_Linv, c->d_Dinv, c->d_alpha, c->d_w, c->d_small, c->d_info,
                  c->d_planes, c->d_alpha_f32, c->d_obs_f32, c->d_chunk_bbox, c->d_fr_img, c->d_fr_lut, c->d_cp_idx, c->d_cp_counts, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
                  c->d_partials, c->d_result, c->d_ticket, c->d_frontier, c->d_sel_keys, c->d_sel_width, c->d_sel_out,
-                 c->d_gather};
+                 c->d_gather, c->d_drift_mu, c->d_drift_s2, c->d_drift_out};
   for (void* p : dev)
     if (p) cudaFree(p);
   if (c->h_result) cudaFreeHost(c->h_result);
@@ -79,12 +79,88 @@ void fill_out(const sbo_ctx* ctx, const SetsResult& r, int kernel_used, const fl
   out->argmax_width.idx = r.width_idx;
   out->argmax_width.value = r.width_idx >= 0 ? r.width_val : 0.0;
   out->clamped_sigma2 = r.clamped;
+  out->low_sigma2 = r.low_sigma2;
+  out->refreshed = ctx->inc_refreshed;
+  out->drift = ctx->inc_drift;
   out->n_obs = ctx->n;
   out->kernel_used = kernel_used;
   out->ms_posterior = ms[0];
   out->ms_sets = ms[1];
   out->ms_comm = ms[2];
   out->ms_total = ms[3];
+}
+
+// Drift estimate of the incremental chain: `drift_rows` grid rows of this shard are re-evaluated from scratch with the
+// full-refresh kernel of the context's precision (O(W n^2) each) into scratch buffers and compared with the stored,
+// incrementally updated values.  The result is read with the step's record (finish_step); above tol / 4 the next
+// incremental step becomes a full refresh.
+template <typename T>
+__global__ void drift_compare_kernel(const T* __restrict__ mu, const T* __restrict__ s2, const T* __restrict__ mu_x,
+                                     const T* __restrict__ s2_x, int W, long long off, double inv_sf2, double* __restrict__ out) {
+  double dm = 0.0, ds = 0.0;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < W; c += gridDim.x * blockDim.x) {
+    const double m0 = (double)mu_x[c], m1 = (double)mu[off + c];
+    dm = fmax(dm, fabs(m1 - m0) / fmax(1.0, fabs(m0)));
+    ds = fmax(ds, fabs((double)s2[off + c] - (double)s2_x[c]) * inv_sf2);
+  }
+  for (int d = 16; d > 0; d >>= 1) {
+    dm = fmax(dm, __shfl_xor_sync(0xffffffffu, dm, d));
+    ds = fmax(ds, __shfl_xor_sync(0xffffffffu, ds, d));
+  }
+  if ((threadIdx.x & 31) == 0) {   // non-negative doubles order like their bit patterns
+    atomicMax(reinterpret_cast<unsigned long long*>(out), (unsigned long long)__double_as_longlong(dm));
+    atomicMax(reinterpret_cast<unsigned long long*>(out + 1), (unsigned long long)__double_as_longlong(ds));
+  }
+}
+
+int32_t drift_check(sbo_ctx* ctx) {
+  const int rows = ctx->row1 - ctx->row0, W = ctx->W;
+  const int dr = std::min(std::max(ctx->opt.drift_rows, 1), rows);
+  if (rows <= 0 || ctx->n == 0) return SBO_OK;
+  int which = 0;
+  SBO_TRY(pick_kernel(ctx, &which));
+  const size_t es = elem_size(ctx);
+  if (ctx->drift_cap < W) {
+    for (void** p : {&ctx->d_drift_mu, &ctx->d_drift_s2}) {
+      if (*p) cudaFree(*p);
+      *p = nullptr;
+      SBO_CUDA(ctx, cudaMalloc(p, es * (size_t)W));
+    }
+    if (!ctx->d_drift_out) SBO_CUDA(ctx, cudaMalloc(&ctx->d_drift_out, 2 * sizeof(double)));
+    ctx->drift_cap = W;
+  }
+  SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_drift_out, 0, 2 * sizeof(double), ctx->stream));
+  // the launchers read the shard geometry and the output buffers from the context: point them at one row + the scratch
+  const int row0 = ctx->row0, row1 = ctx->row1;
+  const int64_t m_local = ctx->m_local, cell0 = ctx->cell0;
+  void* mu = ctx->d_mu;
+  void* s2 = ctx->d_s2;
+  int32_t st = SBO_OK;
+  for (int i = 0; i < dr && st == SBO_OK; ++i) {
+    const int lr = (int)(((2LL * i + 1) * rows) / (2LL * dr));   // spread over the shard
+    ctx->row0 = row0 + lr; ctx->row1 = row0 + lr + 1;
+    ctx->m_local = W; ctx->cell0 = (int64_t)ctx->row0 * W;
+    ctx->d_mu = ctx->d_drift_mu; ctx->d_s2 = ctx->d_drift_s2;
+    if (which == SBO_KERNEL_TCGEN05) st = launch_posterior_tc(ctx, 0, ctx->n, false);
+    else if (which == SBO_KERNEL_DMMA) st = launch_posterior_f64(ctx, 0, ctx->n, false);
+    else st = launch_posterior_simt(ctx, 0, ctx->n, false);
+    ctx->row0 = row0; ctx->row1 = row1; ctx->m_local = m_local; ctx->cell0 = cell0; ctx->d_mu = mu; ctx->d_s2 = s2;
+    if (st != SBO_OK) break;
+    const double inv_sf2 = 1.0 / (ctx->cfg.sigma_f * ctx->cfg.sigma_f);
+    const long long off = (long long)lr * W;
+    if (ctx->cfg.precision == SBO_FP64)
+      drift_compare_kernel<double><<<std::min((W + 255) / 256, 64), 256, 0, ctx->stream>>>(
+          static_cast<const double*>(mu), static_cast<const double*>(s2), static_cast<const double*>(ctx->d_drift_mu),
+          static_cast<const double*>(ctx->d_drift_s2), W, off, inv_sf2, ctx->d_drift_out);
+    else
+      drift_compare_kernel<float><<<std::min((W + 255) / 256, 64), 256, 0, ctx->stream>>>(
+          static_cast<const float*>(mu), static_cast<const float*>(s2), static_cast<const float*>(ctx->d_drift_mu),
+          static_cast<const float*>(ctx->d_drift_s2), W, off, inv_sf2, ctx->d_drift_out);
+    SBO_LAUNCH_CHECK(ctx, "drift_compare_kernel");
+  }
+  SBO_TRY(st);
+  ctx->drift_pending = true;
+  return SBO_OK;
 }
 
 // posterior (full or incremental) + sets + collective, all on ctx->stream; events around each phase.
@@ -95,16 +171,28 @@ int32_t run_step(sbo_ctx* ctx, double beta, double f_min, bool incremental, int*
   SBO_TRY(pick_kernel(ctx, &which));
   int j_lo = 0, j_hi = ctx->n;
   bool accumulate = false;
+  ctx->inc_refreshed = 0;
+  ctx->inc_drift = -1.f;
   if (incremental) {
     if (!ctx->posterior_valid || ctx->posterior_n > ctx->n)
       return fail(ctx, SBO_ERR_STATE, "sbo_step_incremental: no previous posterior on this grid for a prefix of the observations");
-    j_lo = ctx->posterior_n;
-    accumulate = true;
+    // Refresh policy: the incremental update subtracts from the stored sigma^2 and adds to mu, so rounding
+    // accumulates; the reference rebuilds all state every step (:633-644) and cannot drift.  A full posterior replaces the
+    // update every `refresh_every` incremental steps, or when the last drift check (below) came out above tol / 4.
+    int every = ctx->opt.refresh_every;
+    if (every < 0) every = ctx->cfg.precision == SBO_FP64 ? 0 : 256;
+    if (ctx->force_refresh || (every > 0 && ctx->inc_steps + 1 >= every)) {
+      incremental = false;
+      ctx->inc_refreshed = 1;
+    } else {
+      j_lo = ctx->posterior_n;
+      accumulate = true;
+    }
   }
   SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
   // a few new rows: the thin SIMT kernel (O(m n k)); otherwise the row blocks that hold them
-  static const bool thin_off = std::getenv("SBO_THIN") && std::atoi(std::getenv("SBO_THIN")) == 0;
+  const bool thin_off = !ctx->opt.thin;
   if (incremental && which == SBO_KERNEL_TCGEN05 && tc_inc_applicable(ctx, j_hi - j_lo)) {
     // large grid, fp32: the k projections as a tensor-core GEMM through the separable kernel (posterior_tc_inc.cuh)
     SBO_TRY(launch_posterior_tc_inc(ctx, j_lo));
@@ -117,6 +205,13 @@ int32_t run_step(sbo_ctx* ctx, double beta, double f_min, bool incremental, int*
     SBO_TRY(launch_posterior_f64(ctx, j_lo, j_hi, accumulate));
   } else {
     SBO_TRY(launch_posterior_simt(ctx, j_lo, j_hi, accumulate));
+  }
+  if (incremental) {
+    ++ctx->inc_steps;
+    if (ctx->opt.drift_check_every > 0 && ctx->inc_steps % ctx->opt.drift_check_every == 0) SBO_TRY(drift_check(ctx));
+  } else {
+    ctx->inc_steps = 0;
+    ctx->force_refresh = false;
   }
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
   SBO_TRY(launch_sets_step(ctx, beta, f_min));
@@ -133,8 +228,18 @@ int32_t run_step(sbo_ctx* ctx, double beta, double f_min, bool incremental, int*
 
 int32_t finish_step(sbo_ctx* ctx, int kernel_used, sbo_step_out* out) {
   SBO_CUDA(ctx, cudaMemcpyAsync(ctx->h_result, ctx->d_result, sizeof(SetsResult), cudaMemcpyDeviceToHost, ctx->stream));
+  double drift[2] = {0.0, 0.0};
+  const bool drift_read = ctx->drift_pending;
+  if (drift_read)
+    SBO_CUDA(ctx, cudaMemcpyAsync(drift, ctx->d_drift_out, sizeof(drift), cudaMemcpyDeviceToHost, ctx->stream));
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[4], ctx->stream));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (drift_read) {
+    ctx->drift_pending = false;
+    ctx->inc_drift = (float)std::max(drift[0], drift[1]);
+    const double tol = ctx->cfg.precision == SBO_FP64 ? 1e-10 : 1e-5;
+    if (std::max(drift[0], drift[1]) > 0.25 * tol) ctx->force_refresh = true;   // the next incremental step refreshes
+  }
   if (out) {
     float ms[4] = {0, 0, 0, 0};
     cudaEventElapsedTime(&ms[0], ctx->ev[0], ctx->ev[1]);
@@ -222,7 +327,7 @@ int32_t sbo_create(const sbo_config* cfg, sbo_ctx** out) {
   CREATE_CUDA(cudaMalloc(&c->d_alpha, sizeof(double) * nc));
   CREATE_CUDA(cudaMalloc(&c->d_w, sizeof(double) * nc));
   CREATE_CUDA(cudaMalloc(&c->d_small, sizeof(double) * (2 * (size_t)kMaxAppend * nc + 2 * (size_t)kMaxAppend * kMaxAppend)));
-  CREATE_CUDA(cudaMalloc(&c->d_info, sizeof(int)));
+  CREATE_CUDA(cudaMalloc(&c->d_info, 32));   // Cholesky status + measured row 1-norms of L^-1 (factor.cu InfoRecord)
   CREATE_CUDA(cudaMemset(c->d_Linv, 0, sizeof(double) * nc * nc));
   CREATE_CUDA(cudaMemset(c->d_alpha, 0, sizeof(double) * nc));
   CREATE_CUDA(cudaMemset(c->d_xy, 0, sizeof(double) * 2 * nc));
@@ -317,6 +422,63 @@ int32_t sbo_tc_plan(sbo_ctx* ctx, int32_t* cta_group, int32_t* skipping, double*
   return SBO_OK;
 }
 
+static int* option_slot(sbo_ctx* c, int32_t option) {
+  switch (option) {
+    case SBO_OPT_TC_CTA_GROUP: return &c->tc_cg;
+    case SBO_OPT_TC_PAIR: return &c->opt.tc_pair;
+    case SBO_OPT_TC_EAGER: return &c->opt.tc_eager;
+    case SBO_OPT_TC_INC: return &c->opt.tc_inc;
+    case SBO_OPT_THIN: return &c->opt.thin;
+    case SBO_OPT_THIN_2D: return &c->opt.thin_2d;
+    case SBO_OPT_TC_GRADED: return &c->opt.tc_graded;
+    case SBO_OPT_TC_STRIP: return &c->opt.tc_strip;
+    case SBO_OPT_REFRESH_EVERY: return &c->opt.refresh_every;
+    case SBO_OPT_DRIFT_CHECK_EVERY: return &c->opt.drift_check_every;
+    case SBO_OPT_DRIFT_ROWS: return &c->opt.drift_rows;
+    default: return nullptr;
+  }
+}
+
+int32_t sbo_set_option(sbo_ctx* ctx, int32_t option, int32_t value) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (option == SBO_OPT_TC_SKIP) {
+    ctx->tc_skip = value != 0;
+    ctx->tc_skip_plan = -1;
+    return SBO_OK;
+  }
+  int* slot = option_slot(ctx, option);
+  if (!slot) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_option: unknown option");
+  if (value < 0 && option != SBO_OPT_REFRESH_EVERY) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_option: negative value");
+  if (option == SBO_OPT_TC_CTA_GROUP) {
+    if (value != 1 && value != 2) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_option: SBO_OPT_TC_CTA_GROUP is 1 or 2");
+    SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+    tc_eager_cancel(ctx);
+    cudaStreamSynchronize(ctx->stream);
+    return ctx->tc_ok ? tc_set_cta_group(ctx, value) : SBO_OK;
+  }
+  if (option == SBO_OPT_TC_EAGER && value == 0) tc_eager_cancel(ctx);
+  if (option == SBO_OPT_TC_GRADED) ctx->tc_skip_plan = -1;
+  *slot = value;
+  return SBO_OK;
+}
+
+int32_t sbo_get_option(const sbo_ctx* ctx, int32_t option, int32_t* value) {
+  if (!ctx || !value) return SBO_ERR_INVALID_ARG;
+  if (option == SBO_OPT_TC_SKIP) {
+    *value = ctx->tc_skip ? 1 : 0;
+    return SBO_OK;
+  }
+  const int* slot = option_slot(const_cast<sbo_ctx*>(ctx), option);
+  if (!slot) return SBO_ERR_INVALID_ARG;
+  *value = *slot;
+  return SBO_OK;
+}
+
+int32_t sbo_tc_plan_detail(sbo_ctx* ctx, double out[6]) {
+  if (!ctx || !out) return SBO_ERR_INVALID_ARG;
+  return tc_plan_detail(ctx, out);
+}
+
 int32_t sbo_device_info(const sbo_ctx* ctx, int32_t* sm_count, int32_t* tcgen05_ok) {
   if (!ctx) return SBO_ERR_INVALID_ARG;
   if (sm_count) *sm_count = ctx->sm_count;
@@ -331,28 +493,13 @@ int32_t sbo_device_info(const sbo_ctx* ctx, int32_t* sm_count, int32_t* tcgen05_
 // ---------------------------------------------------------------------------------------------
 extern "C" {
 
-int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, int32_t n) {
-  if (!ctx) return SBO_ERR_INVALID_ARG;
-  if (n < 0 || (n > 0 && (!xy || !y))) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_observations: null input or n < 0");
-  if (n > ctx->n_cap || n > ctx->cfg.max_obs) return fail(ctx, SBO_ERR_CAPACITY, "sbo_set_observations: n exceeds max_obs");
-  if (!all_finite(xy, 2 * (size_t)n) || !all_finite(y, (size_t)n))
-    return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_observations: NaN/Inf in the observations");
+// Sort spatially, upload, factorise.  On failure the factor buffers hold garbage (the caller decides what to restore).
+static int32_t fit_from(sbo_ctx* ctx, const double* xy, const double* y, int32_t n) {
   SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   tc_eager_cancel(ctx);
   // spatial order: bands of two length-scales in y, by x inside a band (see sbo_copy_order)
-  std::vector<int32_t> order((size_t)n);
-  for (int i = 0; i < n; ++i) order[i] = i;
-  if (n > 1) {
-    double ymin = xy[1];
-    for (int i = 1; i < n; ++i) ymin = std::min(ymin, xy[2 * i + 1]);
-    const double inv_band = 1.0 / (2.0 * ctx->cfg.length_scale);
-    std::vector<long long> band((size_t)n);
-    for (int i = 0; i < n; ++i) band[i] = (long long)std::floor((xy[2 * i + 1] - ymin) * inv_band);
-    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
-      if (band[a] != band[b]) return band[a] < band[b];
-      return xy[2 * a] < xy[2 * b];
-    });
-  }
+  std::vector<int32_t> order;
+  spatial_order(ctx->cfg.length_scale, xy, n, order);
   std::vector<double> sxy(2 * (size_t)n), r((size_t)n);
   for (int i = 0; i < n; ++i) {
     sxy[2 * i] = xy[2 * (size_t)order[i]];
@@ -377,21 +524,52 @@ int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, in
   const int32_t st = factor_full(ctx);
   if (st != SBO_OK) {
     tc_eager_cancel(ctx);
-    ctx->n = 0;  // the factor buffers were overwritten: no observations until the next successful fit
-    ctx->order.clear();
-    ctx->h_xy_sorted.clear();
-    ctx->h_xy_arrival.clear();
-    ctx->h_y_arrival.clear();
-    ctx->n_at_fit = 0;
-    cudaMemsetAsync(ctx->d_Linv, 0, sizeof(double) * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
-    cudaMemsetAsync(ctx->d_alpha, 0, sizeof(double) * (size_t)ctx->n_cap, ctx->stream);
-    if (ctx->d_planes) cudaMemsetAsync(ctx->d_planes, 0, sizeof(uint16_t) * 2 * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
-    if (ctx->d_alpha_f32) cudaMemsetAsync(ctx->d_alpha_f32, 0, sizeof(float) * (size_t)ctx->n_cap, ctx->stream);
-    cudaStreamSynchronize(ctx->stream);
     return st;
   }
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return SBO_OK;
+}
+
+int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, int32_t n) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (n < 0 || (n > 0 && (!xy || !y))) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_observations: null input or n < 0");
+  if (n > ctx->n_cap || n > ctx->cfg.max_obs) return fail(ctx, SBO_ERR_CAPACITY, "sbo_set_observations: n exceeds max_obs");
+  if (!all_finite(xy, 2 * (size_t)n) || !all_finite(y, (size_t)n))
+    return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_observations: NaN/Inf in the observations");
+  // "ctx left in last good state" (SURVEY B4): the fit overwrites the factor buffers in place (L^-1 alone is 2 GiB at
+  // n = 16 384, so there is no second copy); a failed fit is followed by a refit of the observations held before the
+  // call -- a cost paid on the failure path only.  The stored posterior stays valid if it belonged to exactly that set.
+  const int32_t prev_n = ctx->n;
+  const std::vector<double> prev_xy(ctx->h_xy_arrival.begin(), ctx->h_xy_arrival.begin() + 2 * (size_t)prev_n);
+  const std::vector<double> prev_y(ctx->h_y_arrival.begin(), ctx->h_y_arrival.begin() + (size_t)prev_n);
+  const bool prev_post = ctx->posterior_valid && ctx->posterior_n == prev_n;
+  const PosteriorSource prev_source = ctx->source;
+  const int32_t st = fit_from(ctx, xy, y, n);
+  if (st == SBO_OK) return SBO_OK;
+  const std::string why = ctx->err;
+  int32_t st2 = SBO_ERR_STATE;
+  if (prev_n > 0) st2 = fit_from(ctx, prev_xy.data(), prev_y.data(), prev_n);
+  if (st2 == SBO_OK) {
+    ctx->posterior_valid = prev_post;
+    ctx->source = prev_source;
+    ctx->err = why + " (the previous " + std::to_string(prev_n) + " observations were restored)";
+    return st;
+  }
+  // nothing to go back to (first fit, or the restore failed as well): an empty, consistent observation set
+  ctx->n = 0;
+  ctx->order.clear();
+  ctx->h_xy_sorted.clear();
+  ctx->h_xy_arrival.clear();
+  ctx->h_y_arrival.clear();
+  ctx->n_at_fit = 0;
+  ctx->posterior_valid = false;
+  cudaMemsetAsync(ctx->d_Linv, 0, sizeof(double) * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
+  cudaMemsetAsync(ctx->d_alpha, 0, sizeof(double) * (size_t)ctx->n_cap, ctx->stream);
+  if (ctx->d_planes) cudaMemsetAsync(ctx->d_planes, 0, sizeof(uint16_t) * 2 * (size_t)ctx->n_cap * ctx->n_cap, ctx->stream);
+  if (ctx->d_alpha_f32) cudaMemsetAsync(ctx->d_alpha_f32, 0, sizeof(float) * (size_t)ctx->n_cap, ctx->stream);
+  cudaStreamSynchronize(ctx->stream);
+  ctx->err = why;
+  return st;
 }
 
 int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y, int32_t k) {
@@ -448,10 +626,11 @@ int32_t sbo_ingest_measurements(sbo_ctx* ctx, const sbo_measurement* recs, int32
   const bool refit = ctx->n == 0 || tail > std::max<int64_t>(64, ctx->n_at_fit / 4);
   int32_t st;
   if (refit) {
-    ctx->h_xy_arrival.insert(ctx->h_xy_arrival.end(), xy.begin(), xy.end());
-    ctx->h_y_arrival.insert(ctx->h_y_arrival.end(), y.begin(), y.end());
-    const int32_t n_all = (int32_t)ctx->h_y_arrival.size();
-    st = sbo_set_observations(ctx, ctx->h_xy_arrival.data(), ctx->h_y_arrival.data(), n_all);
+    std::vector<double> all_xy(ctx->h_xy_arrival.begin(), ctx->h_xy_arrival.begin() + 2 * (size_t)ctx->n);
+    std::vector<double> all_y(ctx->h_y_arrival.begin(), ctx->h_y_arrival.begin() + (size_t)ctx->n);
+    all_xy.insert(all_xy.end(), xy.begin(), xy.end());
+    all_y.insert(all_y.end(), y.begin(), y.end());
+    st = sbo_set_observations(ctx, all_xy.data(), all_y.data(), (int32_t)all_y.size());   // failure: previous set restored
     if (refitted && st == SBO_OK) *refitted = 1;
   } else {
     st = sbo_append_observations(ctx, xy.data(), y.data(), count);
@@ -726,6 +905,9 @@ int32_t sbo_merge_step_out(const sbo_step_out* parts, int32_t count, sbo_step_ou
     if (host_better(o.argmax_width, r.argmax_width)) r.argmax_width = o.argmax_width;
     r.safe_count += o.safe_count;
     r.clamped_sigma2 += o.clamped_sigma2;
+    r.low_sigma2 += o.low_sigma2;
+    r.refreshed = r.refreshed || o.refreshed;
+    r.drift = std::max(r.drift, o.drift);
     r.n_cells += o.n_cells;
     r.ms_posterior = std::max(r.ms_posterior, o.ms_posterior);
     r.ms_sets = std::max(r.ms_sets, o.ms_sets);

@@ -1,8 +1,8 @@
 // comm.cu -- multi-GPU reduction of the per-shard step results.
 //
 // Cells shard across GPUs by row bands (one process per GPU); the only exchange on the path is
-// the argmax / safe-count reduction.  Each rank contributes one 48-byte record
-// (ucb value+index, width value+index, safe count, clamped count); a single ncclAllGather moves
+// the argmax / safe-count reduction.  Each rank contributes one 56-byte record
+// (ucb value+index, width value+index, safe / clamped / low-sigma^2 counts); a single ncclAllGather moves
 // the records over NVLink and a one-warp kernel folds them with the library's total order
 // (value desc, index asc).  fp64 values do not fit a packed 64-bit max-key, hence gather+fold
 // rather than ncclMax on a key.
@@ -47,7 +47,8 @@ NcclApi& nccl() {
     if (api.handle) break;
   }
   if (!api.handle) {
-    api.err = std::string("cannot dlopen libnccl.so.2 (set SBO_NCCL_LIB): ") + (dlerror() ? dlerror() : "");
+    const char* e = dlerror();   // (one call: dlerror clears the state it returns)
+    api.err = std::string("cannot dlopen libnccl.so.2 (set SBO_NCCL_LIB): ") + (e ? e : "");
     return api;
   }
   api.get_unique_id = (GetUniqueIdFn)dlsym(api.handle, "ncclGetUniqueId");
@@ -71,6 +72,7 @@ __global__ void fold_records_kernel(const SetsResult* __restrict__ parts, int co
     if (better(o.width_val, o.width_idx, r.width_val, r.width_idx)) { r.width_val = o.width_val; r.width_idx = o.width_idx; }
     r.safe_count += o.safe_count;
     r.clamped += o.clamped;
+    r.low_sigma2 += o.low_sigma2;
   }
   *out = r;
 }

@@ -25,6 +25,14 @@ struct SetsResult {
   long long width_idx;
   long long safe_count;
   long long clamped;
+  long long low_sigma2;   // cells with sigma^2 < 0.02 sigma_f^2
+};
+
+// sbo_set_option state (include/sbo.h sbo_option); the defaults are the product path
+struct Options {
+  int tc_pair = 1, tc_eager = 1, tc_inc = 1, thin = 1, thin_2d = 1, tc_graded = 1, tc_strip = 4;
+  int refresh_every = -1;       // -1: by precision (256 fp32, never fp64)
+  int drift_check_every = 16, drift_rows = 2;
 };
 
 enum class PosteriorSource : int { kNone = 0, kStep = 1, kHostArrays = 2 };
@@ -43,6 +51,17 @@ struct sbo_ctx {
   std::vector<cudaEvent_t> ev_factor;     // [0] fork/join, [1 + 2k] diag k done, [2 + 2k] panel k done
   std::string err;
   int64_t launches = 0;
+  sbo::Options opt;
+  bool attr_factor = false, attr_f64 = false;   // per-context (= per-device) cudaFuncSetAttribute done
+  int inc_steps = 0;             // incremental steps since the last full posterior (refresh policy)
+  int inc_refreshed = 0;         // the last sbo_step_incremental ran a full refresh
+  float inc_drift = -1.f;        // result of the last drift check (-1: none)
+  void* d_drift_mu = nullptr;    // drift check scratch: exact mu / sigma^2 of the sample rows (lazy)
+  void* d_drift_s2 = nullptr;
+  double* d_drift_out = nullptr; // [2] max deviations
+  int64_t drift_cap = 0;
+  bool drift_pending = false;   // a drift check was queued in this step: finish_step reads it
+  bool force_refresh = false;   // the last drift check exceeded tol / 4: the next incremental step is a full refresh
 
   // grid
   bool grid_set = false;
@@ -72,6 +91,8 @@ struct sbo_ctx {
   std::vector<double> h_xy_arrival, h_y_arrival;   // every observation in arrival order (ingestion refits from these)
   int n_at_fit = 0;              // observations at the last full factorisation
   double tc_kept_frac = 1.0;     // planner's estimate: share of (row block, chunk) visits that survive the box test
+  double tc_pass_frac = 1.0;     // ... and share of the dense walk's MMA passes that are issued (ring visits issue 1 of 3)
+  double linv_r1 = 0.0;          // max row 1-norm of L^-1, measured by the fit / append (0: unknown)
   int tc_skip_plan = -1;         // cached decision of tc_plan_skip for this grid + observation set (-1: stale)
   std::vector<double> h_xy_sorted;  // host copy of d_xy (internal order), for the skip planner
   float* d_chunk_bbox = nullptr; // [n_cap / 64] float4 scaled bounding boxes of the observation chunks
@@ -172,15 +193,26 @@ int32_t factor_full(sbo_ctx* ctx);                 // d_xy, d_r, n -> d_A (L), d
 int32_t factor_append(sbo_ctx* ctx, int k);        // rows [n, n+k) already in d_xy / d_r
 int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end, cudaStream_t stream = nullptr);   // nullptr: ctx->stream
 
+// plan.cu (host)
+void spatial_order(double length_scale, const double* xy, int n, std::vector<int32_t>& order);
+double tc_xscale(const sbo_config& cfg);
+void chunk_boxes(const double* xy_sorted, int n, double xs, std::vector<double>& box);
+void tile_visit_cost(const std::vector<double>& box, int n, double xlo, double xhi, double y, double bits, double ring,
+                     double* total, double* kept, double* passes);
+double tc_skip_bits_of(const sbo_config& cfg, int n, double r1);
+double tc_ring_bits_of(const sbo_config& cfg, int n, double r1, int shift_a);
+
 // posterior_simt.cu
 int32_t launch_posterior_simt(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
 
 // posterior_tc.cu
 int32_t tc_init(sbo_ctx* ctx);                     // tensor map, attributes, plane scales; sets ctx->tc_ok
+int32_t tc_set_cta_group(sbo_ctx* ctx, int cg);    // re-encodes the tensor map of the planes for 1 or 2 CTAs per MMA group
 void tc_plane_shifts(const sbo_config& cfg, int* shift_a, int* shift_b);
 int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);
 void tc_destroy(sbo_ctx* ctx);
 bool tc_plan_skip(sbo_ctx* ctx);                   // worth walking chunk masks on this grid / observation set?
+int32_t tc_plan_detail(sbo_ctx* ctx, double out[6]);
 bool tc_inc_applicable(sbo_ctx* ctx, int k);       // incremental step with k new rows through the GEMM kernel?
 int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo);
 int tc_eager_pairs(sbo_ctx* ctx);                   // row-block pairs factor_full may launch early (0: none)

@@ -763,10 +763,32 @@ append_alpha_kernel(const double* __restrict__ X, int ld, int n, int k, const do
   if (alpha_f32) alpha_f32[c] = (float)a;
 }
 
-int32_t check_info(sbo_ctx* ctx, const char* what) {
-  int info = 0;
-  SBO_CUDA(ctx, cudaMemcpyAsync(&info, ctx->d_info, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+// max over rows [row_begin, row_end) of sum_c |X[row][c]| (c <= row): one warp per row, max by atomicMax on the bit
+// pattern (non-negative doubles order like their bits).  Feeds the cut-off of the block-sparse walk (plan.cu).
+__global__ void __launch_bounds__(256)
+row_l1_max_kernel(const double* __restrict__ X, int ld, int row_begin, int row_end, double* __restrict__ out) {
+  const int row = row_begin + ((blockIdx.x * 256 + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (row >= row_end) return;
+  const double* x = X + (size_t)row * ld;
+  double s = 0.0;
+  for (int c = lane; c <= row; c += 32) s += fabs(x[c]);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+  if (lane == 0) atomicMax(reinterpret_cast<unsigned long long*>(out), (unsigned long long)__double_as_longlong(s));
+}
+
+// d_info: [0] Cholesky status (int), [8] max row 1-norm of L^-1 over the rows of a full fit, [16] over the rows of an append
+struct InfoRecord {
+  int info, pad;
+  double r1_full, r1_new;
+};
+
+int32_t check_info(sbo_ctx* ctx, const char* what, InfoRecord* rec_out = nullptr) {
+  InfoRecord rec;
+  SBO_CUDA(ctx, cudaMemcpyAsync(&rec, ctx->d_info, sizeof(rec), cudaMemcpyDeviceToHost, ctx->stream));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (rec_out) *rec_out = rec;
+  const int info = rec.info;
   if (info != 0)
     return fail(ctx, SBO_ERR_NOT_POSDEF,
                 std::string(what) + ": covariance not positive definite at row " + std::to_string(info - 1));
@@ -784,6 +806,14 @@ int32_t compute_alpha(sbo_ctx* ctx, int n) {
 }
 
 }  // namespace
+
+// the shared-memory opt-in is per device: kept per context, not in a process-wide flag
+static int32_t ensure_factor_attr(sbo_ctx* ctx) {
+  if (ctx->attr_factor) return SBO_OK;
+  SBO_CUDA(ctx, cudaFuncSetAttribute(diag_chol_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDiagSmem));
+  ctx->attr_factor = true;
+  return SBO_OK;
+}
 
 static int32_t ensure_factor_streams(sbo_ctx* ctx, int nblk) {
   if (!ctx->aux_stream) SBO_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking));
@@ -815,13 +845,9 @@ int32_t factor_full(sbo_ctx* ctx) {
   const double inv2l2 = 1.0 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale);
   cudaStream_t st = ctx->stream;
 
-  static bool attr_done = false;
-  if (!attr_done) {
-    SBO_CUDA(ctx, cudaFuncSetAttribute(diag_chol_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)kDiagSmem));
-    attr_done = true;
-  }
-  SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_info, 0, sizeof(int), st));
+  SBO_TRY(ensure_factor_attr(ctx));
+  ctx->linv_r1 = 0.0;
+  SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_info, 0, sizeof(InfoRecord), st));
   SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_Linv, 0, sizeof(double) * (size_t)ld * ld, st));
   SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_alpha, 0, sizeof(double) * (size_t)ld, st));
   if (ctx->d_alpha_f32) SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_alpha_f32, 0, sizeof(float) * (size_t)ld, st));
@@ -907,7 +933,11 @@ int32_t factor_full(sbo_ctx* ctx) {
     clear_pad_kernel<<<(np - n + 127) / 128, 128, 0, st>>>(ctx->d_Linv, ld, n, np);
     SBO_LAUNCH_CHECK(ctx, "clear_pad_kernel");
   }
-  SBO_TRY(check_info(ctx, "sbo_set_observations"));
+  row_l1_max_kernel<<<(n * 32 + 255) / 256, 256, 0, st>>>(ctx->d_Linv, ld, 0, n, reinterpret_cast<double*>(ctx->d_info) + 1);
+  SBO_LAUNCH_CHECK(ctx, "row_l1_max_kernel");
+  InfoRecord rec;
+  SBO_TRY(check_info(ctx, "sbo_set_observations", &rec));
+  ctx->linv_r1 = rec.r1_full;
   SBO_TRY(compute_alpha(ctx, n));
   SBO_TRY(refresh_planes(ctx, planes_done, ld));   // (rows the eager launch is reading were converted for it above)
   return SBO_OK;
@@ -923,7 +953,9 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
   double* S = ctx->d_small + (size_t)2 * kMaxAppend * ld;       // [kMaxAppend][kMaxAppend] -> L22
   double* X22 = S + (size_t)kMaxAppend * kMaxAppend;            // [kMaxAppend][kMaxAppend]
 
+  SBO_TRY(ensure_factor_attr(ctx));   // (an append can be the first factor call of a context)
   SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_info, 0, sizeof(int), st));
+  SBO_CUDA(ctx, cudaMemsetAsync(reinterpret_cast<double*>(ctx->d_info) + 2, 0, sizeof(double), st));
   {
     dim3 g((n + k + 127) / 128, k);
     append_cov_kernel<<<g, 128, 0, st>>>(ctx->d_xy, n, k, sf2, inv2l2, ctx->cfg.noise_var, K21, ld, S);
@@ -963,8 +995,18 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
     SBO_TRY(compute_alpha(ctx, n + k));
   }
   SBO_TRY(refresh_planes(ctx, n, n + k));
-  const int32_t verdict = check_info(ctx, "sbo_append_observations");   // synchronises the stream
-  if (verdict != SBO_OK) {   // not positive definite: the new rows were computed from garbage; put alpha back
+  row_l1_max_kernel<<<(k * 32 + 255) / 256, 256, 0, st>>>(ctx->d_Linv, ld, n, n + k, reinterpret_cast<double*>(ctx->d_info) + 2);
+  SBO_LAUNCH_CHECK(ctx, "row_l1_max_kernel");
+  InfoRecord rec;
+  const int32_t verdict = check_info(ctx, "sbo_append_observations", &rec);   // synchronises the stream
+  if (verdict == SBO_OK && rec.r1_new > ctx->linv_r1) ctx->linv_r1 = rec.r1_new;
+  if (verdict != SBO_OK) {   // not positive definite: the new rows were computed from garbage
+    // rows [n, n + k) of L^-1 and their fp16 planes go back to zero (the invariant the posterior kernels rely on:
+    // L^-1 is zero beyond n), alpha back to the old observations'
+    const std::string why = ctx->err;
+    SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_Linv + (size_t)n * ld, 0, sizeof(double) * (size_t)k * ld, st));
+    SBO_TRY(refresh_planes(ctx, n, n + k));
+    ctx->err = why;
     SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_alpha + n, 0, sizeof(double) * (size_t)k, st));
     if (ctx->d_alpha_f32) SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_alpha_f32 + n, 0, sizeof(float) * (size_t)k, st));
     if (n > 0) SBO_TRY(compute_alpha(ctx, n));

@@ -281,10 +281,9 @@ int32_t launch_posterior_f64(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) 
   p.inv2l2 = 1.0 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale);
   p.prior_mean = ctx->cfg.prior_mean;
   if (p.ld % 2 != 0) return fail(ctx, SBO_ERR_STATE, "posterior_f64: odd leading dimension of L^-1");
-  static bool attr_set = false;
-  if (!attr_set) {
+  if (!ctx->attr_f64) {   // the attribute is per device: kept per context, not in a process-wide flag
     SBO_CUDA(ctx, cudaFuncSetAttribute(posterior_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F64Smem)));
-    attr_set = true;
+    ctx->attr_f64 = true;
   }
   const long long ntiles = (long long)((p.W + PC - 1) / PC) * ((p.rows_local + PR - 1) / PR);
   const unsigned grid = (unsigned)std::min<long long>(ntiles, ctx->sm_count);

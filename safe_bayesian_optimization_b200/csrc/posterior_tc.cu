@@ -81,7 +81,7 @@ struct __align__(16) TcShared {
   float4 obs_y[kGenWarps][8];      //   y factor of K* (incl. sigma_f^2 and the A scale)
   float4 obs_a[kGenWarps][8];      //   alpha
   float mu_part[2][3][BM];         // partial mu of k-quarters 1..3, double-buffered by tile parity
-  uint32_t cmask[kThreadsTc / 32][kMaskWords];  // per warp: bit c set = chunk c is contracted for the current tile (pair)
+  uint32_t cmask[kThreadsTc / 32][2 * kMaskWords];  // per warp: [0, 16) bit c set = chunk c is contracted for the current tile (pair); [16, 32) = with all three split products
 };
 
 struct TcParams {
@@ -104,6 +104,8 @@ struct TcParams {
   const float4* bbox;      // [n_cap / 64] scaled bounding box (xmin, xmax, ymin, ymax) of every 64-observation chunk
   int skip;                // 1: chunks whose K* entries are all below 2^-skip_bits sigma_f^2 for a tile are not contracted
   float skip_bits;         // tc_skip_bits(): chosen so that everything skipped moves sigma^2 by < 1e-7 sigma_f^2
+  float ring_bits;         // graded split depth: visits whose K* entries are all < 2^-ring_bits sigma_f^2 issue hi.hi only (>= skip_bits: none)
+  int strip_tiles;         // strip-major tile order: tiles per strip (even; 0 = raster), see TileMap
   int pi_lo, pi_hi;        // pair kernel: row-block pairs [pi_lo, pi_hi) of this launch
   int rs_mode;             // pair kernel: 0 whole job; 1 partial (store the running row sums in rs_part, no sigma^2 / mu); 2 resume from rs_part
   float2* rs_part;         // [m_local] double-word fp32 running sums of a partial launch
@@ -285,24 +287,51 @@ __device__ __forceinline__ float box_dist2(const float4 b, float xlo, float xhi,
   return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
 }
 
+// Tile order.  Raster order makes the co-resident CTA pairs (74 of them = 148 tiles) cover a one-row strip across the WHOLE
+// width of the grid: together they touch every observation chunk of the ~4 bands of observations near that row, for every
+// row block of L^-1 -- ~94 MB of fp16 planes per sweep at n = 16 384, more than the L2 holds once the pairs drift apart
+// (measured round 1: 50 % of the TMA bytes came from DRAM, 2.4 TB/s).  Strip-major order walks a strip of `strip` tiles
+// (a few length-scales wide) down all the rows of the shard before the next strip, so the co-resident pairs cover a compact
+// patch and share most of their chunks.  Needs an even number of tiles per row (a tile pair never straddles rows).
+struct TileMap {
+  int tiles_per_row, rows, strip;   // strip: tiles per strip (even) or 0 = raster
+  __device__ __forceinline__ void locate(long long tile, int& lrow, int& col0) const {
+    if (strip == 0) {
+      lrow = (int)(tile / tiles_per_row);
+      col0 = (int)(tile % tiles_per_row) * BM;
+    } else {
+      const long long per_strip = (long long)strip * rows;
+      const int nstrips = (tiles_per_row + strip - 1) / strip;
+      const int s = (int)min(tile / per_strip, (long long)(nstrips - 1));
+      const long long rem = tile - (long long)s * per_strip;
+      const int w = min(strip, tiles_per_row - s * strip);
+      lrow = (int)(rem / w);
+      col0 = (s * strip + (int)(rem % w)) * BM;
+    }
+  }
+};
+
 // __noinline__ on purpose: every role of both CTAs must derive bit-identical masks (they walk them in lock step
 // through the mbarrier pipelines), so there is exactly one compiled copy of this arithmetic.
 struct MaskGeom {  // by value: taking the address of the kernel parameter block would move it to local memory
   double x0, y0, rx, ry, xscale;
   const float4* bbox;
   int row0, skip;
-  float skip_bits;
+  float skip_bits, ring_bits;
+  TileMap tm;
 };
 
+// mask[0 .. 16): chunks that are contracted; mask[16 .. 32): those of them that need all three split products (the rest
+// -- every K* entry of the chunk below 2^-ring_bits sigma_f^2 for both tiles -- run hi.hi only: graded split depth).
 template <int CG>
-__device__ __noinline__ void build_chunk_mask(uint32_t* mask, const MaskGeom p, long long gt, long long ntiles,
-                                              int tiles_per_row, int nchunks) {
+__device__ __noinline__ void build_chunk_mask(uint32_t* mask, const MaskGeom p, long long gt, long long ntiles, int nchunks) {
   const int lane = threadIdx.x & 31;
   float xlo[CG], xhi[CG], yy[CG];
 #pragma unroll
   for (int t = 0; t < CG; ++t) {
     const long long tile = min(gt * CG + t, ntiles - 1);
-    const int lrow = (int)(tile / tiles_per_row), col0 = (int)(tile % tiles_per_row) * BM;
+    int lrow, col0;
+    p.tm.locate(tile, lrow, col0);
     const double xs = cell_coord(p.x0, p.rx, col0) * p.xscale, ys = cell_coord(p.y0, p.ry, p.row0 + lrow) * p.xscale;
     const double w = (double)(BM - 1) * p.rx * p.xscale;
     xlo[t] = (float)fmin(xs, xs + w) - 1e-3f;   // margin: the box test runs in fp32
@@ -313,21 +342,29 @@ __device__ __noinline__ void build_chunk_mask(uint32_t* mask, const MaskGeom p, 
 #pragma unroll 1
   for (int w = 0; w < kMaskWords; ++w) {
     const int c = w * 32 + lane;
-    bool on = false;
+    bool on = false, full = false;
     if (c < nchunks) {
-      on = true;
+      on = full = true;
       if (p.skip) {
         const float4 b = p.bbox[c];
-        on = false;
+        on = full = false;
 #pragma unroll
-        for (int t = 0; t < CG; ++t) on = on || box_dist2(b, xlo[t], xhi[t], yy[t]) <= p.skip_bits + 0.5f;
+        for (int t = 0; t < CG; ++t) {
+          const float d2 = box_dist2(b, xlo[t], xhi[t], yy[t]);
+          on = on || d2 <= p.skip_bits + 0.5f;
+          full = full || d2 <= p.ring_bits + 0.5f;
+        }
       }
     }
-    const uint32_t bits = __ballot_sync(0xffffffffu, on);
-    if (lane == 0) mask[w] = bits;
+    const uint32_t bits = __ballot_sync(0xffffffffu, on), fbits = __ballot_sync(0xffffffffu, full);
+    if (lane == 0) {
+      mask[w] = bits;
+      mask[kMaskWords + w] = fbits;
+    }
   }
   __syncwarp();
 }
+__device__ __forceinline__ bool chunk_full(const uint32_t* mask, int kc) { return (mask[kMaskWords + (kc >> 5)] >> (kc & 31)) & 1u; }
 
 // Walk over the set bits of a chunk mask in ascending order: one shared-memory load per 32 chunks, a pop
 // (bits &= bits - 1) per chunk -- this sits on the per-chunk path of every role.  kSkip = false (the host found
@@ -551,7 +588,8 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   const int jb_lo = p.j_lo / BN, jb_hi = (p.j_hi + BN - 1) / BN;
   const int nchunks = n_pad / BK;
   uint32_t* cmask = sh->cmask[warp];
-  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip, p.skip_bits};
+  const TileMap tmap_tiles = {tiles_per_row, p.rows_local, 0};   // raster order (incremental steps: every tile walks the same few row blocks)
+  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip, p.skip_bits, p.skip_bits, tmap_tiles};
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -575,7 +613,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     // =============================== TMA producer (converged warp, one elected lane issues) ===============================
     uint32_t it = 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
-      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, nchunks);
       for (int jb = jb_lo; jb < jb_hi; ++jb) {
         const int nch = chunks_of(jb, n_pad);
         bool fresh = true;
@@ -615,7 +653,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     long long ck_full = 0, ck_issue = 0, ck_acc = 0;
     const bool clk_on = SBO_TC_CLOCKS && p.dbg_clk != nullptr && blockIdx.x == 0;
     for (long long gt = group; rank == 0 && gt < ngtiles; gt += ngroups) {
-      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, nchunks);
       for (int jb = jb_lo; jb < jb_hi; ++jb) {
         const int nch = chunks_of(jb, n_pad);
         ChunkIter<kSkip> ci;
@@ -672,7 +710,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     uint32_t acc_it = 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
       const long long tile = gt * CG + rank;
-      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, nchunks);
       float rs_hi = 0.f, rs_lo = 0.f;  // sum of squares of this cell's row of V (scaled), double-word fp32
       ChunkIter<kSkip> ci0;
       ci0.reset(cmask);
@@ -768,7 +806,7 @@ posterior_tc_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       const float oxh = (float)ox0, oxl = (float)(ox0 - (double)oxh);
       const float oyh = (float)oy0, oyl = (float)(oy0 - (double)oyh);
       float mu_hi = 0.f, mu_lo = 0.f;  // fp32 inside a 32-observation half-chunk, double-word fp32 across chunks
-      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, nchunks);
       TileWalk<kSkip> w, scout;
       w.start(cmask, jb_lo, jb_hi, n_pad);
       scout = w;
@@ -906,6 +944,27 @@ void tc_plane_shifts(const sbo_config& cfg, int* shift_a, int* shift_b) {
   *shift_b = std::max(-60, std::min(60, (int)std::floor(15.0 - std::log2(bmax))));
 }
 
+// (Re-)encode the tensor map of the fp16 planes: the TMA box is this CTA's share of a 256-row B tile.
+int32_t tc_set_cta_group(sbo_ctx* ctx, int cg) {
+  if (!g_encode_tiled) return fail(ctx, SBO_ERR_STATE, "tc_set_cta_group: tcgen05 path not initialised");
+  CUtensorMap* map = ctx->tmap_planes ? static_cast<CUtensorMap*>(ctx->tmap_planes) : new CUtensorMap;
+  const cuuint64_t nc = (cuuint64_t)ctx->n_cap;
+  const cuuint64_t gdim[2] = {nc, 2 * nc};                 // inner: k (columns of L^-1), outer: hi rows then lo rows
+  const cuuint64_t gstride[1] = {nc * sizeof(__half)};     // bytes between rows
+  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)(BN / cg)};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = g_encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, ctx->d_planes, gdim, gstride, box, estr,
+                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    if (!ctx->tmap_planes) delete map;
+    return fail(ctx, SBO_ERR_CUDA, "tc_set_cta_group: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+  }
+  ctx->tmap_planes = map;
+  ctx->tc_cg = cg;
+  return SBO_OK;
+}
+
 int32_t tc_init(sbo_ctx* ctx) {
   ctx->tc_ok = false;
   if (!(ctx->cfg.noise_var > 0.0))
@@ -915,26 +974,11 @@ int32_t tc_init(sbo_ctx* ctx) {
   cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
   if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn)
     return fail(ctx, SBO_ERR_CUDA, "tc_init: cuTensorMapEncodeTiled not available from the driver");
-  int cg = 2;
-  if (const char* s = std::getenv("SBO_TC_CTA_GROUP")) cg = (std::atoi(s) == 1) ? 1 : 2;
-  ctx->tc_cg = cg;
-  ctx->tc_skip = true;   // SBO_TC_SKIP=0: contract every chunk (dense), for A/B measurements
-  if (const char* s = std::getenv("SBO_TC_SKIP")) ctx->tc_skip = std::atoi(s) != 0;
+  ctx->tc_skip = true;   // sbo_set_option(SBO_OPT_TC_SKIP, 0): contract every chunk (dense), for A/B measurements
   tc_plane_shifts(ctx->cfg, &ctx->shift_a, &ctx->shift_b);
   g_encode_tiled = reinterpret_cast<EncodeTiledFn>(fn);
-  CUtensorMap* map = new CUtensorMap;
-  const cuuint64_t nc = (cuuint64_t)ctx->n_cap;
-  const cuuint64_t gdim[2] = {nc, 2 * nc};                 // inner: k (columns of L^-1), outer: hi rows then lo rows
-  const cuuint64_t gstride[1] = {nc * sizeof(__half)};     // bytes between rows
-  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)(BN / cg)};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = reinterpret_cast<EncodeTiledFn>(fn)(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, ctx->d_planes, gdim, gstride,
-                                                         box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                                                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    delete map;
-    return fail(ctx, SBO_ERR_CUDA, "tc_init: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
-  }
+  SBO_TRY(tc_set_cta_group(ctx, 2));
+  // (per device: sbo_create has made ctx->device current)
   e = cudaFuncSetAttribute(posterior_tc_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<1>());
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(posterior_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_smem_bytes<1>());
@@ -952,10 +996,10 @@ int32_t tc_init(sbo_ctx* ctx) {
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(posterior_tc_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc_pair_smem_bytes());
   if (e != cudaSuccess) {
-    delete map;
+    delete static_cast<CUtensorMap*>(ctx->tmap_planes);
+    ctx->tmap_planes = nullptr;
     return cuda_fail(ctx, e, "tc_init: cudaFuncSetAttribute(max dynamic smem)");
   }
-  ctx->tmap_planes = map;
   ctx->tc_ok = true;
   return SBO_OK;
 }
@@ -995,58 +1039,60 @@ int32_t tc_pack_observations(sbo_ctx* ctx, cudaStream_t stream) {
   return SBO_OK;
 }
 
-// Is there enough to skip on this grid with these observations to pay for the mask walk (~3 % at C2, where
-// almost every chunk matters everywhere)?  Host-side estimate on a sample of cell tiles: the fraction of
-// (row block, chunk) visits that the box test keeps, with the same boxes and cut-off as the kernel.  Cached
-// until the grid or the observations change.
-// Cut-off of the block-sparse walk, in bits: a chunk is skipped for a tile when every K* entry in it is < 2^-bits sigma_f^2.
-// Skipped entries move a component of v = L^-1 k* by at most 2^-bits sigma_f^2 ||row of L^-1||_1 <= 2^-bits sigma_f^2 sqrt(n / noise_var)
-// (||L^-1||_2 <= noise_var^-1/2), hence sigma^2 = sigma_f^2 - |v|^2 by at most 2 sqrt(n) |v| max|dv| <= 2 n sqrt(sigma_f^2 / noise_var) 2^-bits
-// relative to sigma_f^2.  bits is the smallest integer that keeps this under 1e-7 (1 % of the fp32 tolerance), never below 36.
-float tc_skip_bits(const sbo_ctx* ctx) {
-  const double sf2 = ctx->cfg.sigma_f * ctx->cfg.sigma_f;
-  const double bound = 2.0 * std::max(ctx->n, 1) * std::sqrt(sf2 / std::max(ctx->cfg.noise_var, 1e-300)) * 1e7;
-  return (float)std::min(60.0, std::max(36.0, std::ceil(std::log2(bound))));
+// Cut-offs of the block-sparse walk (plan.cu has the derivation).  The measured row 1-norm of L^-1 replaces its a-priori
+// bound where the walk is always planned after the fit: beyond kEagerMaxObs observations (below that the eager first
+// pairs start inside the fit, before the norm exists, and must walk the same masks as the launch that resumes them).
+constexpr int kEagerMaxObs = 2048;
+static double tc_r1(const sbo_ctx* ctx) { return ctx->n > kEagerMaxObs ? ctx->linv_r1 : 0.0; }
+float tc_skip_bits(const sbo_ctx* ctx) { return (float)tc_skip_bits_of(ctx->cfg, ctx->n, tc_r1(ctx)); }
+float tc_ring_bits(const sbo_ctx* ctx) {
+  if (!ctx->opt.tc_graded) return tc_skip_bits(ctx);
+  return (float)tc_ring_bits_of(ctx->cfg, ctx->n, tc_r1(ctx), ctx->shift_a);
 }
 
+// Is there enough to skip on this grid with these observations to pay for the mask walk (~3 % at C2, where
+// almost every chunk matters everywhere)?  Host-side estimate on a sample of cell tiles: the share of the dense walk's
+// MMA passes that the box test keeps, with the same boxes and cut-offs as the kernel.  Cached until the grid or the
+// observations change.
 bool tc_plan_skip(sbo_ctx* ctx) {
   if (!ctx->tc_skip) return false;
   if (ctx->tc_skip_plan >= 0) return ctx->tc_skip_plan != 0;
   const int n = ctx->n, nchunks = (n + BK - 1) / BK;
   ctx->tc_skip_plan = 0;
   ctx->tc_kept_frac = 1.0;
+  ctx->tc_pass_frac = 1.0;
   if (nchunks < 8 || (int)ctx->h_xy_sorted.size() < 2 * n) return false;
-  const double xs = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
-  std::vector<double> box(4 * (size_t)nchunks);
-  for (int c = 0; c < nchunks; ++c) {
-    double x0 = 1e300, x1 = -1e300, y0 = 1e300, y1 = -1e300;
-    for (int k = c * BK; k < std::min(n, (c + 1) * BK); ++k) {
-      const double x = ctx->h_xy_sorted[2 * (size_t)k] * xs, y = ctx->h_xy_sorted[2 * (size_t)k + 1] * xs;
-      x0 = std::min(x0, x); x1 = std::max(x1, x); y0 = std::min(y0, y); y1 = std::max(y1, y);
-    }
-    box[4 * c] = x0; box[4 * c + 1] = x1; box[4 * c + 2] = y0; box[4 * c + 3] = y1;
-  }
+  const double xs = tc_xscale(ctx->cfg);
+  std::vector<double> box;
+  chunk_boxes(ctx->h_xy_sorted.data(), n, xs, box);
   const int rows = ctx->row1 - ctx->row0, tiles_per_row = (ctx->W + BM - 1) / BM;
-  const int nblocks = (n + BN - 1) / BN;
-  const double bits = tc_skip_bits(ctx);
+  const double bits = tc_skip_bits(ctx), ring = tc_ring_bits(ctx);
   const int sr = std::min(rows, 24), sc = std::min(tiles_per_row, 24);
-  double kept = 0.0, total = 0.0;
+  double kept = 0.0, total = 0.0, passes = 0.0;
   for (int a = 0; a < sr; ++a)
     for (int b = 0; b < sc; ++b) {
       const int row = ctx->row0 + (int)((long long)a * rows / sr), col0 = (int)((long long)b * tiles_per_row / sc) * BM;
       const double tx0 = (ctx->x0 + col0 * ctx->rx) * xs, tx1 = tx0 + (BM - 1) * ctx->rx * xs;
-      const double xlo = std::min(tx0, tx1), xhi = std::max(tx0, tx1), y = (ctx->y0 + row * ctx->ry) * xs;
-      for (int c = 0; c < nchunks; ++c) {
-        const double wgt = nblocks - c / (BN / BK);  // row blocks that walk chunk c
-        const double dx = std::max(std::max(box[4 * c] - xhi, xlo - box[4 * c + 1]), 0.0);
-        const double dy = std::max(std::max(box[4 * c + 2] - y, y - box[4 * c + 3]), 0.0);
-        total += wgt;
-        if (dx * dx + dy * dy <= bits + 0.5) kept += wgt;
-      }
+      double t, k, p;
+      tile_visit_cost(box, n, std::min(tx0, tx1), std::max(tx0, tx1), (ctx->y0 + row * ctx->ry) * xs, bits, ring, &t, &k, &p);
+      total += t; kept += k; passes += p;
     }
   ctx->tc_kept_frac = total > 0.0 ? kept / total : 1.0;
+  ctx->tc_pass_frac = total > 0.0 ? passes / (3.0 * total) : 1.0;
   ctx->tc_skip_plan = (total > 0.0 && kept < 0.85 * total) ? 1 : 0;
   return ctx->tc_skip_plan != 0;
+}
+
+int32_t tc_plan_detail(sbo_ctx* ctx, double out[6]) {
+  const bool skip = ctx->tc_ok && ctx->grid_set ? tc_plan_skip(ctx) : false;
+  out[0] = tc_skip_bits(ctx);
+  out[1] = skip ? tc_ring_bits(ctx) : out[0];
+  out[2] = skip ? ctx->tc_kept_frac : 1.0;
+  out[3] = skip ? ctx->tc_pass_frac : 1.0;
+  out[4] = tc_r1(ctx);
+  const int tpr = (ctx->W + BM - 1) / BM, strip = 2 * ctx->opt.tc_strip;
+  out[5] = (strip > 0 && tpr % 2 == 0 && tpr > strip) ? strip : 0;
+  return SBO_OK;
 }
 
 static void tc_fill_params(sbo_ctx* ctx, TcParams& p, int j_lo, int j_hi, bool accumulate) {
@@ -1075,6 +1121,11 @@ static void tc_fill_params(sbo_ctx* ctx, TcParams& p, int j_lo, int j_hi, bool a
   p.bbox = reinterpret_cast<const float4*>(ctx->d_chunk_bbox);
   p.skip = tc_plan_skip(ctx) ? 1 : 0;
   p.skip_bits = tc_skip_bits(ctx);
+  p.ring_bits = p.skip ? tc_ring_bits(ctx) : p.skip_bits;
+  // strip-major tile order (pair kernel): needs whole tile pairs per row and per strip
+  const int tpr = (ctx->W + BM - 1) / BM;
+  const int strip = 2 * ctx->opt.tc_strip;
+  p.strip_tiles = (strip > 0 && tpr % 2 == 0 && tpr > strip) ? strip : 0;
   p.pi_lo = 0;
   p.pi_hi = ((ctx->n + BN - 1) / BN + 1) / 2;
   p.rs_mode = 0;
@@ -1111,12 +1162,11 @@ static cudaError_t tc_launch_pair(sbo_ctx* ctx, const TcParams& p, cudaStream_t 
 // same sums in the same order, so sigma^2 and mu are bit-identical to the one-launch result).  Anything else that
 // touches the grid or the observations first waits for the side stream and drops the partial result.
 int tc_eager_pairs(sbo_ctx* ctx) {
-  static const bool off = std::getenv("SBO_TC_EAGER") && std::atoi(std::getenv("SBO_TC_EAGER")) == 0;
-  static const bool pair_off = std::getenv("SBO_TC_PAIR") && std::atoi(std::getenv("SBO_TC_PAIR")) == 0;
+  const bool off = !ctx->opt.tc_eager, pair_off = !ctx->opt.tc_pair;
   if (off || pair_off || !ctx->tc_ok || ctx->tc_cg != 2 || ctx->cfg.precision != SBO_FP32 || !ctx->grid_set || ctx->m_local == 0)
     return 0;
   if (ctx->cfg.kernel != SBO_KERNEL_AUTO && ctx->cfg.kernel != SBO_KERNEL_TCGEN05) return 0;
-  if (ctx->n < 2 * BN || ctx->n > 4096 || g_dbg_v) return 0;   // beyond ~4k observations the factorisation is a few % of the step
+  if (ctx->n < 2 * BN || ctx->n > kEagerMaxObs || g_dbg_v) return 0;   // beyond that the factorisation is a few % of the step, and the walk is planned with the measured norm of L^-1
   const long long ntiles = (long long)(ctx->row1 - ctx->row0) * ((ctx->W + BM - 1) / BM);
   if (ntiles < 2 * ctx->sm_count) return 0;                    // a grid that small is latency, not throughput
   // How many pairs: as many as finish about when the factorisation does.  While they run the factor kernels share the SMs
@@ -1195,8 +1245,7 @@ static void tc_inc_shape(const sbo_ctx* ctx, int k, int* lq, int* nslabs, long l
 }
 
 bool tc_inc_applicable(sbo_ctx* ctx, int k) {
-  const char* env = std::getenv("SBO_TC_INC");
-  const bool off = env && std::atoi(env) == 0;
+  const bool off = !ctx->opt.tc_inc;
   if (off || !ctx->tc_ok || ctx->tc_cg != 2 || ctx->cfg.precision != SBO_FP32 || !g_encode_tiled) return false;
   if (k < 1 || k > 16 || ctx->m_local == 0 || ctx->n < 1) return false;
   int lq, nslabs;
@@ -1309,11 +1358,16 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
     p.rs_part = reinterpret_cast<float2*>(ctx->d_rs_part);
   }
   p.dbg = 0;
-  if (SBO_TC_CLOCKS)
-    if (const char* s = std::getenv("SBO_TC_DBG")) p.dbg = std::atoi(s);
+#if SBO_TC_CLOCKS
+  if (const char* s = std::getenv("SBO_TC_DBG")) p.dbg = std::atoi(s);
+#endif
   p.dbg_clk = nullptr;
   static long long* d_clk = nullptr;
-  const bool want_clk = SBO_TC_CLOCKS && std::getenv("SBO_TC_CLK") != nullptr;
+#if SBO_TC_CLOCKS
+  const bool want_clk = std::getenv("SBO_TC_CLK") != nullptr;
+#else
+  const bool want_clk = false;
+#endif
   if (want_clk) {
     if (!d_clk) cudaMalloc(&d_clk, 64 * sizeof(long long));
     cudaMemsetAsync(d_clk, 0, 64 * sizeof(long long), ctx->stream);
@@ -1343,9 +1397,9 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    // full refresh over at least two row blocks: the K*-stationary pair kernel (SBO_TC_PAIR=0: off)
+    // full refresh over at least two row blocks: the K*-stationary pair kernel (SBO_OPT_TC_PAIR = 0: off)
     bool pair = !p.accumulate && p.j_lo == 0 && p.j_hi == p.n && p.n > BN && p.dbg_v == nullptr;
-    if (const char* s = std::getenv("SBO_TC_PAIR")) pair = pair && std::atoi(s) != 0;
+    pair = pair && ctx->opt.tc_pair != 0;
     if (resume && !pair) return fail(ctx, SBO_ERR_STATE, "eager first pairs without the pair kernel");
     const cudaError_t e = pair     ? tc_launch_pair(ctx, p, ctx->stream, pairs)
                           : p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, true>, tmap, p)

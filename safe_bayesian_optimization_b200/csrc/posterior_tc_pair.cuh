@@ -38,7 +38,7 @@ struct __align__(16) TcPairShared {
   float4 obs_y[kGenWarps][8];
   float4 obs_a[kGenWarps][8];
   float mu_part[2][3][BM];
-  uint32_t cmask[kThreadsTc / 32][kMaskWords];  // per warp: bit c set = chunk c is contracted for the current tile pair
+  uint32_t cmask[kThreadsTc / 32][2 * kMaskWords];  // per warp: chunk masks of the current tile pair (contracted / all three products), see build_chunk_mask
 };
 
 constexpr size_t tc_pair_smem_bytes() {
@@ -94,7 +94,8 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   const int npairs = (nblocks + 1) / 2;
   const int nchunks = n_pad / BK;
   uint32_t* cmask = sh->cmask[warp];
-  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip, p.skip_bits};
+  const TileMap tmap_tiles = {tiles_per_row, p.rows_local, p.strip_tiles};
+  const MaskGeom geom = {p.x0, p.y0, p.rx, p.ry, p.xscale, p.bbox, p.row0, p.skip, p.skip_bits, p.ring_bits, tmap_tiles};
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 4; ++s) {
@@ -118,7 +119,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   if (warp == 0) {
     // =============================== TMA producer: B stages in consumption order ===============================
     uint32_t itb = 0;
-    auto load_b = [&](int jb, int kc, bool fresh) {
+    auto load_b = [&](int jb, int kc, bool fresh, bool full3) {
       const int s = itb % kPairStagesB;
       const uint32_t ph = (itb / kPairStagesB) & 1u;
       // diagonal block: rows < 64 c hold zeros, the tile starts below them.  An accumulator's first contracted chunk
@@ -128,15 +129,15 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       mbar_wait(&sh->empty_b[s], ph ^ 1u);
       const uint32_t bar = mapa(smem_u32(&sh->full_b[s]), 0);
       if (elect_one()) {
-        if (rank == 0) mbar_arrive_expect_tx(&sh->full_b[s], kPairBBytes * CG);
+        if (rank == 0) mbar_arrive_expect_tx(&sh->full_b[s], (full3 ? kPairBBytes : TcCfg<2>::kBBytes) * CG);
         tma_load_2d<CG>(&tmap, bar, b_hi(s), kc * BK, row);
-        tma_load_2d<CG>(&tmap, bar, b_lo(s), kc * BK, p.n_cap + row);
+        if (full3) tma_load_2d<CG>(&tmap, bar, b_lo(s), kc * BK, p.n_cap + row);   // (hi.hi only: the lo plane is not read)
       }
       __syncwarp();
       ++itb;
     };
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
-      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, nchunks);
       for (int pi = p.pi_lo; pi < p.pi_hi; ++pi) {
         const int jb0 = 2 * pi;
         const bool has1 = jb0 + 1 < nblocks;
@@ -145,8 +146,9 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         ChunkIter<kSkip> ci;
         ci.reset(cmask);
         for (int kc = ci.next(); kc < nchl; kc = ci.next()) {
-          if (kc < nch0) { load_b(jb0, kc, fresh0); fresh0 = false; }
-          if (has1) { load_b(jb0 + 1, kc, fresh1); fresh1 = false; }
+          const bool full3 = !kSkip || chunk_full(cmask, kc);
+          if (kc < nch0) { load_b(jb0, kc, fresh0, full3); fresh0 = false; }
+          if (has1) { load_b(jb0 + 1, kc, fresh1, full3); fresh1 = false; }
         }
       }
     }
@@ -154,7 +156,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     // =============================== MMA issuer (leader CTA; converged warp, one elected lane issues) ===============================
     uint32_t ita = 0, itb = 0, use0 = 0, use1 = 0;
     for (long long gt = group; rank == 0 && gt < ngtiles; gt += ngroups) {
-      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, nchunks);
       for (int pi = p.pi_lo; pi < p.pi_hi; ++pi) {
         const int jb0 = 2 * pi;
         const bool has1 = jb0 + 1 < nblocks;
@@ -165,6 +167,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         bool fresh0 = true, fresh1 = true;
         for (int kn; kc < nchl; kc = kn, ++ita) {
           kn = ci.next();  // the next contracted chunk: tells whether this visit is an accumulator's last
+          const bool full3 = !kSkip || chunk_full(cmask, kc);   // graded split depth: far chunks run hi.hi only
           const int sa = ita % kPairStagesA;
           mbar_wait(&sh->full_a[sa], (ita / kPairStagesA) & 1u);  // generators stored their planes
           tc_fence_after();
@@ -190,9 +193,13 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
 #pragma unroll
               for (int ks = 0; ks < BK / UK; ++ks) {
                 const uint64_t adv = (uint64_t)((ks * UK * 2) >> 4);
-                umma_f16<CG>(d_col, dal + adv, dbh + adv, idesc, (fresh && ks == 0) ? 0u : 1u);
-                umma_f16<CG>(d_col, dah + adv, dbl + adv, idesc, 1u);
-                umma_f16<CG>(d_col, dah + adv, dbh + adv, idesc, 1u);
+                if (full3) {
+                  umma_f16<CG>(d_col, dal + adv, dbh + adv, idesc, (fresh && ks == 0) ? 0u : 1u);
+                  umma_f16<CG>(d_col, dah + adv, dbl + adv, idesc, 1u);
+                  umma_f16<CG>(d_col, dah + adv, dbh + adv, idesc, 1u);
+                } else {
+                  umma_f16<CG>(d_col, dah + adv, dbh + adv, idesc, (fresh && ks == 0) ? 0u : 1u);
+                }
               }
               umma_commit<CG>(&sh->empty_b[sb]);
               if (half == 1 || !has1) umma_commit<CG>(&sh->empty_a[sa]);  // last use: K* stage reusable once these MMAs have read it
@@ -212,10 +219,12 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     uint32_t use0 = 0, use1 = 0;
     for (long long gt = group; gt < ngtiles; gt += ngroups) {
       const long long tile = gt * CG + rank;
-      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, nchunks);
       float rs_hi = 0.f, rs_lo = 0.f;  // sum of squares of this cell's row of V (scaled), double-word fp32
       const long long e_tile = min(tile, ntiles - 1);
-      const int e_lrow = (int)(e_tile / tiles_per_row), e_col = (int)(e_tile % tiles_per_row) * BM + r;
+      int e_lrow, e_col0;
+      tmap_tiles.locate(e_tile, e_lrow, e_col0);
+      const int e_col = e_col0 + r;
       const bool e_live = tile < ntiles && e_col < p.W;
       const long long e_lc = (long long)e_lrow * p.W + e_col;
       if (p.rs_mode == 2 && e_live) {  // resume: pairs < pi_lo were contracted by an earlier launch (same sums, same order)
@@ -243,6 +252,11 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             uint32_t v[32];
             tmem_ld32(taddr + c * 32, v);
             tmem_ld_wait();
+            if (jc + 32 > p.n) {  // the group that holds row n - 1 (warp-uniform): rows >= n are zero by invariant, masked all the same
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (jc + i >= p.n) v[i] = 0u;
+            }
             // same arithmetic as posterior_tc_kernel's epilogue: exact squares, four 8-term fp32 partial sums, 2Sum
             float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
@@ -288,12 +302,13 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
     for (long long gt = group; gt < ngtiles; gt += ngroups, tile_par ^= 1u) {
       const long long tile = min(gt * CG + (long long)rank, ntiles - 1);  // an odd last tile: the peer recomputes it, no store
       const bool live = gt * CG + rank < ntiles;
-      const int lrow = (int)(tile / tiles_per_row), col0 = (int)(tile % tiles_per_row) * BM;
+      int lrow, col0;
+      tmap_tiles.locate(tile, lrow, col0);
       const double ox0 = cell_coord(p.x0, p.rx, col0) * p.xscale, oy0 = cell_coord(p.y0, p.ry, p.row0 + lrow) * p.xscale;
       const float oxh = (float)ox0, oxl = (float)(ox0 - (double)oxh);
       const float oyh = (float)oy0, oyl = (float)(oy0 - (double)oyh);
       float mu_hi = 0.f, mu_lo = 0.f;
-      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, tiles_per_row, nchunks);
+      if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, nchunks);
       PairWalk<kSkip> w, scout;
       w.start(cmask, nblocks, n_pad, p.pi_lo, p.pi_hi);
       scout = w;
@@ -310,6 +325,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         if (kn < 0) kn = grp == 0 ? first0 : first1;
         if ((vi & 1u) != (uint32_t)grp) continue;
         const bool last = (w.pi == npairs - 1);  // the last pair walks every chunk: mu is summed there
+        const bool full3 = !kSkip || chunk_full(cmask, kc);
         const int s = ita % kPairStagesA;
         const uint32_t ph = (ita / kPairStagesA) & 1u;
         {
@@ -340,9 +356,11 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
           const uint32_t u0 = (uint32_t)(oh * 4 + half * 2);
           const uint32_t off0 = ((u0 ^ swz) << 4), off1 = (((u0 + 1u) ^ swz) << 4);
           *reinterpret_cast<uint4*>(pa_hi + off0) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-          *reinterpret_cast<uint4*>(pa_lo + off0) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
           *reinterpret_cast<uint4*>(pa_hi + off1) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-          *reinterpret_cast<uint4*>(pa_lo + off1) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+          if (full3) {   // (hi.hi only: the lo plane of this stage is not read)
+            *reinterpret_cast<uint4*>(pa_lo + off0) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+            *reinterpret_cast<uint4*>(pa_lo + off1) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+          }
         }
         if (last) {
           float m0, m1;

@@ -363,9 +363,8 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
     }
   } else {
     const long long tiles2d = (long long)((p.W + kT2 - 1) / kT2) * ((p.rows_local + kT2 - 1) / kT2);
-    const char* e2d = std::getenv("SBO_THIN_2D");
     const bool span_ok = kT2 * std::max(std::fabs(p.rx), std::fabs(p.ry)) <= 4.0 * ctx->cfg.length_scale;  // see the staging recurrence
-    if (kr == 1 && tiles2d >= ctx->sm_count && span_ok && !(e2d && std::atoi(e2d) == 0)) {   // enough 128 x 128 tiles for every SM
+    if (kr == 1 && tiles2d >= ctx->sm_count && span_ok && ctx->opt.thin_2d) {   // enough 128 x 128 tiles for every SM
       const size_t smem = (size_t)2 * kT2Chunk * kT2Ld * sizeof(double);
       // per device, so not cached in a process-wide flag (a process may hold contexts on several GPUs); a few microseconds
       const cudaError_t ea = cudaFuncSetAttribute(posterior_thin2d_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

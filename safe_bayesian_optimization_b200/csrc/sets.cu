@@ -48,18 +48,20 @@ struct Acc {
   Best wid{0.0, -1};
   long long safe = 0;
   long long clamped = 0;
+  long long low = 0;   // sigma^2 < low_thr (0.02 sigma_f^2): cells where fp32 mode cannot hold 1e-5 of sigma^2 itself
 };
 
 // One cell.  kStd: `s` is already a standard deviation (reference's std_);
 // otherwise it is a variance: clamp at 0, add the noise term, take the root.
 template <bool kStd>
 __device__ __forceinline__ uint32_t eval_cell(double mu, double s, double beta, double f_min, double noise_add,
-                                              long long idx, Acc& acc, double& q0, double& q1) {
+                                              double low_thr, long long idx, Acc& acc, double& q0, double& q1) {
   double sd;
   if (kStd) {
     sd = s;
   } else {
     double v = s;
+    if (v < low_thr) acc.low++;
     if (v < 0.0) {
       v = 0.0;
       acc.clamped++;
@@ -113,7 +115,7 @@ __device__ __forceinline__ void store_q(double* q, long long base, double v0, do
 template <typename T, bool kStd, bool kVec>
 __global__ void __launch_bounds__(kThreads)
 sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long long cell0, double beta, double f_min,
-            double noise_add, uint8_t* __restrict__ mask, double* __restrict__ q0out, double* __restrict__ q1out,
+            double noise_add, double low_thr, uint8_t* __restrict__ mask, double* __restrict__ q0out, double* __restrict__ q1out,
             SetsResult* __restrict__ partials, SetsResult* __restrict__ result, unsigned int* __restrict__ ticket) {
   Acc acc;
   const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
@@ -140,7 +142,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
           uint32_t bytes = 0;
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            bytes |= eval_cell<kStd>(qm[u].get(e), qs[u].get(e), beta, f_min, noise_add, cell0 + base + e, acc, a0[e],
+            bytes |= eval_cell<kStd>(qm[u].get(e), qs[u].get(e), beta, f_min, noise_add, low_thr, cell0 + base + e, acc, a0[e],
                                      a1[e])
                      << (8 * e);
           }
@@ -155,7 +157,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
     if (tid < m - tail0) {
       const long long c = tail0 + tid;
       double a0, a1;
-      const uint32_t b = eval_cell<kStd>((double)mu[c], (double)s[c], beta, f_min, noise_add, cell0 + c, acc, a0, a1);
+      const uint32_t b = eval_cell<kStd>((double)mu[c], (double)s[c], beta, f_min, noise_add, low_thr, cell0 + c, acc, a0, a1);
       mask[c] = (uint8_t)b;
       if (q0out) q0out[c] = a0;
       if (q1out) q1out[c] = a1;
@@ -163,7 +165,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
   } else {
     for (long long c = tid; c < m; c += nthreads) {
       double a0, a1;
-      const uint32_t b = eval_cell<kStd>((double)mu[c], (double)s[c], beta, f_min, noise_add, cell0 + c, acc, a0, a1);
+      const uint32_t b = eval_cell<kStd>((double)mu[c], (double)s[c], beta, f_min, noise_add, low_thr, cell0 + c, acc, a0, a1);
       mask[c] = (uint8_t)b;
       if (q0out) q0out[c] = a0;
       if (q1out) q1out[c] = a1;
@@ -178,11 +180,12 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
     merge(acc.wid, w.v, w.i);
     acc.safe += __shfl_down_sync(0xffffffffu, acc.safe, d);
     acc.clamped += __shfl_down_sync(0xffffffffu, acc.clamped, d);
+    acc.low += __shfl_down_sync(0xffffffffu, acc.low, d);
   }
   __shared__ SetsResult warp_res[kThreads / 32];
   __shared__ bool is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (lane == 0) warp_res[warp] = SetsResult{acc.ucb.v, acc.ucb.i, acc.wid.v, acc.wid.i, acc.safe, acc.clamped};
+  if (lane == 0) warp_res[warp] = SetsResult{acc.ucb.v, acc.ucb.i, acc.wid.v, acc.wid.i, acc.safe, acc.clamped, acc.low};
   __syncthreads();
   if (threadIdx.x == 0) {
     SetsResult r = warp_res[0];
@@ -192,6 +195,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
       if (better(o.width_val, o.width_idx, r.width_val, r.width_idx)) { r.width_val = o.width_val; r.width_idx = o.width_idx; }
       r.safe_count += o.safe_count;
       r.clamped += o.clamped;
+      r.low_sigma2 += o.low_sigma2;
     }
     partials[blockIdx.x] = r;
     __threadfence();
@@ -209,6 +213,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
     merge(tot.wid, o.width_val, o.width_idx);
     tot.safe += o.safe_count;
     tot.clamped += o.clamped;
+    tot.low += o.low_sigma2;
   }
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) {
@@ -217,9 +222,10 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
     merge(tot.wid, w.v, w.i);
     tot.safe += __shfl_down_sync(0xffffffffu, tot.safe, d);
     tot.clamped += __shfl_down_sync(0xffffffffu, tot.clamped, d);
+    tot.low += __shfl_down_sync(0xffffffffu, tot.low, d);
   }
   __syncthreads();  // warp_res reuse
-  if (lane == 0) warp_res[warp] = SetsResult{tot.ucb.v, tot.ucb.i, tot.wid.v, tot.wid.i, tot.safe, tot.clamped};
+  if (lane == 0) warp_res[warp] = SetsResult{tot.ucb.v, tot.ucb.i, tot.wid.v, tot.wid.i, tot.safe, tot.clamped, tot.low};
   __syncthreads();
   if (threadIdx.x == 0) {
     SetsResult r = warp_res[0];
@@ -229,6 +235,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
       if (better(o.width_val, o.width_idx, r.width_val, r.width_idx)) { r.width_val = o.width_val; r.width_idx = o.width_idx; }
       r.safe_count += o.safe_count;
       r.clamped += o.clamped;
+      r.low_sigma2 += o.low_sigma2;
     }
     *result = r;
     *ticket = 0;  // ready for the next launch
@@ -238,6 +245,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
 template <typename T, bool kStd>
 int32_t launch(sbo_ctx* ctx, const T* mu, const T* s, int64_t m, int64_t cell0, double beta, double f_min,
                double noise_add, uint8_t* mask, double* q0, double* q1) {
+  const double low_thr = kStd ? 0.0 : 0.02 * ctx->cfg.sigma_f * ctx->cfg.sigma_f;
   auto aligned = [](const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
   const bool vec = aligned(mu, 16) && aligned(s, 16) && aligned(mask, 4) && (!q0 || aligned(q0, 16)) &&
                    (!q1 || aligned(q1, 16));
@@ -248,10 +256,10 @@ int32_t launch(sbo_ctx* ctx, const T* mu, const T* s, int64_t m, int64_t cell0, 
   if (blocks < 1) blocks = 1;
   if (vec) {
     sets_kernel<T, kStd, true><<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(
-        mu, s, m, cell0, beta, f_min, noise_add, mask, q0, q1, ctx->d_partials, ctx->d_result, ctx->d_ticket);
+        mu, s, m, cell0, beta, f_min, noise_add, low_thr, mask, q0, q1, ctx->d_partials, ctx->d_result, ctx->d_ticket);
   } else {
     sets_kernel<T, kStd, false><<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(
-        mu, s, m, cell0, beta, f_min, noise_add, mask, q0, q1, ctx->d_partials, ctx->d_result, ctx->d_ticket);
+        mu, s, m, cell0, beta, f_min, noise_add, low_thr, mask, q0, q1, ctx->d_partials, ctx->d_result, ctx->d_ticket);
   }
   SBO_LAUNCH_CHECK(ctx, "sets_kernel");
   return SBO_OK;

@@ -36,12 +36,15 @@ class StepResult:
     ms_sets: float
     ms_comm: float
     ms_total: float
+    low_sigma2: int = 0      # cells with sigma^2 < 0.02 sigma_f^2
+    refreshed: int = 0       # an incremental step that the refresh policy turned into a full posterior
+    drift: float = -1.0      # result of this step's drift check (-1: none)
 
     @staticmethod
     def from_c(o: L.SboStepOut) -> "StepResult":
         return StepResult(o.n_cells, o.safe_count, (o.argmax_ucb.idx, o.argmax_ucb.value),
                           (o.argmax_width.idx, o.argmax_width.value), o.clamped_sigma2, o.n_obs, o.kernel_used,
-                          o.ms_posterior, o.ms_sets, o.ms_comm, o.ms_total)
+                          o.ms_posterior, o.ms_sets, o.ms_comm, o.ms_total, o.low_sigma2, o.refreshed, o.drift)
 
 
 def _dptr(a):
@@ -133,6 +136,15 @@ class SboContext:
 
     def synchronize(self):
         self._check(self.lib.sbo_synchronize(self._h))
+
+    def set_option(self, name: str, value: int):
+        """sbo_set_option by name (``_lib.OPTIONS``): the A/B and policy switches; nothing is read from the environment."""
+        self._check(self.lib.sbo_set_option(self._h, L.OPTIONS[name], int(value)))
+
+    def get_option(self, name: str) -> int:
+        v = C.c_int32(0)
+        self._check(self.lib.sbo_get_option(self._h, L.OPTIONS[name], C.byref(v)))
+        return int(v.value)
 
     def device_info(self):
         sm, ok = C.c_int32(), C.c_int32()
@@ -254,6 +266,12 @@ class SboContext:
         self._check(self.lib.sbo_tc_plan(self._h, C.byref(cg), C.byref(sk), C.byref(kf)))
         return cg.value, bool(sk.value), kf.value
 
+    def tc_plan_detail(self):
+        """dict: bits, ring_bits, kept_fraction, pass_fraction, linv_row_l1, strip_tiles (sbo_tc_plan_detail)."""
+        out = np.zeros(6)
+        self._check(self.lib.sbo_tc_plan_detail(self._h, _dptr(out)))
+        return dict(zip(("bits", "ring_bits", "kept_fraction", "pass_fraction", "linv_row_l1", "strip_tiles"), out.tolist()))
+
     def frontier_image(self):
         """(img H x W uint8 0/255, col_of_px int32[W], row_of_py int32[H]): the image of reference :444-456 built on the
         GPU with the reference's pixel map, and the pixel -> cell tables that replace its hash map (:468-475)."""
@@ -309,6 +327,24 @@ def shard_rows(H: int, rank: int, world: int):
     return r0, r0 + base + (1 if rank < rem else 0)
 
 
+def plan_row_bands(p, parts: int, max_rows: int = 0, precision=None, kernel="auto"):
+    """Cost-balanced row bands for problem ``p`` (anything with xy, x0, y0, rx, ry, W, H and the hyper-parameters) over
+    ``parts`` GPUs: (row_cuts list[parts + 1], cost_share list[parts]).  Host arithmetic (sbo_plan_row_bands)."""
+    lib = L.load()
+    cfg = L.SboConfig(p.sigma_f, p.length, p.noise_var, p.prior_mean, 0,
+                      {"fp32": L.SBO_FP32, "fp64": L.SBO_FP64}[precision or p.precision],
+                      {"auto": L.SBO_KERNEL_AUTO, "simt": L.SBO_KERNEL_SIMT, "tcgen05": L.SBO_KERNEL_TCGEN05}[kernel], 0,
+                      max(int(p.xy.shape[0]), 1), 0, 1)
+    xy = np.ascontiguousarray(p.xy, dtype=np.float64).reshape(-1, 2)
+    cuts = np.zeros(parts + 1, dtype=np.int32)
+    share = np.zeros(parts)
+    st = lib.sbo_plan_row_bands(C.byref(cfg), _dptr(xy), xy.shape[0], p.x0, p.y0, p.rx, p.ry, p.W, p.H, parts, int(max_rows),
+                                cuts.ctypes.data_as(C.POINTER(C.c_int32)), _dptr(share))
+    if st != L.SBO_OK:
+        raise L.SboError(st, "sbo_plan_row_bands")
+    return cuts.tolist(), share.tolist()
+
+
 def merge_results(parts):
     """Fold per-shard StepResults with the library's order (value desc, index asc)."""
     def better(a, b):
@@ -322,4 +358,5 @@ def merge_results(parts):
     return StepResult(sum(p.n_cells for p in parts), sum(p.safe_count for p in parts), ucb, wid,
                       sum(p.clamped_sigma2 for p in parts), parts[0].n_obs, parts[0].kernel_used,
                       max(p.ms_posterior for p in parts), max(p.ms_sets for p in parts),
-                      max(p.ms_comm for p in parts), max(p.ms_total for p in parts))
+                      max(p.ms_comm for p in parts), max(p.ms_total for p in parts),
+                      sum(p.low_sigma2 for p in parts), max(p.refreshed for p in parts), max(p.drift for p in parts))

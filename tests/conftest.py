@@ -29,7 +29,11 @@ def pkg():
     return p
 
 
-def make_ctx(pkg, p, precision=None, kernel="auto", max_obs=None, max_cells=None, **kw):
-    return pkg.SboContext(sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean,
-                          precision=precision or p.precision, kernel=kernel, max_obs=max_obs or max(p.n, 1),
-                          max_cells=max_cells or p.m, **kw)
+def make_ctx(pkg, p, precision=None, kernel="auto", max_obs=None, max_cells=None, options=None, **kw):
+    """A context for problem p; `options` = {name: value} applied with sbo_set_option (the A/B switches)."""
+    ctx = pkg.SboContext(sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean,
+                         precision=precision or p.precision, kernel=kernel, max_obs=max_obs or max(p.n, 1),
+                         max_cells=max_cells or p.m, **kw)
+    for name, value in (options or {}).items():
+        ctx.set_option(name, value)
+    return ctx

@@ -24,15 +24,16 @@ def test_library_exports_every_declared_symbol(pkg):
     lib = pkg.load()
     for name in header_symbols():
         assert hasattr(lib, name), name
-    assert lib.sbo_abi_version() == 1
+    assert lib.sbo_abi_version() == 2
 
 
 def test_struct_layout_matches_c(pkg):
     from safe_bayesian_optimization_b200 import _lib
     assert C.sizeof(_lib.SboConfig) == 4 * 8 + 6 * 4 + 8
     assert C.sizeof(_lib.SboArgmax) == 16
-    assert C.sizeof(_lib.SboStepOut) == 8 + 8 + 16 + 16 + 8 + 4 + 4 + 4 * 4
+    assert C.sizeof(_lib.SboStepOut) == 8 + 8 + 16 + 16 + 8 + 4 + 4 + 4 * 4 + 8 + 4 + 4
     assert _lib.SboStepOut.argmax_width.offset == 32 and _lib.SboStepOut.ms_posterior.offset == 64
+    assert _lib.SboStepOut.low_sigma2.offset == 80 and _lib.SboStepOut.drift.offset == 92
 
 
 def test_null_and_bad_arguments_are_rejected_without_a_gpu(pkg):
@@ -69,3 +70,23 @@ def test_merge_step_out(pkg):
     assert (out.argmax_ucb.idx, out.argmax_ucb.value) == (2, 1.0)      # tie on value -> lower index
     assert (out.argmax_width.idx, out.argmax_width.value) == (9, 0.4)
     assert out.safe_count == 14 and out.n_cells == 300
+
+
+def test_plan_row_bands_is_a_partition_and_balances_work(pkg):
+    """sbo_plan_row_bands is host arithmetic: a partition of the rows for every part count; on a domain much wider than
+    the kernel's reach (block-sparse walk) the bands carry equal estimated work, not equal rows."""
+    from safe_bayesian_optimization_b200 import synthetic as S
+    from safe_bayesian_optimization_b200.optimizer import plan_row_bands
+    p = S.make_problem("C4", n=4096, W=2048, H=2048)
+    for parts in (1, 2, 3, 8):
+        cuts, share = plan_row_bands(p, parts)
+        assert cuts[0] == 0 and cuts[-1] == p.H and all(b > a for a, b in zip(cuts, cuts[1:]))
+        assert abs(sum(share) - 1.0) < 1e-9 and max(share) - min(share) < 0.05
+    cuts8, _ = plan_row_bands(p, 8)
+    rows = [b - a for a, b in zip(cuts8, cuts8[1:])]
+    assert max(rows) > min(rows)                       # equal work is not equal rows here (edge bands see fewer chunks)
+    cap, _ = plan_row_bands(p, 8, max_rows=p.H // 8 + 8)
+    assert max(b - a for a, b in zip(cap, cap[1:])) <= p.H // 8 + 8 and cap[-1] == p.H
+    small = S.make_problem("C2", n=300, W=256, H=100)   # dense walk: equal rows
+    c2, _ = plan_row_bands(small, 4)
+    assert c2 == [0, 25, 50, 75, 100]

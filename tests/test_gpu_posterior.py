@@ -5,10 +5,13 @@ incremental (rank-k) step, row-band shards, and the committed golden fixtures.
 Tolerances (north_star: "mu and sigma^2 within 1e-5 relative error in fp32, tighter in fp64"):
   fp32:  |dmu| <= 1e-5 * max|mu_ref|      |dsigma^2| <= 1e-5 * sigma_f^2
   fp64:  |dmu| <= 1e-10 * max|mu_ref|     |dsigma^2| <= 1e-10 * sigma_f^2
-i.e. relative to the scale of each field; sigma^2 = sigma_f^2 - |v|^2 cancels, so an error relative to
-sigma^2 itself is below fp32 resolution where sigma^2 << sigma_f^2 (reported, not gated).  The mask must
-be identical outside the band |LCB_ref - f_min| <= dmu_tol + beta * ds2_tol / (2 sigma_ref); the argmax
-must agree in index or differ only between candidates whose values lie within the same band."""
+i.e. relative to the scale of each field.  sigma^2 = sigma_f^2 - |v|^2 cancels, so next to observations (sigma^2 down
+to ~0.008 sigma_f^2) an error relative to sigma^2 ITSELF cannot be 1e-5 in fp32: storing |v|^2 ~ 0.99 alone costs 6e-8
+= 7e-6 sigma^2.  SURVEY H1's metric |dsigma^2| / max(sigma^2_ref, 1e-3 sigma_f^2) is printed for every case and gated at
+the level the fp32 path achieves (H1_GATE; measured 2.4e-4 at C4: include/sbo.h SBO_FP32 states it), and the quantity the
+mask depends on is gated directly: |dLCB| <= 2e-5 max(1, max|mu|) in fp32.  The mask must be identical outside the band
+|LCB_ref - f_min| <= dmu_tol + beta * ds2_tol / (2 sigma_ref); the argmax must agree in index or differ only between
+candidates whose values lie within the same band."""
 import glob
 import os
 
@@ -20,6 +23,8 @@ from safe_bayesian_optimization_b200 import synthetic as S
 
 pytestmark = pytest.mark.gpu
 TOL = {"fp32": 1e-5, "fp64": 1e-10}
+H1_GATE = {"fp32": 5e-4, "fp64": 1e-8}      # SURVEY H1 metric of sigma^2 (relative to sigma^2 itself, floor 1e-3 sigma_f^2)
+LCB_GATE = {"fp32": 2e-5, "fp64": 1e-9}     # |dLCB| / max(1, max|mu|): what the safe mask sees
 GOLDEN = sorted(glob.glob(os.path.join(os.path.dirname(__file__), "golden", "*.npz")))
 
 
@@ -48,6 +53,12 @@ def check_step(p, ref, res, mask, mu, s2, precision, cell0=0, label=""):
     print(f"[{label} {precision}] n={p.n} m={mu.size} max|dmu|={emu:.3e} (tol {mu_tol:.1e}) max|ds2|={es2:.3e} "
           f"(tol {s2_tol:.1e}) plain-rel ds2={rel_plain:.2e} min s2={s2_ref.min():.3e} clamped={res.clamped_sigma2}")
     assert emu <= mu_tol and es2 <= s2_tol
+    h1 = (np.abs(s2 - s2_ref) / np.maximum(s2_ref, 1e-3 * p.sigma_f ** 2)).max()
+    lcb = mu - p.beta * np.sqrt(np.maximum(s2, 0.0))
+    elcb = np.abs(lcb - q0).max() / max(1.0, np.abs(ref["mu"]).max())
+    print(f"    H1 metric |ds2|/max(s2, 1e-3 sf2) = {h1:.2e} (gate {H1_GATE[precision]:.0e})   |dLCB|/max(1,|mu|) = {elcb:.2e} "
+          f"(gate {LCB_GATE[precision]:.0e})   low_sigma2 cells = {res.low_sigma2}")
+    assert h1 <= H1_GATE[precision] and elcb <= LCB_GATE[precision]
     band = mu_tol + p.beta * s2_tol / (2.0 * np.sqrt(np.maximum(s2_ref, 1e-12)))
     diff = mask != mref
     in_band = np.abs(q0 - p.f_min) <= band
@@ -57,11 +68,11 @@ def check_step(p, ref, res, mask, mu, s2, precision, cell0=0, label=""):
     return band
 
 
-def check_argmax(res, ref, band, mask):
+def check_argmax(res, ref, band, mask, f_min=None):
     for got, val in ((res.argmax_ucb, ref["q1"]), (res.argmax_width, ref["q1"] - ref["q0"])):
         safe = ref["mask"] == 255
-        if not safe.any():
-            assert got[0] == -1 or band[got[0]] > 0
+        if not safe.any():   # no safe cell in the reference: a reported one must be a mismatch inside the tolerance band
+            assert got[0] == -1 or (f_min is not None and abs(ref["q0"][got[0]] - f_min) <= band[got[0]])
             continue
         best = np.flatnonzero(safe & (val == val[safe].max()))[0]
         if got[0] != best:      # allowed only between candidates inside the band
@@ -89,7 +100,7 @@ def test_step_matches_oracle(pkg, oracle, coracle, cfg, n, W, H, precision, kern
         assert res.kernel_used == {"tcgen05": 2, "simt": 1, "auto": 4}[kernel] and res.n_obs == n and res.n_cells == p.m
         band = check_step(p, ref, res, mask, ctx.mu(), ctx.sigma2(), precision, label=kernel)
         assert res.safe_count == int((mask == 255).sum())
-        check_argmax(res, ref, band, mask)
+        check_argmax(res, ref, band, mask, p.f_min)
         assert np.array_equal(ctx.mask(), mask)
 
 
@@ -113,7 +124,7 @@ def test_incremental_step_equals_full(pkg, oracle, coracle, precision, kernel, n
             q = S.make_problem("C3", n=total, W=300, H=21); q.xy, q.y = p.xy[:n], p.y[:n]
             ref = reference(oracle, coracle, q)
             band = check_step(q, ref, res, mask, ctx.mu(), ctx.sigma2(), precision, label=f"incr+{k}")
-            check_argmax(res, ref, band, mask)
+            check_argmax(res, ref, band, mask, q.f_min)
 
 
 @pytest.mark.parametrize("precision,kernel", [("fp32", "tcgen05"), ("fp64", "simt"), ("fp64", "auto")])
@@ -184,15 +195,14 @@ def test_optimizer_core_end_to_end(pkg, oracle, coracle):
     core.ctx.close()
 
 
-def test_single_cta_variant_matches_pair(pkg, oracle, coracle, monkeypatch):
-    """SBO_TC_CTA_GROUP=1 runs the same kernel as one CTA per tile (cta_group::1); both forms must meet the
+def test_single_cta_variant_matches_pair(pkg, oracle, coracle):
+    """SBO_OPT_TC_CTA_GROUP = 1 runs the same kernel as one CTA per tile (cta_group::1); both forms must meet the
     oracle and agree with each other to rounding (the MMA order per accumulator is identical)."""
     p = S.make_problem("C2", n=700, W=384, H=9)
     ref = reference(oracle, coracle, p)
     out = {}
     for cg in ("1", "2"):
-        monkeypatch.setenv("SBO_TC_CTA_GROUP", cg)
-        with make_ctx(pkg, p, kernel="tcgen05") as ctx:
+        with make_ctx(pkg, p, kernel="tcgen05", options={"tc_cta_group": int(cg)}) as ctx:
             ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
             ctx.set_observations(p.xy, p.y)
             res, mask = ctx.step(p.beta, p.f_min)
@@ -202,17 +212,15 @@ def test_single_cta_variant_matches_pair(pkg, oracle, coracle, monkeypatch):
 
 
 @pytest.mark.parametrize("n,W,H", [(700, 384, 9), (1100, 256, 7), (2304, 640, 3), (512, 130, 4)])
-def test_pair_kernel_matches_row_block_kernel(pkg, oracle, coracle, monkeypatch, n, W, H):
+def test_pair_kernel_matches_row_block_kernel(pkg, oracle, coracle, n, W, H):
     """The dense full refresh runs the K*-stationary pair kernel (one K* generation per two row blocks of L^-1;
-    odd row-block counts end in a single).  SBO_TC_PAIR=0 runs the one-row-block kernel instead: both meet the
+    odd row-block counts end in a single).  SBO_OPT_TC_PAIR = 0 runs the one-row-block kernel instead: both meet the
     oracle, and sigma^2 agrees bit for bit (same MMAs per accumulator in the same order, same epilogue sums)."""
     p = S.make_problem("C2", n=n, W=W, H=H)
     ref = reference(oracle, coracle, p)
     out = {}
     for pair in ("0", "1"):
-        monkeypatch.setenv("SBO_TC_PAIR", pair)
-        monkeypatch.setenv("SBO_TC_SKIP", "0")
-        with make_ctx(pkg, p, kernel="tcgen05") as ctx:
+        with make_ctx(pkg, p, kernel="tcgen05", options={"tc_pair": int(pair), "tc_skip": 0}) as ctx:
             ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
             ctx.set_observations(p.xy, p.y)
             res, mask = ctx.step(p.beta, p.f_min)
@@ -235,24 +243,23 @@ def test_long_rank1_chain_stays_in_tolerance(pkg, oracle, coracle, precision):
         for t in range(steps):
             ctx.append_observations(p.xy[n0 + t:n0 + t + 1], p.y[n0 + t:n0 + t + 1])
             res, mask = ctx.step(p.beta, p.f_min, incremental=True)
-            assert res.kernel_used == 3
+            assert res.kernel_used == 3 or res.refreshed      # (a drift check above tol / 4 turns the next step into a refresh)
         ref = reference(oracle, coracle, p)
         band = check_step(p, ref, res, mask, ctx.mu(), ctx.sigma2(), precision, label="chain48")
-        check_argmax(res, ref, band, mask)
+        check_argmax(res, ref, band, mask, p.f_min)
 
 
 @pytest.mark.parametrize("ks", [[1, 3], [8, 16], [2, 5, 1]])
-def test_incremental_gemm_kernel(pkg, monkeypatch, ks):
+def test_incremental_gemm_kernel(pkg, ks):
     """fp32, a grid with at least one (256-row slab, column pair) item per CTA pair: the incremental step runs as a
     tensor-core GEMM through the separable RBF (posterior_tc_inc.cuh; kernel_used = 2 for any k <= 16).  Checked against a
-    full refresh of the same observations and against the FMA kernels (SBO_TC_INC=0) on the same chain; ragged edges."""
+    full refresh of the same observations and against the FMA kernels (SBO_OPT_TC_INC = 0) on the same chain; ragged edges."""
     n0 = 600   # enough observations for the library's cost model to prefer the GEMM at k = 1 on this grid
     total = n0 + sum(ks)
     p = S.make_problem("C3", n=total, W=1990, H=2400)
     out = {}
     for flag in ("1", "0"):
-        monkeypatch.setenv("SBO_TC_INC", flag)
-        with make_ctx(pkg, p, precision="fp32", kernel="tcgen05", max_obs=total) as ctx:
+        with make_ctx(pkg, p, precision="fp32", kernel="tcgen05", max_obs=total, options={"tc_inc": int(flag)}) as ctx:
             ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
             ctx.set_observations(p.xy[:n0], p.y[:n0])
             ctx.step(p.beta, p.f_min, want_mask=False)
@@ -283,6 +290,7 @@ p = S.make_problem('C2', n={n}, W={W}, H={H})
 out = sys.argv[1]
 ctx = pkg.SboContext(sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean,
                      precision='fp32', max_obs=p.n + 8, max_cells=p.m)
+ctx.set_option('tc_eager', int(sys.argv[2]))
 ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
 for rep in range(3):                                   # fit (+ eager first pairs) then step, three times over
     ctx.set_observations(p.xy, p.y)
@@ -303,12 +311,12 @@ ctx.close()
 """
 
 
-@pytest.mark.parametrize("n,W,H", [(1024, 1024, 64), (700, 512, 96), (1600, 640, 80), (2304, 1024, 40)])
+@pytest.mark.parametrize("n,W,H", [(1024, 1024, 64), (700, 512, 96), (1600, 640, 80), (2048, 1024, 40)])
 def test_eager_first_pairs_bit_identical(pkg, oracle, coracle, n, W, H):
     """sbo_set_observations launches the first row-block pairs of the posterior on a side stream while the factorisation
-    is still running (>= 2 tiles per SM, dense walk, 512 <= n <= 4096); the next sbo_step resumes from their running sums.
-    Same sums in the same order: mu, sigma^2 and the mask equal the one-launch result (SBO_TC_EAGER=0) bit for bit, also
-    when a grid change or an append drops the partial result.  The switch is read once per process: one process each."""
+    is still running (>= 2 tiles per SM, 512 <= n <= 2048); the next sbo_step resumes from their running sums.
+    Same sums in the same order: mu, sigma^2 and the mask equal the one-launch result (SBO_OPT_TC_EAGER = 0) bit for bit,
+    also when a grid change or an append drops the partial result.  One process per setting."""
     import subprocess, sys, tempfile
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     script = _EAGER_SCRIPT.format(root=root, n=n, W=W, H=H)
@@ -316,8 +324,7 @@ def test_eager_first_pairs_bit_identical(pkg, oracle, coracle, n, W, H):
     res = {}
     with tempfile.TemporaryDirectory() as td:
         for flag in ("1", "0"):
-            subprocess.run([sys.executable, "-c", script, os.path.join(td, "e" + flag)], check=True,
-                           env=dict(os.environ, SBO_TC_EAGER=flag), timeout=600)
+            subprocess.run([sys.executable, "-c", script, os.path.join(td, "e" + flag), flag], check=True, timeout=600)
             res[flag] = {k: np.load(os.path.join(td, "e" + flag + "_" + k + ".npy")) for k in keys}
     for k in keys:
         assert np.array_equal(res["1"][k], res["0"][k]), k
@@ -329,16 +336,16 @@ def test_eager_first_pairs_bit_identical(pkg, oracle, coracle, n, W, H):
 
 
 @pytest.mark.parametrize("precision", ["fp64"])
-def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, monkeypatch, precision):
+def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, precision):
     """One new row, >= one 128 x 128 tile per SM: the 2-D register-tile kernels.  Same projections as the column-strip
-    kernel (SBO_THIN_2D=0), different summation order: agreement to rounding; ragged tile edges; and against a full
+    kernel (SBO_OPT_THIN_2D = 0), different summation order: agreement to rounding; ragged tile edges; and against a full
     refresh of the same observation set."""
     n0 = 130
     p = S.make_problem("C5", n=n0 + 2, W=1990, H=1250)
     out = {}
     for flag in ("0", "1"):
-        monkeypatch.setenv("SBO_THIN_2D", flag)
-        with make_ctx(pkg, p, precision=precision, kernel="auto" if precision == "fp64" else "tcgen05", max_obs=n0 + 2) as ctx:
+        with make_ctx(pkg, p, precision=precision, kernel="auto" if precision == "fp64" else "tcgen05", max_obs=n0 + 2,
+                      options={"thin_2d": int(flag)}) as ctx:
             ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
             ctx.set_observations(p.xy[:n0], p.y[:n0])
             ctx.step(p.beta, p.f_min, want_mask=False)
@@ -357,25 +364,25 @@ def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, monkeypatch, precision):
 
 
 @pytest.mark.parametrize("spread,n", [(1.0, 1500), (4.0, 1500), (12.0, 1500), (4.0, 1100), (12.0, 2100)])  # 6, 5 and 9 row blocks
-def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, monkeypatch, spread, n):
+def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, spread, n):
     """The tcgen05 kernel leaves out 64-observation chunks whose K* entries are all < 2^-b sigma_f^2 for a cell tile (b from tc_skip_bits: sigma^2 moves by < 1e-7 sigma_f^2)
     (posterior_tc.cu, block sparsity of K*).  Stretching the domain (spread) makes most chunks, whole row blocks and
     for some tiles everything skippable; results must still meet the oracle and agree with the dense walk
-    (SBO_TC_SKIP=0) far below the tolerance."""
+    (SBO_OPT_TC_SKIP = 0) far below the tolerance.  The default walk is also graded (far visits issue hi.hi only) and
+    strip-major; n = 2100 plans with the measured row norm of L^-1."""
     p = S.make_problem("C3", n=n, W=384, H=7)
     p.xy = p.xy * spread
     p.rx, p.ry = p.rx * spread, p.ry * spread * 9.0        # a tall grid: rows far from each other
     ref = reference(oracle, coracle, p)
     out = {}
     for skip in ("1", "0"):
-        monkeypatch.setenv("SBO_TC_SKIP", skip)
-        with make_ctx(pkg, p, kernel="tcgen05") as ctx:
+        with make_ctx(pkg, p, kernel="tcgen05", options={"tc_skip": int(skip)}) as ctx:
             ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
             ctx.set_observations(p.xy, p.y)
             res, mask = ctx.step(p.beta, p.f_min)
             out[skip] = (ctx.mu(), ctx.sigma2(), res.ms_posterior)
             band = check_step(p, ref, res, mask, out[skip][0], out[skip][1], "fp32", label=f"spread {spread} skip={skip}")
-            check_argmax(res, ref, band, mask)
+            check_argmax(res, ref, band, mask, p.f_min)
     print(f"    posterior ms: skipping {out['1'][2]:.3f}, dense {out['0'][2]:.3f}")
     assert np.abs(out["1"][0] - out["0"][0]).max() <= 1e-9 * max(1.0, np.abs(ref["mu"]).max()) + 2e-6
     assert np.abs(out["1"][1] - out["0"][1]).max() <= 1e-6
