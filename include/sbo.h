@@ -337,6 +337,10 @@ int32_t sbo_tc_plan(sbo_ctx* ctx, int32_t* cta_group, int32_t* skipping, double*
  * [3] share of the dense walk's MMA passes that are issued (executed tensor flops / dense 3-product flops), [4] measured
  * max row 1-norm of L^-1 (0 = a-priori bound in use), [5] tiles per strip of the tile order (0 = raster). */
 int32_t sbo_tc_plan_detail(sbo_ctx* ctx, double out[6]);
+/* Tensor-core flops the last full tcgen05 refresh of this context EXECUTED (counted by the MMA issuers: every split
+ * product, block-triangular padding included, skipped chunks excluded): the numerator of a pipe-utilisation figure, as
+ * opposed to the credited m n (n + 1) of SURVEY M4.  0 when the last step ran another kernel. */
+int32_t sbo_tc_executed_flops(sbo_ctx* ctx, double* flops);
 /* Device properties the library sees: SM count, and 1 if tcgen05 path usable. */
 int32_t sbo_device_info(const sbo_ctx* ctx, int32_t* sm_count, int32_t* tcgen05_ok);
 

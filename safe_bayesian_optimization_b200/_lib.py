@@ -90,6 +90,7 @@ SYMBOLS = {
                                             C.POINTER(C.c_int32)]),
     "sbo_tc_plan": (C.c_int32, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double)]),
     "sbo_tc_plan_detail": (C.c_int32, [_P, _D]),
+    "sbo_tc_executed_flops": (C.c_int32, [_P, _D]),
     "sbo_set_option": (C.c_int32, [_P, C.c_int32, C.c_int32]),
     "sbo_get_option": (C.c_int32, [_P, C.c_int32, C.POINTER(C.c_int32)]),
     "sbo_plan_row_bands": (C.c_int32, [C.POINTER(SboConfig), _D, C.c_int32, C.c_double, C.c_double, C.c_double, C.c_double,

@@ -95,6 +95,7 @@ struct sbo_ctx {
   double linv_r1 = 0.0;          // max row 1-norm of L^-1, measured by the fit / append (0: unknown)
   int tc_skip_plan = -1;         // cached decision of tc_plan_skip for this grid + observation set (-1: stale)
   std::vector<double> h_xy_sorted;  // host copy of d_xy (internal order), for the skip planner
+  unsigned long long* d_exec_cols = nullptr;   // executed-work counter of the last full tcgen05 refresh (sbo_tc_executed_flops)
   float* d_chunk_bbox = nullptr; // [n_cap / 64] float4 scaled bounding boxes of the observation chunks
   float* d_alpha_f32 = nullptr;  // [n_cap]
   float* d_obs_f32 = nullptr;    // [n_cap] float4: scaled observation coordinates as fp32 (hi, lo) pairs (posterior_tc.cu)

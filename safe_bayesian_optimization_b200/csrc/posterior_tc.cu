@@ -109,6 +109,7 @@ struct TcParams {
   int pi_lo, pi_hi;        // pair kernel: row-block pairs [pi_lo, pi_hi) of this launch
   int rs_mode;             // pair kernel: 0 whole job; 1 partial (store the running row sums in rs_part, no sigma^2 / mu); 2 resume from rs_part
   float2* rs_part;         // [m_local] double-word fp32 running sums of a partial launch
+  unsigned long long* exec_cols;   // pair kernel: += sum of N over the issued MMAs (M 256, K 16 each); executed flops = 2 * 256 * 16 * that
   long long* dbg_clk;      // SBO_TC_CLK=1: per-role cycle counters of cluster 0 (timing forensics)
   int dbg;                 // SBO_TC_DBG (timing experiments only, results are wrong): 1 generators skip the K* math, 2 epilogue skips the TMEM reads, 4 one MMA pass instead of three
 };
@@ -1130,6 +1131,7 @@ static void tc_fill_params(sbo_ctx* ctx, TcParams& p, int j_lo, int j_hi, bool a
   p.pi_hi = ((ctx->n + BN - 1) / BN + 1) / 2;
   p.rs_mode = 0;
   p.rs_part = nullptr;
+  p.exec_cols = ctx->d_exec_cols;
   p.dbg = 0;
   p.dbg_clk = nullptr;
 }
@@ -1217,6 +1219,7 @@ int32_t tc_eager_launch(sbo_ctx* ctx, int pairs, cudaEvent_t ready) {
   p.pi_hi = pairs;
   p.rs_mode = 1;
   p.rs_part = reinterpret_cast<float2*>(ctx->d_rs_part);
+  if (ctx->d_exec_cols) SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_exec_cols, 0, sizeof(unsigned long long), se));
   const long long ntiles = (long long)p.rows_local * ((p.W + BM - 1) / BM);
   // leave ~1/8 of the SMs to the factorisation's own kernels
   const long long clusters =
@@ -1401,6 +1404,8 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
     bool pair = !p.accumulate && p.j_lo == 0 && p.j_hi == p.n && p.n > BN && p.dbg_v == nullptr;
     pair = pair && ctx->opt.tc_pair != 0;
     if (resume && !pair) return fail(ctx, SBO_ERR_STATE, "eager first pairs without the pair kernel");
+    if (pair && !resume && ctx->d_exec_cols)   // executed-work counter of this launch (a resumed launch adds to the eager part's count)
+      SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_exec_cols, 0, sizeof(unsigned long long), ctx->stream));
     const cudaError_t e = pair     ? tc_launch_pair(ctx, p, ctx->stream, pairs)
                           : p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, true>, tmap, p)
                                    : cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, false>, tmap, p);

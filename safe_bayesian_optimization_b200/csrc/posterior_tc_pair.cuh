@@ -155,6 +155,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
   } else if (warp == 1) {
     // =============================== MMA issuer (leader CTA; converged warp, one elected lane issues) ===============================
     uint32_t ita = 0, itb = 0, use0 = 0, use1 = 0;
+    unsigned long long issued_cols = 0;   // sum over the MMAs issued of their N (each is M 256 x N x K 16): the executed tensor work
     for (long long gt = group; rank == 0 && gt < ngtiles; gt += ngroups) {
       if (kSkip) build_chunk_mask<CG>(cmask, geom, gt, ntiles, nchunks);
       for (int pi = p.pi_lo; pi < p.pi_hi; ++pi) {
@@ -189,6 +190,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
             // diagonal block, chunk c: columns < 64 c of the accumulator get no contribution (zeros of L^-1)
             const uint32_t c = fresh ? 0u : (uint32_t)max(kc - jb * (BN / BK), 0);
             const uint32_t idesc = idesc_f16<CG>(BN - c * BK), d_col = tmem_base + half * BN + c * BK;
+            issued_cols += (unsigned long long)((BK / UK) * (full3 ? 3 : 1)) * (BN - c * BK);
             if (elect_one()) {
 #pragma unroll
               for (int ks = 0; ks < BK / UK; ++ks) {
@@ -212,6 +214,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         }
       }
     }
+    if (p.exec_cols && rank == 0 && lane == 0 && issued_cols) atomicAdd(p.exec_cols, issued_cols);
   } else if (warp >= 4 && warp < 8) {
     // =============================== epilogue ===============================
     const int q = warp & 3;

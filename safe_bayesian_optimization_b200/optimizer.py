@@ -272,6 +272,12 @@ class SboContext:
         self._check(self.lib.sbo_tc_plan_detail(self._h, _dptr(out)))
         return dict(zip(("bits", "ring_bits", "kept_fraction", "pass_fraction", "linv_row_l1", "strip_tiles"), out.tolist()))
 
+    def tc_executed_flops(self) -> float:
+        """Tensor flops the last full tcgen05 refresh executed (sbo_tc_executed_flops)."""
+        v = C.c_double(0.0)
+        self._check(self.lib.sbo_tc_executed_flops(self._h, C.byref(v)))
+        return float(v.value)
+
     def frontier_image(self):
         """(img H x W uint8 0/255, col_of_px int32[W], row_of_py int32[H]): the image of reference :444-456 built on the
         GPU with the reference's pixel map, and the pixel -> cell tables that replace its hash map (:468-475)."""
