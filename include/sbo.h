@@ -143,9 +143,11 @@ typedef enum {
   SBO_OPT_TC_STRIP = 9,          /* tile pairs per strip of the strip-major tile order (default 4; 0 = raster order)       */
   SBO_OPT_REFRESH_EVERY = 10,    /* sbo_step_incremental runs a full refresh after this many incremental steps
                                     (default 256 in SBO_FP32, 0 = never in SBO_FP64)                                        */
-  SBO_OPT_DRIFT_CHECK_EVERY = 11,/* every this many incremental steps, re-evaluate SBO_OPT_DRIFT_ROWS grid rows exactly
-                                    and refresh when the deviation exceeds tol / 4 (default 16; 0 = never)                  */
-  SBO_OPT_DRIFT_ROWS = 12        /* grid rows of the drift sample (default 2, spread over the shard)                       */
+  SBO_OPT_DRIFT_CHECK_EVERY = 11,/* every this many incremental steps, re-evaluate SBO_OPT_DRIFT_ROWS sample blocks exactly
+                                    and refresh when the deviation exceeds tol / 4 (default: 16 in SBO_FP32, 256 in
+                                    SBO_FP64, where a check costs several incremental steps; 0 = never)                     */
+  SBO_OPT_DRIFT_ROWS = 12        /* sample blocks per check, spread over the shard (default 2; a block is one grid row,
+                                    eight consecutive rows in SBO_FP64: the DMMA kernel's tile is a 16 x 8 patch of cells)  */
 } sbo_option;
 int32_t sbo_set_option(sbo_ctx* ctx, int32_t option, int32_t value);
 int32_t sbo_get_option(const sbo_ctx* ctx, int32_t option, int32_t* value);
@@ -322,6 +324,37 @@ int32_t sbo_plan_row_bands(const sbo_config* cfg, const double* xy, int32_t n, d
 /* Host-side merge of per-shard results with the library's total order
  * (value desc, index asc); used when the host does its own transport. */
 int32_t sbo_merge_step_out(const sbo_step_out* parts, int32_t count, sbo_step_out* merged);
+
+/* ---- one context over several GPUs (single process, single caller thread) ------------------------------------------
+ *
+ * The node is one process with a SingleThreadedExecutor (:1500-1508); it cannot run one process per GPU.  A group owns
+ * one sbo_ctx per device, cuts the grid into bands of rows of equal estimated work (sbo_plan_row_bands, re-planned when
+ * the observations are replaced), drives the members from one host thread per device inside each call, writes every
+ * band of the safe mask straight into the caller's ONE H x W image and folds the per-band records with the library's
+ * total order.  cfg->device is ignored (devices[] decides; a device may be listed more than once); cfg->max_cells is
+ * the capacity in cells of the WHOLE grid.  Semantics, status codes and "last good state" behaviour are those of the
+ * single-context calls they mirror.  sbo_group_member gives the member contexts for everything else (options, plan,
+ * read-back of a band). */
+typedef struct sbo_group sbo_group;
+int32_t sbo_group_create(const sbo_config* cfg, const int32_t* devices, int32_t n_devices, sbo_group** out);
+int32_t sbo_group_destroy(sbo_group* g);
+const char* sbo_group_last_error(const sbo_group* g);   /* g may be NULL: last create error */
+int32_t sbo_group_size(const sbo_group* g);
+sbo_ctx* sbo_group_member(sbo_group* g, int32_t i);
+int32_t sbo_group_bands(const sbo_group* g, int32_t* row_cuts /* [size + 1] */);
+int32_t sbo_group_set_option(sbo_group* g, int32_t option, int32_t value);
+int32_t sbo_group_set_grid(sbo_group* g, double x0, double y0, double rx, double ry, int32_t W, int32_t H);
+int32_t sbo_group_set_observations(sbo_group* g, const double* xy, const double* y, int32_t n);
+int32_t sbo_group_append_observations(sbo_group* g, const double* xy, const double* y, int32_t k);
+int32_t sbo_group_num_observations(const sbo_group* g);
+/* mask_host: the whole H x W image (may be NULL); out: merged over the bands (timings = the slowest member). */
+int32_t sbo_group_step(sbo_group* g, double beta, double f_min, uint8_t* mask_host, sbo_step_out* out);
+int32_t sbo_group_step_incremental(sbo_group* g, double beta, double f_min, uint8_t* mask_host, sbo_step_out* out);
+/* GetNextSubgoal's rule (:508-549) on a frontier that crosses the bands. */
+int32_t sbo_group_select_subgoal(sbo_group* g, const int32_t* frontier, int64_t F, double goal_x, double goal_y,
+                                 int32_t* out_cell);
+int32_t sbo_group_copy_mu_f64(sbo_group* g, double* host_dst);       /* W * H values */
+int32_t sbo_group_copy_sigma2_f64(sbo_group* g, double* host_dst);
 
 /* ---- introspection -------------------------------------------------------- */
 

@@ -107,6 +107,23 @@ SYMBOLS = {
     "sbo_comm_init": (C.c_int32, [_P, _U8, C.c_int32, C.c_int32]),
     "sbo_comm_destroy": (C.c_int32, [_P]),
     "sbo_merge_step_out": (C.c_int32, [C.POINTER(SboStepOut), C.c_int32, C.POINTER(SboStepOut)]),
+    "sbo_group_create": (C.c_int32, [C.POINTER(SboConfig), C.POINTER(C.c_int32), C.c_int32, C.POINTER(_P)]),
+    "sbo_group_destroy": (C.c_int32, [_P]),
+    "sbo_group_last_error": (C.c_char_p, [_P]),
+    "sbo_group_size": (C.c_int32, [_P]),
+    "sbo_group_member": (_P, [_P, C.c_int32]),
+    "sbo_group_bands": (C.c_int32, [_P, C.POINTER(C.c_int32)]),
+    "sbo_group_set_option": (C.c_int32, [_P, C.c_int32, C.c_int32]),
+    "sbo_group_set_grid": (C.c_int32, [_P, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int32, C.c_int32]),
+    "sbo_group_set_observations": (C.c_int32, [_P, _D, _D, C.c_int32]),
+    "sbo_group_append_observations": (C.c_int32, [_P, _D, _D, C.c_int32]),
+    "sbo_group_num_observations": (C.c_int32, [_P]),
+    "sbo_group_step": (C.c_int32, [_P, C.c_double, C.c_double, _U8, C.POINTER(SboStepOut)]),
+    "sbo_group_step_incremental": (C.c_int32, [_P, C.c_double, C.c_double, _U8, C.POINTER(SboStepOut)]),
+    "sbo_group_select_subgoal": (C.c_int32, [_P, C.POINTER(C.c_int32), C.c_int64, C.c_double, C.c_double,
+                                             C.POINTER(C.c_int32)]),
+    "sbo_group_copy_mu_f64": (C.c_int32, [_P, _D]),
+    "sbo_group_copy_sigma2_f64": (C.c_int32, [_P, _D]),
     "sbo_launch_count": (C.c_int64, [_P]),
     "sbo_device_info": (C.c_int32, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
 }

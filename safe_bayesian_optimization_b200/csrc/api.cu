@@ -115,19 +115,23 @@ __global__ void drift_compare_kernel(const T* __restrict__ mu, const T* __restri
 
 int32_t drift_check(sbo_ctx* ctx) {
   const int rows = ctx->row1 - ctx->row0, W = ctx->W;
-  const int dr = std::min(std::max(ctx->opt.drift_rows, 1), rows);
   if (rows <= 0 || ctx->n == 0) return SBO_OK;
   int which = 0;
   SBO_TRY(pick_kernel(ctx, &which));
+  // A sample = a block of consecutive grid rows: one row for the tcgen05 / SIMT kernels (their tiles are pieces of one
+  // row), 8 for the DMMA kernel, whose tile is a 16 x 8 patch of cells -- a single row would cost it the same as eight.
+  const int rb = std::min(rows, which == SBO_KERNEL_DMMA ? 8 : 1);
+  const int dr = std::min(std::max(ctx->opt.drift_rows, 1), rows / rb);
   const size_t es = elem_size(ctx);
-  if (ctx->drift_cap < W) {
+  const int64_t need = (int64_t)W * rb;
+  if (ctx->drift_cap < need) {
     for (void** p : {&ctx->d_drift_mu, &ctx->d_drift_s2}) {
       if (*p) cudaFree(*p);
       *p = nullptr;
-      SBO_CUDA(ctx, cudaMalloc(p, es * (size_t)W));
+      SBO_CUDA(ctx, cudaMalloc(p, es * (size_t)need));
     }
     if (!ctx->d_drift_out) SBO_CUDA(ctx, cudaMalloc(&ctx->d_drift_out, 2 * sizeof(double)));
-    ctx->drift_cap = W;
+    ctx->drift_cap = need;
   }
   SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_drift_out, 0, 2 * sizeof(double), ctx->stream));
   // the launchers read the shard geometry and the output buffers from the context: point them at one row + the scratch
@@ -137,9 +141,9 @@ int32_t drift_check(sbo_ctx* ctx) {
   void* s2 = ctx->d_s2;
   int32_t st = SBO_OK;
   for (int i = 0; i < dr && st == SBO_OK; ++i) {
-    const int lr = (int)(((2LL * i + 1) * rows) / (2LL * dr));   // spread over the shard
-    ctx->row0 = row0 + lr; ctx->row1 = row0 + lr + 1;
-    ctx->m_local = W; ctx->cell0 = (int64_t)ctx->row0 * W;
+    const int lr = std::min((int)(((2LL * i + 1) * rows) / (2LL * dr)), rows - rb);   // spread over the shard
+    ctx->row0 = row0 + lr; ctx->row1 = row0 + lr + rb;
+    ctx->m_local = need; ctx->cell0 = (int64_t)ctx->row0 * W;
     ctx->d_mu = ctx->d_drift_mu; ctx->d_s2 = ctx->d_drift_s2;
     if (which == SBO_KERNEL_TCGEN05) st = launch_posterior_tc(ctx, 0, ctx->n, false);
     else if (which == SBO_KERNEL_DMMA) st = launch_posterior_f64(ctx, 0, ctx->n, false);
@@ -149,13 +153,13 @@ int32_t drift_check(sbo_ctx* ctx) {
     const double inv_sf2 = 1.0 / (ctx->cfg.sigma_f * ctx->cfg.sigma_f);
     const long long off = (long long)lr * W;
     if (ctx->cfg.precision == SBO_FP64)
-      drift_compare_kernel<double><<<std::min((W + 255) / 256, 64), 256, 0, ctx->stream>>>(
+      drift_compare_kernel<double><<<(int)std::min<int64_t>((need + 255) / 256, 64), 256, 0, ctx->stream>>>(
           static_cast<const double*>(mu), static_cast<const double*>(s2), static_cast<const double*>(ctx->d_drift_mu),
-          static_cast<const double*>(ctx->d_drift_s2), W, off, inv_sf2, ctx->d_drift_out);
+          static_cast<const double*>(ctx->d_drift_s2), (int)need, off, inv_sf2, ctx->d_drift_out);
     else
-      drift_compare_kernel<float><<<std::min((W + 255) / 256, 64), 256, 0, ctx->stream>>>(
+      drift_compare_kernel<float><<<(int)std::min<int64_t>((need + 255) / 256, 64), 256, 0, ctx->stream>>>(
           static_cast<const float*>(mu), static_cast<const float*>(s2), static_cast<const float*>(ctx->d_drift_mu),
-          static_cast<const float*>(ctx->d_drift_s2), W, off, inv_sf2, ctx->d_drift_out);
+          static_cast<const float*>(ctx->d_drift_s2), (int)need, off, inv_sf2, ctx->d_drift_out);
     SBO_LAUNCH_CHECK(ctx, "drift_compare_kernel");
   }
   SBO_TRY(st);
@@ -379,6 +383,7 @@ int32_t sbo_destroy(sbo_ctx* ctx) {
 
 int32_t sbo_set_stream(sbo_ctx* ctx, void* cuda_stream) {
   if (!ctx) return SBO_ERR_INVALID_ARG;
+  cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   ctx->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
   return SBO_OK;
@@ -386,6 +391,7 @@ int32_t sbo_set_stream(sbo_ctx* ctx, void* cuda_stream) {
 
 int32_t sbo_synchronize(sbo_ctx* ctx) {
   if (!ctx) return SBO_ERR_INVALID_ARG;
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return SBO_OK;
 }
@@ -402,6 +408,7 @@ int32_t sbo_set_grid(sbo_ctx* ctx, double x0, double y0, double rx, double ry, i
   ctx->W = W; ctx->H = H; ctx->row0 = row0; ctx->row1 = row1;
   ctx->cell0 = (int64_t)row0 * W;
   ctx->m_local = m_local;
+  cudaSetDevice(ctx->device);
   tc_eager_cancel(ctx);
   ++ctx->grid_epoch;
   ctx->grid_set = true;
@@ -450,7 +457,7 @@ int32_t sbo_set_option(sbo_ctx* ctx, int32_t option, int32_t value) {
   }
   int* slot = option_slot(ctx, option);
   if (!slot) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_option: unknown option");
-  if (value < 0 && option != SBO_OPT_REFRESH_EVERY) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_option: negative value");
+  if (value < 0 && option != SBO_OPT_REFRESH_EVERY && option != SBO_OPT_DRIFT_CHECK_EVERY) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_option: negative value");
   if (option == SBO_OPT_TC_CTA_GROUP) {
     if (value != 1 && value != 2) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_set_option: SBO_OPT_TC_CTA_GROUP is 1 or 2");
     SBO_CUDA(ctx, cudaSetDevice(ctx->device));
@@ -688,6 +695,7 @@ int32_t sbo_copy_linv(sbo_ctx* ctx, double* host_dst) {
   if (!ctx || !host_dst) return SBO_ERR_INVALID_ARG;
   const size_t n = (size_t)ctx->n;
   if (n == 0) return SBO_OK;
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   SBO_CUDA(ctx, cudaMemcpy2DAsync(host_dst, n * sizeof(double), ctx->d_Linv, (size_t)ctx->n_cap * sizeof(double),
                                   n * sizeof(double), n, cudaMemcpyDeviceToHost, ctx->stream));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -697,6 +705,7 @@ int32_t sbo_copy_linv(sbo_ctx* ctx, double* host_dst) {
 int32_t sbo_copy_alpha(sbo_ctx* ctx, double* host_dst) {
   if (!ctx || !host_dst) return SBO_ERR_INVALID_ARG;
   if (ctx->n == 0) return SBO_OK;
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   std::vector<double> tmp((size_t)ctx->n);
   SBO_CUDA(ctx, cudaMemcpyAsync(tmp.data(), ctx->d_alpha, sizeof(double) * (size_t)ctx->n, cudaMemcpyDeviceToHost, ctx->stream));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -839,16 +848,9 @@ int32_t sbo_compact_cells(sbo_ctx* ctx, int32_t mode, int32_t* idx_host, int64_t
   return compact_cells(ctx, mode, idx_host, cap, count);
 }
 
-int32_t sbo_select_subgoal(sbo_ctx* ctx, const int32_t* frontier, int64_t F, double goal_x, double goal_y,
-                           int32_t* out_cell) {
-  if (!ctx || !out_cell) return SBO_ERR_INVALID_ARG;
-  *out_cell = -1;
-  if (F < 0 || (F > 0 && !frontier)) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_select_subgoal: null frontier or F < 0");
-  if (F == 0) return SBO_OK;  // "No frontier points found" (:503-506)
-  if (ctx->source == PosteriorSource::kNone)
-    return fail(ctx, SBO_ERR_STATE, "sbo_select_subgoal: no posterior yet (call sbo_step or sbo_compute_sets first)");
-  if (!ctx->grid_set) return fail(ctx, SBO_ERR_STATE, "sbo_select_subgoal: grid not set");
-  if (F > 0xFFFFFFFFll) return fail(ctx, SBO_ERR_CAPACITY, "sbo_select_subgoal: frontier longer than 2^32");
+}  // extern "C"
+namespace sbo {
+int32_t select_upload(sbo_ctx* ctx, const int32_t* frontier, int64_t F) {
   SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   if (F > ctx->sel_cap) {
     for (void** p : {(void**)&ctx->d_frontier, (void**)&ctx->d_sel_keys, (void**)&ctx->d_sel_width}) {
@@ -862,6 +864,22 @@ int32_t sbo_select_subgoal(sbo_ctx* ctx, const int32_t* frontier, int64_t F, dou
     ctx->sel_cap = cap;
   }
   SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_frontier, frontier, sizeof(int32_t) * (size_t)F, cudaMemcpyHostToDevice, ctx->stream));
+  return SBO_OK;
+}
+}  // namespace sbo
+extern "C" {
+
+int32_t sbo_select_subgoal(sbo_ctx* ctx, const int32_t* frontier, int64_t F, double goal_x, double goal_y,
+                           int32_t* out_cell) {
+  if (!ctx || !out_cell) return SBO_ERR_INVALID_ARG;
+  *out_cell = -1;
+  if (F < 0 || (F > 0 && !frontier)) return fail(ctx, SBO_ERR_INVALID_ARG, "sbo_select_subgoal: null frontier or F < 0");
+  if (F == 0) return SBO_OK;  // "No frontier points found" (:503-506)
+  if (ctx->source == PosteriorSource::kNone)
+    return fail(ctx, SBO_ERR_STATE, "sbo_select_subgoal: no posterior yet (call sbo_step or sbo_compute_sets first)");
+  if (!ctx->grid_set) return fail(ctx, SBO_ERR_STATE, "sbo_select_subgoal: grid not set");
+  if (F > 0xFFFFFFFFll) return fail(ctx, SBO_ERR_CAPACITY, "sbo_select_subgoal: frontier longer than 2^32");
+  SBO_TRY(select_upload(ctx, frontier, F));
   SBO_TRY(launch_select(ctx, ctx->d_frontier, F, goal_x, goal_y));
   SBO_CUDA(ctx, cudaMemcpyAsync(ctx->h_sel_out, ctx->d_sel_out, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -879,6 +897,7 @@ static int32_t copy_posterior(sbo_ctx* ctx, const void* src, void* dst, bool to_
   if (!ctx->posterior_valid) return fail(ctx, SBO_ERR_STATE, "sbo_copy_*: no posterior yet (call sbo_step first)");
   const size_t m = (size_t)ctx->m_local;
   if (m == 0) return SBO_OK;
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   if (!to_f64 || ctx->cfg.precision == SBO_FP64) {
     SBO_CUDA(ctx, cudaMemcpyAsync(dst, src, elem_size(ctx) * m, cudaMemcpyDeviceToHost, ctx->stream));
     SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -902,6 +921,7 @@ int32_t sbo_copy_mask(sbo_ctx* ctx, uint8_t* host_dst) {
   if (ctx->source == PosteriorSource::kNone) return fail(ctx, SBO_ERR_STATE, "sbo_copy_mask: no step yet");
   const size_t m = (size_t)(ctx->source == PosteriorSource::kHostArrays ? ctx->source_m : ctx->m_local);
   if (m == 0) return SBO_OK;
+  SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   SBO_CUDA(ctx, cudaMemcpyAsync(host_dst, ctx->d_mask, m, cudaMemcpyDeviceToHost, ctx->stream));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return SBO_OK;

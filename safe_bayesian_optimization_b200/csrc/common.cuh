@@ -32,7 +32,8 @@ struct SetsResult {
 struct Options {
   int tc_pair = 1, tc_eager = 1, tc_inc = 1, thin = 1, thin_2d = 1, tc_graded = 1, tc_strip = 4;
   int refresh_every = -1;       // -1: by precision (256 fp32, never fp64)
-  int drift_check_every = 16, drift_rows = 2;
+  int drift_check_every = -1;   // -1: by precision (16 fp32, 256 fp64)
+  int drift_rows = 2;           // sample blocks per check (a block = 1 grid row; 8 rows for the DMMA kernel's 16 x 8 cell patches)
 };
 
 enum class PosteriorSource : int { kNone = 0, kStep = 1, kHostArrays = 2 };
@@ -187,7 +188,8 @@ int32_t launch_sets_arrays(sbo_ctx* ctx, const double* d_mu, const double* d_std
 int sets_grid_size(const sbo_ctx* ctx);
 
 // select.cu
-int32_t launch_select(sbo_ctx* ctx, const int32_t* d_frontier, int64_t F, double gx, double gy);
+int32_t launch_select(sbo_ctx* ctx, const int32_t* d_frontier, int64_t F, double gx, double gy, int mode = 0);
+int32_t select_upload(sbo_ctx* ctx, const int32_t* frontier, int64_t F);   // api.cu: scratch sized for F entries, frontier H2D
 
 // factor.cu
 int32_t factor_full(sbo_ctx* ctx);                 // d_xy, d_r, n -> d_A (L), d_Linv, d_alpha, planes

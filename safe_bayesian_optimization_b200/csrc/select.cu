@@ -46,7 +46,10 @@ template <typename T, bool kStd>
 __global__ void __launch_bounds__(kSelThreads)
 select_kernel(const int32_t* __restrict__ frontier, long long F, SelParams p, const T* __restrict__ mu,
               const T* __restrict__ s, unsigned long long* __restrict__ keys, double* __restrict__ width,
-              int32_t* __restrict__ out) {
+              int32_t* __restrict__ out, int mode) {
+  // mode 0: the whole rule.  Device groups (group.cu) split it: mode 1 = phase 1 only, on the cells of THIS shard (cells
+  // of other shards are marked key = ~0, width = -2 and are no error); mode 2 = phases 2 and 3 on keys / widths that the
+  // host has merged from all shards.
   __shared__ unsigned int hist[256];
   __shared__ unsigned long long sh_prefix;
   __shared__ long long sh_rank;
@@ -57,11 +60,11 @@ select_kernel(const int32_t* __restrict__ frontier, long long F, SelParams p, co
   __syncthreads();
 
   // ---- phase 1: distance keys and widths --------------------------------------
-  for (long long i = tid; i < F; i += kSelThreads) {
+  for (long long i = tid; mode != 2 && i < F; i += kSelThreads) {
     const long long cell = frontier[i];
     const long long local = cell - p.cell0;
     if (local < 0 || local >= p.m) {
-      sh_bad = 1;
+      if (mode == 0) sh_bad = 1;
       keys[i] = ~0ull;
       width[i] = -2.0;
       continue;
@@ -89,6 +92,7 @@ select_kernel(const int32_t* __restrict__ frontier, long long F, SelParams p, co
     if (tid == 0) *out = -2;  // frontier cell outside this context's cells
     return;
   }
+  if (mode == 1) return;
 
   // ---- phase 2: radix select of the T-th smallest (key, position) -------------
   long long top = F / 4;
@@ -182,25 +186,25 @@ select_kernel(const int32_t* __restrict__ frontier, long long F, SelParams p, co
 
 }  // namespace
 
-int32_t launch_select(sbo_ctx* ctx, const int32_t* d_frontier, int64_t F, double gx, double gy) {
+int32_t launch_select(sbo_ctx* ctx, const int32_t* d_frontier, int64_t F, double gx, double gy, int mode) {
   SelParams p;
   p.x0 = ctx->x0; p.y0 = ctx->y0; p.rx = ctx->rx; p.ry = ctx->ry; p.W = ctx->W;
   p.beta = ctx->last_beta; p.gx = gx; p.gy = gy;
   if (ctx->source == PosteriorSource::kHostArrays) {
     p.cell0 = 0; p.m = ctx->source_m; p.noise_add = 0.0;
     select_kernel<double, true><<<1, kSelThreads, 0, ctx->stream>>>(d_frontier, F, p, ctx->d_mu64, ctx->d_std64,
-                                                                     ctx->d_sel_keys, ctx->d_sel_width, ctx->d_sel_out);
+                                                                     ctx->d_sel_keys, ctx->d_sel_width, ctx->d_sel_out, mode);
   } else {
     p.cell0 = ctx->cell0; p.m = ctx->m_local;
     p.noise_add = ctx->cfg.include_noise_in_sigma ? ctx->cfg.noise_var : 0.0;
     if (ctx->cfg.precision == SBO_FP64) {
       select_kernel<double, false><<<1, kSelThreads, 0, ctx->stream>>>(
           d_frontier, F, p, static_cast<const double*>(ctx->d_mu), static_cast<const double*>(ctx->d_s2),
-          ctx->d_sel_keys, ctx->d_sel_width, ctx->d_sel_out);
+          ctx->d_sel_keys, ctx->d_sel_width, ctx->d_sel_out, mode);
     } else {
       select_kernel<float, false><<<1, kSelThreads, 0, ctx->stream>>>(
           d_frontier, F, p, static_cast<const float*>(ctx->d_mu), static_cast<const float*>(ctx->d_s2),
-          ctx->d_sel_keys, ctx->d_sel_width, ctx->d_sel_out);
+          ctx->d_sel_keys, ctx->d_sel_width, ctx->d_sel_out, mode);
     }
   }
   SBO_LAUNCH_CHECK(ctx, "select_kernel");

@@ -326,6 +326,100 @@ class SboContext:
         self._check(self.lib.sbo_comm_init(self._h, buf, rank, world))
 
 
+class SboGroup:
+    """One object over several GPUs of the box, driven from one host thread (``sbo_group``): cost-balanced row bands, one
+    H x W mask image, merged argmax records.  ``devices`` may repeat an ordinal (several bands on one GPU)."""
+
+    def __init__(self, devices, *, sigma_f=1.0, length_scale=0.4, noise_var=0.1, prior_mean=0.0, precision="fp32",
+                 kernel="auto", max_obs=1024, max_cells=1 << 20, include_noise_in_sigma=False):
+        self.lib = L.load()
+        cfg = L.SboConfig(sigma_f, length_scale, noise_var, prior_mean, int(include_noise_in_sigma),
+                          {"fp32": L.SBO_FP32, "fp64": L.SBO_FP64}[precision],
+                          {"auto": L.SBO_KERNEL_AUTO, "simt": L.SBO_KERNEL_SIMT, "tcgen05": L.SBO_KERNEL_TCGEN05}[kernel],
+                          0, max_obs, 0, max_cells)
+        dev = np.ascontiguousarray(devices, dtype=np.int32)
+        self._h = C.c_void_p()
+        st = self.lib.sbo_group_create(C.byref(cfg), dev.ctypes.data_as(C.POINTER(C.c_int32)), dev.size, C.byref(self._h))
+        if st != L.SBO_OK:
+            msg = self.lib.sbo_group_last_error(None).decode()
+            self._h = None
+            raise L.SboError(st, msg)
+        self.size = dev.size
+        self.W = self.H = 0
+
+    def _check(self, st):
+        if st != L.SBO_OK:
+            raise L.SboError(st, self.lib.sbo_group_last_error(self._h).decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.sbo_group_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_option(self, name, value):
+        self._check(self.lib.sbo_group_set_option(self._h, L.OPTIONS[name], int(value)))
+
+    def set_grid(self, x0, y0, rx, ry, W, H):
+        self._check(self.lib.sbo_group_set_grid(self._h, x0, y0, rx, ry, W, H))
+        self.W, self.H = W, H
+
+    def set_observations(self, xy, y):
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1, 2)
+        y = np.ascontiguousarray(y, dtype=np.float64).reshape(-1)
+        self._check(self.lib.sbo_group_set_observations(self._h, _dptr(xy), _dptr(y), xy.shape[0]))
+
+    def append_observations(self, xy, y):
+        xy = np.ascontiguousarray(xy, dtype=np.float64).reshape(-1, 2)
+        y = np.ascontiguousarray(y, dtype=np.float64).reshape(-1)
+        self._check(self.lib.sbo_group_append_observations(self._h, _dptr(xy), _dptr(y), xy.shape[0]))
+
+    @property
+    def n_obs(self):
+        return int(self.lib.sbo_group_num_observations(self._h))
+
+    def bands(self):
+        cuts = np.zeros(self.size + 1, dtype=np.int32)
+        self._check(self.lib.sbo_group_bands(self._h, cuts.ctypes.data_as(C.POINTER(C.c_int32))))
+        return cuts.tolist()
+
+    def step(self, beta, f_min, mask_out=None, incremental=False):
+        if mask_out is None:
+            mask_out = np.empty(self.W * self.H, dtype=np.uint8)
+        out = L.SboStepOut()
+        fn = self.lib.sbo_group_step_incremental if incremental else self.lib.sbo_group_step
+        self._check(fn(self._h, float(beta), float(f_min), _u8ptr(mask_out), C.byref(out)))
+        return StepResult.from_c(out), mask_out
+
+    def select_subgoal(self, frontier, goal_xy) -> int:
+        fr = np.ascontiguousarray(frontier, dtype=np.int32).reshape(-1)
+        cell = C.c_int32(-1)
+        self._check(self.lib.sbo_group_select_subgoal(self._h, fr.ctypes.data_as(C.POINTER(C.c_int32)), fr.size,
+                                                      float(goal_xy[0]), float(goal_xy[1]), C.byref(cell)))
+        return int(cell.value)
+
+    def mu(self):
+        out = np.empty(self.W * self.H)
+        self._check(self.lib.sbo_group_copy_mu_f64(self._h, _dptr(out)))
+        return out
+
+    def sigma2(self):
+        out = np.empty(self.W * self.H)
+        self._check(self.lib.sbo_group_copy_sigma2_f64(self._h, _dptr(out)))
+        return out
+
+
 def shard_rows(H: int, rank: int, world: int):
     """Contiguous band of grid rows owned by `rank`."""
     base, rem = divmod(H, world)
