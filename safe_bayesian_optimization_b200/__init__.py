@@ -6,7 +6,7 @@ library and an sm_100 GPU.
 """
 from ._lib import LIB_PATH, SboError, build, load
 from .node import OptimizerCore, find_safety_contour_indices
-from .optimizer import SboContext, StepResult, merge_results, shard_rows
+from .optimizer import SboContext, SboGroup, StepResult, merge_results, plan_row_bands, shard_rows
 
 __all__ = ["LIB_PATH", "SboError", "build", "load", "OptimizerCore", "find_safety_contour_indices",
-           "SboContext", "StepResult", "merge_results", "shard_rows"]
+           "SboContext", "SboGroup", "StepResult", "merge_results", "plan_row_bands", "shard_rows"]
