@@ -305,6 +305,30 @@ int32_t sbo_compute_sets_device(sbo_ctx* ctx, const double* mu_dev, const double
                                 int64_t m, double beta, double f_min, uint8_t* mask_dev,
                                 sbo_step_out* out);
 
+/* ---- allocation-free variant ------------------------------------------------
+ *
+ * sbo_compute_sets_noalloc has NO COUNTERPART IN THE REFERENCE: it was added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * It is sbo_compute_sets_device without a context: the same kernel (ComputeConfidenceIntervals + UpdateSafeSet + argmax
+ * on device-resident fp64 mu / std, bit-identical results), launched on the CALLER's stream on the CURRENT device, with
+ * the grid-reduction scratch in a fixed __device__ array inside libsbo.so (112.25 KiB per GPU that loads the library,
+ * held until the process exits).  It allocates nothing -- no cudaMalloc / cudaFree, no allocating library routine -- and
+ * does not synchronise: mask_dev (m bytes, 0/255) and *result_dev (a device pointer the caller owns) are complete when
+ * `cuda_stream` reaches this point.  Limits and rules:
+ *   - m <= 134 217 728 cells (2^27); beyond that SBO_ERR_CAPACITY (text via sbo_last_error(NULL));
+ *   - every call on a device shares the one scratch array, which keeps the last call's contents (the call clears what
+ *     must start at zero): calls that OVERLAP on the GPU -- two streams, two host threads -- race; serialise them;
+ *   - the first call on each device looks the array's address up (cudaGetSymbolAddress): make it outside a capture. */
+typedef struct {
+  double ucb_value;     int64_t ucb_idx;      /* max of mu + beta std over safe cells (idx -1: no safe cell), ties -> lowest index */
+  double width_value;   int64_t width_idx;    /* max of Q1 - Q0 over safe cells */
+  int64_t safe_count;
+  int64_t clamped;                            /* always 0 here (std inputs) */
+  int64_t low_sigma2;                         /* always 0 here */
+} sbo_sets_record;
+int32_t sbo_compute_sets_noalloc(const double* mu_dev, const double* std_dev, int64_t m, double beta, double f_min,
+                                 uint8_t* mask_dev, sbo_sets_record* result_dev, void* cuda_stream);
+
 /* ---- multi-GPU ------------------------------------------------------------ */
 
 /* One process per GPU.  Rank 0 calls sbo_comm_unique_id, the host transports

@@ -44,6 +44,11 @@ class SboStepOut(C.Structure):
                 ("low_sigma2", C.c_int64), ("refreshed", C.c_int32), ("drift", C.c_float)]
 
 
+class SboSetsRecord(C.Structure):
+    _fields_ = [("ucb_value", C.c_double), ("ucb_idx", C.c_int64), ("width_value", C.c_double), ("width_idx", C.c_int64),
+                ("safe_count", C.c_int64), ("clamped", C.c_int64), ("low_sigma2", C.c_int64)]
+
+
 class SboMeasurement(C.Structure):
     _fields_ = [("x", C.c_double), ("y", C.c_double), ("z", C.c_double), ("value", C.c_double),
                 ("uncertainty", C.c_double), ("stamp_sec", C.c_int32), ("stamp_nanosec", C.c_uint32)]
@@ -103,6 +108,7 @@ SYMBOLS = {
     "sbo_step_device": (C.c_int32, [_P, C.c_double, C.c_double, C.POINTER(SboStepOut)]),
     "sbo_compute_sets_device": (C.c_int32, [_P, _P, _P, C.c_int64, C.c_double, C.c_double, _P,
                                             C.POINTER(SboStepOut)]),
+    "sbo_compute_sets_noalloc": (C.c_int32, [_P, _P, C.c_int64, C.c_double, C.c_double, _P, _P, _P]),
     "sbo_comm_unique_id": (C.c_int32, [_U8]),
     "sbo_comm_init": (C.c_int32, [_P, _U8, C.c_int32, C.c_int32]),
     "sbo_comm_destroy": (C.c_int32, [_P]),

@@ -15,6 +15,10 @@
 // bytes), several independent accesses in flight per thread; argmax is a
 // warp-shuffle -> block -> last-block-done grid reduction on (value, index)
 // records ordered (value desc, index asc).
+#include <algorithm>
+#include <cmath>
+#include <string>
+
 #include "common.cuh"
 
 namespace sbo {
@@ -285,3 +289,83 @@ int32_t launch_sets_arrays(sbo_ctx* ctx, const double* d_mu, const double* d_std
 }
 
 }  // namespace sbo
+
+// ---------------------------------------------------------------------------------------------------------------------
+// sbo_compute_sets_noalloc -- the CI + mask + argmax pass for callers that may not allocate (code under CUDA graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same kernel as sbo_compute_sets_device (sets_kernel<double, std inputs>); its grid
+// reduction scratch (one record per block + the last-block ticket) lives in a file-scope __device__ array instead of the
+// context's cudaMalloc'ed buffers, so the call needs no context and allocates nothing.  Every GPU that loads libsbo.so
+// holds the array (kNoAllocBlocks x 56 B + 256 B = 112.25 KiB) until the process exits.  All calls on a device share it:
+// calls that overlap on the GPU (two streams, two host threads) race on it -- serialise them.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace sbo {
+namespace {
+
+constexpr int kNoAllocBlocks = 2048;                       // per-block records the scratch holds
+constexpr long long kNoAllocMaxCells = 1LL << 27;           // stated capacity: 134 217 728 cells (2 x the 8192^2 grid of C4)
+struct NoAllocScratch {
+  unsigned int ticket;
+  unsigned int pad[63];                                     // the records start on their own 256-byte line
+  SetsResult partials[kNoAllocBlocks];
+};
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the device address is looked up once
+// per device, with that device current, and cached here.
+constexpr int kNoAllocMaxDevices = 64;
+NoAllocScratch* g_noalloc_ptr[kNoAllocMaxDevices] = {};
+
+int32_t noalloc_scratch(NoAllocScratch** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return cuda_fail(nullptr, e, "sbo_compute_sets_noalloc: cudaGetDevice");
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return fail(nullptr, SBO_ERR_INVALID_ARG, "sbo_compute_sets_noalloc: device ordinal beyond 63");
+  NoAllocScratch* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_noalloc_scratch);      // set-up, once per device (idempotent: a race stores the same value)
+    if (e != cudaSuccess || !sym) return cuda_fail(nullptr, e, "sbo_compute_sets_noalloc: cudaGetSymbolAddress(scratch)");
+    p = static_cast<NoAllocScratch*>(sym);
+    __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return SBO_OK;
+}
+
+}  // namespace
+}  // namespace sbo
+
+extern "C" int32_t sbo_compute_sets_noalloc(const double* mu_dev, const double* std_dev, int64_t m, double beta, double f_min,
+                                            uint8_t* mask_dev, sbo_sets_record* result_dev, void* cuda_stream) {
+  using namespace sbo;
+  static_assert(sizeof(sbo_sets_record) == sizeof(SetsResult), "sbo_sets_record mirrors the device record");
+  if (m < 0 || !result_dev || (m > 0 && (!mu_dev || !std_dev || !mask_dev)))
+    return fail(nullptr, SBO_ERR_INVALID_ARG, "sbo_compute_sets_noalloc: null pointer or m < 0");
+  if (!(std::isfinite(beta) && std::isfinite(f_min))) return fail(nullptr, SBO_ERR_INVALID_ARG, "sbo_compute_sets_noalloc: beta / f_min not finite");
+  if (m > kNoAllocMaxCells)
+    return fail(nullptr, SBO_ERR_CAPACITY, "sbo_compute_sets_noalloc: m = " + std::to_string((long long)m) + " exceeds the fixed capacity of " +
+                                               std::to_string(kNoAllocMaxCells) + " cells (use sbo_compute_sets_device)");
+  NoAllocScratch* scratch = nullptr;
+  SBO_TRY(noalloc_scratch(&scratch));
+  cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+  // the array keeps the last call's contents: the ticket must start at zero (a call that was aborted mid-way leaves it
+  // anywhere); the per-block records are all overwritten before they are read
+  cudaError_t e = cudaMemsetAsync(&scratch->ticket, 0, sizeof(unsigned int), stream);
+  if (e != cudaSuccess) return cuda_fail(nullptr, e, "sbo_compute_sets_noalloc: cudaMemsetAsync(ticket)");
+  auto aligned = [](const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
+  const bool vec = aligned(mu_dev, 16) && aligned(std_dev, 16) && aligned(mask_dev, 4);
+  const int64_t work = vec ? (m + 3) / 4 : m;
+  int64_t blocks = (work + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll);
+  blocks = std::max<int64_t>(1, std::min<int64_t>(blocks, kNoAllocBlocks));
+  SetsResult* result = reinterpret_cast<SetsResult*>(result_dev);
+  if (vec)
+    sets_kernel<double, true, true><<<(unsigned)blocks, kThreads, 0, stream>>>(mu_dev, std_dev, m, 0, beta, f_min, 0.0, 0.0, mask_dev, nullptr,
+                                                                                nullptr, scratch->partials, result, &scratch->ticket);
+  else
+    sets_kernel<double, true, false><<<(unsigned)blocks, kThreads, 0, stream>>>(mu_dev, std_dev, m, 0, beta, f_min, 0.0, 0.0, mask_dev, nullptr,
+                                                                                 nullptr, scratch->partials, result, &scratch->ticket);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return cuda_fail(nullptr, e, "sbo_compute_sets_noalloc: sets_kernel launch");
+  return SBO_OK;   // asynchronous: the record and the mask are complete when `cuda_stream` reaches this point
+}
