@@ -146,8 +146,13 @@ typedef enum {
   SBO_OPT_DRIFT_CHECK_EVERY = 11,/* every this many incremental steps, re-evaluate SBO_OPT_DRIFT_ROWS sample blocks exactly
                                     and refresh when the deviation exceeds tol / 4 (default: 16 in SBO_FP32, 256 in
                                     SBO_FP64, where a check costs several incremental steps; 0 = never)                     */
-  SBO_OPT_DRIFT_ROWS = 12        /* sample blocks per check, spread over the shard (default 2; a block is one grid row,
+  SBO_OPT_DRIFT_ROWS = 12,       /* sample blocks per check, spread over the shard (default 2; a block is one grid row,
                                     eight consecutive rows in SBO_FP64: the DMMA kernel's tile is a 16 x 8 patch of cells)  */
+  SBO_OPT_DIST_FIT = 13          /* the full fit of a context that has a communicator (sbo_comm_init) or belongs to a group
+                                    is SHARED between the ranks: block columns of the Cholesky and of L^-1 dealt in snake
+                                    order, one panel broadcast per step, one all-gather of L^-1 at the end -- bit-identical
+                                    to the replicated fit.  2 (default): from 8192 observations on; 1: always; 0: never.
+                                    Every rank must hold the same value and call sbo_set_observations with the same data  */
 } sbo_option;
 int32_t sbo_set_option(sbo_ctx* ctx, int32_t option, int32_t value);
 int32_t sbo_get_option(const sbo_ctx* ctx, int32_t option, int32_t* value);
@@ -172,6 +177,10 @@ int32_t sbo_set_observations(sbo_ctx* ctx, const double* xy, const double* y, in
  * L^-1 = [-L22^-1 L21 L11^-1, L22^-1], alpha refreshed.  O(k n^2). */
 int32_t sbo_append_observations(sbo_ctx* ctx, const double* xy, const double* y, int32_t k);
 int32_t sbo_num_observations(const sbo_ctx* ctx);
+/* Device time of the last full fit (ms, events on the context's stream) and how many ranks shared it (0: this
+ * context factorised alone; see SBO_OPT_DIST_FIT).  replaces: nothing (the reference only logs the service
+ * round trip, :589, :598-604). */
+int32_t sbo_fit_info(const sbo_ctx* ctx, float* ms, int32_t* shared_ranks);
 /* Internal ordering.  sbo_set_observations stores the observations sorted spatially (bands of 2
  * length-scales in y, by x inside a band): the GP is invariant under the permutation, the sorted
  * order makes the cross-covariance tiles of a cell tile block-sparse and keeps the tensor-core

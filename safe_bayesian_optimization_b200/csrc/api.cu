@@ -40,7 +40,7 @@ void free_all(sbo_ctx* c) {
   void* dev[] = {c->d_xy, c->d_r, c->d_A, c->d_Linv, c->d_Dinv, c->d_alpha, c->d_w, c->d_small, c->d_info,
                  c->d_planes, c->d_alpha_f32, c->d_obs_f32, c->d_chunk_bbox, c->d_exec_cols, c->d_fr_img, c->d_fr_lut, c->d_cp_idx, c->d_cp_counts, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
                  c->d_partials, c->d_result, c->d_ticket, c->d_frontier, c->d_sel_keys, c->d_sel_width, c->d_sel_out,
-                 c->d_gather, c->d_drift_mu, c->d_drift_s2, c->d_drift_out};
+                 c->d_gather, c->d_drift_mu, c->d_drift_s2, c->d_drift_out, c->d_fit_stage, c->d_fit_send, c->d_fit_recv};
   for (void* p : dev)
     if (p) cudaFree(p);
   if (c->h_result) cudaFreeHost(c->h_result);
@@ -49,6 +49,10 @@ void free_all(sbo_ctx* c) {
     if (e) cudaEventDestroy(e);
   for (auto& e : c->ev_factor) cudaEventDestroy(e);
   c->ev_factor.clear();
+  for (auto& e : c->ev_fit)
+    if (e) cudaEventDestroy(e);
+  for (cudaStream_t* q : {&c->fit_hi, &c->fit_lo, &c->fit_cm})
+    if (*q) cudaStreamDestroy(*q);
   if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
 }
@@ -444,6 +448,7 @@ static int* option_slot(sbo_ctx* c, int32_t option) {
     case SBO_OPT_REFRESH_EVERY: return &c->opt.refresh_every;
     case SBO_OPT_DRIFT_CHECK_EVERY: return &c->opt.drift_check_every;
     case SBO_OPT_DRIFT_ROWS: return &c->opt.drift_rows;
+    case SBO_OPT_DIST_FIT: return &c->opt.dist_fit;
     default: return nullptr;
   }
 }
@@ -492,6 +497,13 @@ int32_t sbo_tc_executed_flops(sbo_ctx* ctx, double* flops) {
   SBO_CUDA(ctx, cudaMemcpyAsync(&cols, ctx->d_exec_cols, sizeof(cols), cudaMemcpyDeviceToHost, ctx->stream));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   *flops = 2.0 * 256.0 * 16.0 * (double)cols;   // every counted MMA is M 256 (CTA pair) x N x K 16
+  return SBO_OK;
+}
+
+int32_t sbo_fit_info(const sbo_ctx* ctx, float* ms, int32_t* shared_ranks) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (ms) *ms = ctx->fit_ms;
+  if (shared_ranks) *shared_ranks = ctx->fit_dist_used;
   return SBO_OK;
 }
 

@@ -23,6 +23,7 @@ typedef struct { char internal[128]; } NcclUniqueId;
 typedef int (*GetUniqueIdFn)(NcclUniqueId*);
 typedef int (*CommInitRankFn)(void**, int, NcclUniqueId, int);
 typedef int (*AllGatherFn)(const void*, void*, size_t, int, void*, cudaStream_t);
+typedef int (*BroadcastFn)(const void*, void*, size_t, int, int, void*, cudaStream_t);
 typedef int (*CommDestroyFn)(void*);
 typedef const char* (*GetErrorStringFn)(int);
 
@@ -31,6 +32,7 @@ struct NcclApi {
   GetUniqueIdFn get_unique_id = nullptr;
   CommInitRankFn comm_init_rank = nullptr;
   AllGatherFn all_gather = nullptr;
+  BroadcastFn broadcast = nullptr;
   CommDestroyFn comm_destroy = nullptr;
   GetErrorStringFn get_error_string = nullptr;
   std::string err;
@@ -54,9 +56,10 @@ NcclApi& nccl() {
   api.get_unique_id = (GetUniqueIdFn)dlsym(api.handle, "ncclGetUniqueId");
   api.comm_init_rank = (CommInitRankFn)dlsym(api.handle, "ncclCommInitRank");
   api.all_gather = (AllGatherFn)dlsym(api.handle, "ncclAllGather");
+  api.broadcast = (BroadcastFn)dlsym(api.handle, "ncclBroadcast");
   api.comm_destroy = (CommDestroyFn)dlsym(api.handle, "ncclCommDestroy");
   api.get_error_string = (GetErrorStringFn)dlsym(api.handle, "ncclGetErrorString");
-  if (!api.get_unique_id || !api.comm_init_rank || !api.all_gather || !api.comm_destroy) {
+  if (!api.get_unique_id || !api.comm_init_rank || !api.all_gather || !api.broadcast || !api.comm_destroy) {
     api.err = "libnccl is missing a required symbol";
     api.handle = nullptr;
   }
@@ -89,6 +92,28 @@ int32_t comm_gather_reduce(sbo_ctx* ctx) {
   ctx->launches++;  // NCCL's kernel
   fold_records_kernel<<<1, 32, 0, ctx->stream>>>(ctx->d_gather, ctx->world, ctx->d_result);
   SBO_LAUNCH_CHECK(ctx, "fold_records_kernel");
+  return SBO_OK;
+}
+
+// The two collectives of the shared fit (factor_dist.cuh): panel k from its owner to every rank, and the block columns of
+// L^-1 from every rank to every rank.  Byte counts (ncclInt8), in stream order like every NCCL call.
+int32_t comm_broadcast(sbo_ctx* ctx, void* buf, size_t bytes, int root, cudaStream_t stream) {
+  NcclApi& api = nccl();
+  if (!ctx->nccl_comm || !api.handle) return fail(ctx, SBO_ERR_COMM, "comm_broadcast: no communicator");
+  const int rc = api.broadcast(buf, buf, bytes, /*ncclInt8*/ 0, root, ctx->nccl_comm, stream);
+  if (rc != 0)
+    return fail(ctx, SBO_ERR_COMM, std::string("ncclBroadcast: ") + (api.get_error_string ? api.get_error_string(rc) : "?"));
+  ctx->launches++;
+  return SBO_OK;
+}
+
+int32_t comm_all_gather(sbo_ctx* ctx, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t stream) {
+  NcclApi& api = nccl();
+  if (!ctx->nccl_comm || !api.handle) return fail(ctx, SBO_ERR_COMM, "comm_all_gather: no communicator");
+  const int rc = api.all_gather(send, recv, bytes_per_rank, /*ncclInt8*/ 0, ctx->nccl_comm, stream);
+  if (rc != 0)
+    return fail(ctx, SBO_ERR_COMM, std::string("ncclAllGather: ") + (api.get_error_string ? api.get_error_string(rc) : "?"));
+  ctx->launches++;
   return SBO_OK;
 }
 

@@ -34,7 +34,10 @@ struct Options {
   int refresh_every = -1;       // -1: by precision (256 fp32, never fp64)
   int drift_check_every = -1;   // -1: by precision (16 fp32, 256 fp64)
   int drift_rows = 2;           // sample blocks per check (a block = 1 grid row; 8 rows for the DMMA kernel's 16 x 8 cell patches)
+  int dist_fit = 2;             // fit shared between the ranks / group members: 0 never, 1 always, 2 from 8192 observations on
 };
+
+struct FitPeers;   // factor.cu: rendezvous of the members of a same-process group during a shared fit
 
 enum class PosteriorSource : int { kNone = 0, kStep = 1, kHostArrays = 2 };
 
@@ -148,6 +151,18 @@ struct sbo_ctx {
   unsigned int* d_cp_counts = nullptr;
   long long cp_cap = 0;
 
+  // shared fit (factor_dist.cuh): block columns of the Cholesky / L^-1 work split over the ranks
+  cudaStream_t fit_hi = nullptr, fit_lo = nullptr, fit_cm = nullptr;   // Cholesky chain, rows of L^-1, exchange
+  double* d_fit_stage = nullptr;   // one panel message: header + D_k + L panel k (NCCL transport)
+  double* d_fit_send = nullptr;    // my block columns of L^-1, packed (NCCL transport)
+  double* d_fit_recv = nullptr;    // [world] slots of packed block columns
+  size_t fit_stage_cap = 0, fit_send_cap = 0, fit_recv_cap = 0;   // doubles
+  sbo::FitPeers* fit_peers = nullptr;   // same-process group (not owned); null: NCCL transport when nccl_comm is set
+  int fit_rank = 0;
+  int fit_dist_used = 0;           // the last full fit was shared between this many ranks (0: replicated)
+  float fit_ms = 0.f;              // device time of the last full fit (events on the context's stream)
+  cudaEvent_t ev_fit[2]{};
+
   // communicator
   void* nccl_comm = nullptr;
   int rank = 0, world = 1;
@@ -233,6 +248,13 @@ int32_t compact_cells(sbo_ctx* ctx, int mode, int32_t* idx_host, int64_t cap, in
 
 // comm.cu
 int32_t comm_gather_reduce(sbo_ctx* ctx);          // d_result -> d_result (global), over all ranks
+int32_t comm_broadcast(sbo_ctx* ctx, void* buf, size_t bytes, int root, cudaStream_t stream);              // in place
+int32_t comm_all_gather(sbo_ctx* ctx, const void* send, void* recv, size_t bytes_per_rank, cudaStream_t stream);
+
+// factor.cu: same-process members of a shared fit (group.cu creates one per group and attaches it to the members)
+FitPeers* fit_peers_create(int world);
+void fit_peers_destroy(FitPeers* p);
+void fit_peers_attach(FitPeers* p, sbo_ctx* ctx, int rank);
 
 // ---- device helpers ---------------------------------------------------------
 

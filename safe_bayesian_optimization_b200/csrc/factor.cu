@@ -17,7 +17,12 @@
 // with B (the running right-hand side, initially I) stored in place in L^-1.
 #include <cuda_fp16.h>
 
+#include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <condition_variable>
+#include <mutex>
+#include <new>
 
 #include "common.cuh"
 
@@ -837,7 +842,33 @@ int32_t refresh_planes(sbo_ctx* ctx, int row_begin, int row_end, cudaStream_t st
   return SBO_OK;
 }
 
+#include "factor_dist.cuh"
+
+static int32_t factor_full_timed(sbo_ctx* ctx);
+
 int32_t factor_full(sbo_ctx* ctx) {
+  // device time of the fit for sbo_fit_info (events on the context's stream; the side streams join it before the end)
+  if (!ctx->ev_fit[0]) {
+    SBO_CUDA(ctx, cudaEventCreate(&ctx->ev_fit[0]));
+    SBO_CUDA(ctx, cudaEventCreate(&ctx->ev_fit[1]));
+  }
+  ctx->fit_ms = 0.f;
+  SBO_CUDA(ctx, cudaEventRecord(ctx->ev_fit[0], ctx->stream));
+  const int32_t st = factor_full_timed(ctx);
+  if (st == SBO_OK) {
+    SBO_CUDA(ctx, cudaEventRecord(ctx->ev_fit[1], ctx->stream));
+    SBO_CUDA(ctx, cudaEventSynchronize(ctx->ev_fit[1]));
+    SBO_CUDA(ctx, cudaEventElapsedTime(&ctx->fit_ms, ctx->ev_fit[0], ctx->ev_fit[1]));
+  }
+  return st;
+}
+
+static int32_t factor_full_timed(sbo_ctx* ctx) {
+  if (ctx->n > 0) {
+    int32_t st = SBO_OK;
+    if (factor_full_dist(ctx, &st)) return st;   // shared between the ranks / group members (factor_dist.cuh)
+  }
+  ctx->fit_dist_used = 0;
   const int n = ctx->n, ld = ctx->n_cap;
   const int np = (n + NB - 1) / NB * NB;
   const int nblk = np / NB;

@@ -21,6 +21,7 @@ struct sbo_group {
   double x0 = 0, y0 = 0, rx = 0, ry = 0;
   int W = 0, H = 0;
   std::vector<double> xy, y;          // the observations in arrival order (band planning)
+  sbo::FitPeers* peers = nullptr;     // rendezvous of the members' host threads during a shared fit (factor_dist.cuh)
   std::string err;
 };
 
@@ -92,6 +93,24 @@ int32_t sbo_group_create(const sbo_config* cfg, const int32_t* devices, int32_t 
     }
     g->ctx.push_back(ctx);
   }
+  if (n_devices > 1) {   // the full fit is shared between the members: peer copies between their buffers
+    g->peers = sbo::fit_peers_create(n_devices);
+    if (!g->peers) {
+      for (sbo_ctx* m : g->ctx) sbo_destroy(m);
+      delete g;
+      return gfail(nullptr, SBO_ERR_CUDA, "sbo_group_create: out of host memory");
+    }
+    for (int i = 0; i < n_devices; ++i) {
+      sbo::fit_peers_attach(g->peers, g->ctx[i], i);
+      cudaSetDevice(devices[i]);
+      for (int j = 0; j < n_devices; ++j) {
+        int can = 0;
+        if (devices[j] == devices[i] || cudaDeviceCanAccessPeer(&can, devices[i], devices[j]) != cudaSuccess || !can) continue;
+        cudaDeviceEnablePeerAccess(devices[j], 0);   // (already enabled: harmless error, cleared below)
+      }
+      cudaGetLastError();
+    }
+  }
   *out = g;
   return SBO_OK;
 }
@@ -99,6 +118,7 @@ int32_t sbo_group_create(const sbo_config* cfg, const int32_t* devices, int32_t 
 int32_t sbo_group_destroy(sbo_group* g) {
   if (!g) return SBO_ERR_INVALID_ARG;
   for (sbo_ctx* m : g->ctx) sbo_destroy(m);
+  if (g->peers) sbo::fit_peers_destroy(g->peers);
   delete g;
   return SBO_OK;
 }

@@ -179,6 +179,12 @@ class SboContext:
     def n_obs(self) -> int:
         return int(self.lib.sbo_num_observations(self._h))
 
+    def fit_info(self):
+        """(device ms of the last full fit, ranks that shared it; 0 = this context alone) -- sbo_fit_info."""
+        ms, w = C.c_float(0.0), C.c_int32(0)
+        self._check(self.lib.sbo_fit_info(self._h, C.byref(ms), C.byref(w)))
+        return float(ms.value), int(w.value)
+
     def order(self):
         """order[pos] = caller index of the observation stored at internal position pos."""
         out = np.zeros(self.n_obs, dtype=np.int32)
@@ -388,6 +394,18 @@ class SboGroup:
     @property
     def n_obs(self):
         return int(self.lib.sbo_group_num_observations(self._h))
+
+    def member_factor(self, i):
+        """(L^-1, alpha, (fit ms, ranks that shared the fit)) of member i -- for checking the shared fit."""
+        h = C.c_void_p(self.lib.sbo_group_member(self._h, int(i)))
+        n = self.n_obs
+        linv, alpha = np.zeros((n, n)), np.zeros(n)
+        ms, w = C.c_float(0.0), C.c_int32(0)
+        for st in (self.lib.sbo_copy_linv(h, _dptr(linv)), self.lib.sbo_copy_alpha(h, _dptr(alpha)),
+                   self.lib.sbo_fit_info(h, C.byref(ms), C.byref(w))):
+            if st != L.SBO_OK:
+                raise L.SboError(st, self.lib.sbo_last_error(h).decode())
+        return linv, alpha, (float(ms.value), int(w.value))
 
     def bands(self):
         cuts = np.zeros(self.size + 1, dtype=np.int32)

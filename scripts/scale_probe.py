@@ -7,6 +7,7 @@ import safe_bayesian_optimization_b200 as pkg
 from safe_bayesian_optimization_b200 import synthetic as S
 
 ns = [int(x) for x in (sys.argv[1].split(",") if len(sys.argv) > 1 else "1024,4096,8192,16384".split(","))]
+opts = [kv.split("=") for kv in (sys.argv[2].split(",") if len(sys.argv) > 2 and sys.argv[2] else [])]   # e.g. tc_skip=0,tc_strip=0
 name = {1024: "C2", 4096: "C3", 8192: "C5", 16384: "C4"}
 for n in ns:
     p = S.make_problem(name.get(n, "C2"), n=n)
@@ -16,6 +17,8 @@ for n in ns:
     k = 16
     with pkg.SboContext(sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean,
                         precision="fp32", max_obs=n + k, max_cells=p.m) as ctx:
+        for k_, v_ in opts:
+            ctx.set_option(k_, int(v_))
         ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
         ctx.set_observations(p.xy, p.y)
         t0 = time.perf_counter(); ctx.set_observations(p.xy, p.y); t_fit = time.perf_counter() - t0

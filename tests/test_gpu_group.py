@@ -51,6 +51,51 @@ def test_group_equals_single_context(pkg, precision, members):
             assert np.array_equal(mi, m1) and ri.safe_count == r1.safe_count and ri.n_obs == p.n + 1 and g.n_obs == p.n + 1
 
 
+@pytest.mark.parametrize("precision,members,n", [("fp64", 2, 700), ("fp32", 3, 1100), ("fp32", 8, 1500), ("fp64", 4, 129)])
+def test_shared_fit_bit_identical(pkg, precision, members, n):
+    """SBO_OPT_DIST_FIT: block columns of the Cholesky / L^-1 work dealt to the members (snake order), panel exchange per
+    step, all-gather of L^-1 at the end -- every member must end with the replicated fit's L^-1 and alpha, bit for bit."""
+    p = S.make_problem("C3", n=n, W=256, H=24)
+    with make_ctx(pkg, p, precision=precision, max_obs=p.n + 4) as ctx:
+        ctx.set_observations(p.xy, p.y)
+        linv1, alpha1 = ctx.linv(), ctx.alpha()
+        assert ctx.fit_info()[1] == 0
+    with pkg.SboGroup(_devices(members), sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var,
+                      prior_mean=p.prior_mean, precision=precision, max_obs=p.n + 4, max_cells=p.m) as g:
+        g.set_option("dist_fit", 1)
+        g.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+        for rep in range(2):                                 # twice: the rendezvous and the events are reused
+            g.set_observations(p.xy, p.y)
+            for i in range(members):
+                linv, alpha, (ms, shared) = g.member_factor(i)
+                assert shared == members and ms > 0
+                assert np.array_equal(linv, linv1), f"member {i}: L^-1 differs from the replicated fit"
+                assert np.array_equal(alpha, alpha1)
+        g.set_option("dist_fit", 0)
+        g.set_observations(p.xy, p.y)
+        assert g.member_factor(members - 1)[2][1] == 0 and np.array_equal(g.member_factor(0)[0], linv1)
+
+
+def test_shared_fit_not_positive_definite(pkg):
+    """A failing block in the middle of a shared fit: every member reports the same first failing row and goes back to the
+    observations it held before."""
+    p = S.make_problem("C3", n=600, W=256, H=12)
+    p.xy = p.xy * 12.0; p.rx *= 12.0; p.ry *= 12.0
+    with pkg.SboGroup(_devices(3), sigma_f=p.sigma_f, length_scale=p.length, noise_var=1e-20, prior_mean=p.prior_mean,
+                      precision="fp64", max_obs=p.n + 4, max_cells=p.m) as g:
+        g.set_option("dist_fit", 1)
+        g.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+        g.set_observations(p.xy, p.y)
+        a, mask_a = g.step(p.beta, p.f_min)
+        linv_a = g.member_factor(1)[0]
+        with pytest.raises(pkg.SboError) as e:
+            g.set_observations(np.concatenate([p.xy, p.xy[300:302]]), np.concatenate([p.y, p.y[300:302]]))
+        assert e.value.status == -4 and g.n_obs == p.n
+        assert np.array_equal(g.member_factor(2)[0], linv_a)
+        b, mask_b = g.step(p.beta, p.f_min)
+        assert np.array_equal(mask_a, mask_b) and a.argmax_ucb == b.argmax_ucb
+
+
 def test_group_failed_fit_keeps_last_good_state(pkg):
     p = S.make_problem("C3", n=280, W=256, H=12)
     p.xy = p.xy * 12.0; p.rx *= 12.0; p.ry *= 12.0
