@@ -148,11 +148,14 @@ typedef enum {
                                     SBO_FP64, where a check costs several incremental steps; 0 = never)                     */
   SBO_OPT_DRIFT_ROWS = 12,       /* sample blocks per check, spread over the shard (default 2; a block is one grid row,
                                     eight consecutive rows in SBO_FP64: the DMMA kernel's tile is a 16 x 8 patch of cells)  */
-  SBO_OPT_DIST_FIT = 13          /* the full fit of a context that has a communicator (sbo_comm_init) or belongs to a group
+  SBO_OPT_DIST_FIT = 13,         /* the full fit of a context that has a communicator (sbo_comm_init) or belongs to a group
                                     is SHARED between the ranks: block columns of the Cholesky and of L^-1 dealt in snake
                                     order, one panel broadcast per step, one all-gather of L^-1 at the end -- bit-identical
                                     to the replicated fit.  2 (default): from 8192 observations on; 1: always; 0: never.
                                     Every rank must hold the same value and call sbo_set_observations with the same data  */
+  SBO_OPT_TC_PHASES = 14         /* full refresh of the block-sparse walk as this many launches over consecutive row-block
+                                    pair ranges (running row sums carried between them, bit-identical): keeps the rows of
+                                    L^-1 in flight inside the L2.  0 (default): by size (1 below 8192 observations)         */
 } sbo_option;
 int32_t sbo_set_option(sbo_ctx* ctx, int32_t option, int32_t value);
 int32_t sbo_get_option(const sbo_ctx* ctx, int32_t option, int32_t* value);

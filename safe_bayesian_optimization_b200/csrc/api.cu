@@ -216,7 +216,9 @@ int32_t run_step(sbo_ctx* ctx, double beta, double f_min, bool incremental, int*
   }
   if (incremental) {
     ++ctx->inc_steps;
-    if (ctx->opt.drift_check_every > 0 && ctx->inc_steps % ctx->opt.drift_check_every == 0) SBO_TRY(drift_check(ctx));
+    int check_every = ctx->opt.drift_check_every;
+    if (check_every < 0) check_every = ctx->cfg.precision == SBO_FP64 ? 256 : 16;   // the documented defaults (sbo.h)
+    if (check_every > 0 && ctx->inc_steps % check_every == 0) SBO_TRY(drift_check(ctx));
   } else {
     ctx->inc_steps = 0;
     ctx->force_refresh = false;
@@ -449,6 +451,7 @@ static int* option_slot(sbo_ctx* c, int32_t option) {
     case SBO_OPT_DRIFT_CHECK_EVERY: return &c->opt.drift_check_every;
     case SBO_OPT_DRIFT_ROWS: return &c->opt.drift_rows;
     case SBO_OPT_DIST_FIT: return &c->opt.dist_fit;
+    case SBO_OPT_TC_PHASES: return &c->opt.tc_phases;
     default: return nullptr;
   }
 }

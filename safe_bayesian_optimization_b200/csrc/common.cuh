@@ -34,6 +34,7 @@ struct Options {
   int refresh_every = -1;       // -1: by precision (256 fp32, never fp64)
   int drift_check_every = -1;   // -1: by precision (16 fp32, 256 fp64)
   int drift_rows = 2;           // sample blocks per check (a block = 1 grid row; 8 rows for the DMMA kernel's 16 x 8 cell patches)
+  int tc_phases = 0;            // full refresh in this many launches over consecutive row-block pair ranges (0: by size)
   int dist_fit = 2;             // fit shared between the ranks / group members: 0 never, 1 always, 2 from 8192 observations on
 };
 

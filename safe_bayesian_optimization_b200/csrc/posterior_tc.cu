@@ -107,7 +107,7 @@ struct TcParams {
   float ring_bits;         // graded split depth: visits whose K* entries are all < 2^-ring_bits sigma_f^2 issue hi.hi only (>= skip_bits: none)
   int strip_tiles;         // strip-major tile order: tiles per strip (even; 0 = raster), see TileMap
   int pi_lo, pi_hi;        // pair kernel: row-block pairs [pi_lo, pi_hi) of this launch
-  int rs_mode;             // pair kernel: 0 whole job; 1 partial (store the running row sums in rs_part, no sigma^2 / mu); 2 resume from rs_part
+  int rs_mode;             // pair kernel: 0 whole job; bit 0: partial (store the running row sums in rs_part, no sigma^2 / mu); bit 1: resume from rs_part (3: a middle phase)
   float2* rs_part;         // [m_local] double-word fp32 running sums of a partial launch
   unsigned long long* exec_cols;   // pair kernel: += sum of N over the issued MMAs (M 256, K 16 each); executed flops = 2 * 256 * 16 * that
   long long* dbg_clk;      // SBO_TC_CLK=1: per-role cycle counters of cluster 0 (timing forensics)
@@ -1136,6 +1136,19 @@ static void tc_fill_params(sbo_ctx* ctx, TcParams& p, int j_lo, int j_hi, bool a
   p.dbg_clk = nullptr;
 }
 
+// Number of phases of the full refresh (see launch_posterior_tc).  SBO_OPT_TC_PHASES: 0 = by size, k >= 1 = exactly k.
+// By size: the kept part of the planes a patch of concurrently processed tiles walks, ~1.4 x kept_fraction x n^2 / 2 entries
+// of 4 bytes (hi + lo), in pieces of at most ~24 MB; nothing to gain while the whole of it sits in the L2 (n < 8192).
+static int tc_phase_count(sbo_ctx* ctx, int npairs) {
+  int f = ctx->opt.tc_phases;
+  if (f <= 0) {
+    if (ctx->n < 8192) return 1;
+    const double bytes = 1.4 * ctx->tc_kept_frac * 0.5 * (double)ctx->n * ctx->n * 4.0;
+    f = (int)std::ceil(bytes / (24.0 * 1048576.0));
+  }
+  return std::max(1, std::min(f, npairs));
+}
+
 static cudaError_t tc_launch_pair(sbo_ctx* ctx, const TcParams& p, cudaStream_t stream, long long clusters) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(2 * clusters));
@@ -1406,9 +1419,40 @@ int32_t launch_posterior_tc(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
     if (resume && !pair) return fail(ctx, SBO_ERR_STATE, "eager first pairs without the pair kernel");
     if (pair && !resume && ctx->d_exec_cols)   // executed-work counter of this launch (a resumed launch adds to the eager part's count)
       SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_exec_cols, 0, sizeof(unsigned long long), ctx->stream));
-    const cudaError_t e = pair     ? tc_launch_pair(ctx, p, ctx->stream, pairs)
-                          : p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, true>, tmap, p)
-                                   : cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, false>, tmap, p);
+    // Phased walk (large n, block-sparse plan): the row-block pairs are contracted in `phases` launches over consecutive
+    // pair ranges, the running row sums travelling through rs_part (8 B per cell and phase) exactly as between the eager
+    // first pairs and their resuming launch -- same additions in the same order, bit-identical.  Why: the CTA pairs of ONE
+    // launch drift apart along their tiles' 32-pair walks, so together they keep re-reading the whole kept part of the
+    // 1 GiB planes (~70-100 MB per patch of tiles at C4) through a 126 MB L2: 58 % hit rate, 1.6 TB/s of DRAM reads that
+    // the power-limited tensor pipe pays for in clock.  Inside a phase the B rows in flight are 1 / phases of that.
+    int phases = 1;
+    if (pair && !resume && p.skip) phases = tc_phase_count(ctx, p.pi_hi);
+    cudaError_t e = cudaSuccess;
+    if (phases > 1) {
+      if (ctx->rs_cap < ctx->m_local) {
+        if (ctx->d_rs_part) cudaFree(ctx->d_rs_part);
+        ctx->d_rs_part = nullptr;
+        ctx->rs_cap = 0;
+        SBO_CUDA(ctx, cudaMalloc(&ctx->d_rs_part, sizeof(float2) * (size_t)ctx->m_local));
+        ctx->rs_cap = ctx->m_local;
+      }
+      p.rs_part = reinterpret_cast<float2*>(ctx->d_rs_part);
+      const int np_all = p.pi_hi;
+      for (int f = 0; f < phases && e == cudaSuccess; ++f) {
+        // equal pair counts: beyond the first few row blocks every row of L^-1 a tile walks has the same kept width (the
+        // chunks within reach of the tile), so the bytes in flight go with the number of rows
+        p.pi_lo = (int)((long long)np_all * f / phases);
+        p.pi_hi = (int)((long long)np_all * (f + 1) / phases);
+        if (p.pi_hi <= p.pi_lo) continue;
+        p.rs_mode = (p.pi_lo > 0 ? 2 : 0) | (p.pi_hi < np_all ? 1 : 0);
+        e = tc_launch_pair(ctx, p, ctx->stream, pairs);
+        if (e == cudaSuccess && f + 1 < phases) ++ctx->launches;
+      }
+    } else {
+      e = pair     ? tc_launch_pair(ctx, p, ctx->stream, pairs)
+          : p.skip ? cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, true>, tmap, p)
+                   : cudaLaunchKernelEx(&cfg, posterior_tc_kernel<2, false>, tmap, p);
+    }
     if (e != cudaSuccess) return cuda_fail(ctx, e, "posterior_tc_kernel<2> (cluster launch)");
   }
   SBO_LAUNCH_CHECK(ctx, "posterior_tc_kernel");

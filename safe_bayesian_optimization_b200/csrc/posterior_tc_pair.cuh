@@ -230,7 +230,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
       const int e_col = e_col0 + r;
       const bool e_live = tile < ntiles && e_col < p.W;
       const long long e_lc = (long long)e_lrow * p.W + e_col;
-      if (p.rs_mode == 2 && e_live) {  // resume: pairs < pi_lo were contracted by an earlier launch (same sums, same order)
+      if ((p.rs_mode & 2) && e_live) {  // resume: pairs < pi_lo were contracted by an earlier launch (same sums, same order)
         const float2 v0 = p.rs_part[e_lc];
         rs_hi = v0.x; rs_lo = v0.y;
       }
@@ -279,7 +279,7 @@ posterior_tc_pair_kernel(const __grid_constant__ CUtensorMap tmap, TcParams p) {
         }
       }
       if (e_live) {
-        if (p.rs_mode == 1) p.rs_part[e_lc] = make_float2(rs_hi, rs_lo);  // partial launch: the running sum, nothing else
+        if (p.rs_mode & 1) p.rs_part[e_lc] = make_float2(rs_hi, rs_lo);  // partial launch: the running sum, nothing else
         else p.s2[e_lc] = (float)((double)p.sf2 - ((double)rs_hi + (double)rs_lo) * p.v_unscale2);
       }
     }

@@ -388,6 +388,29 @@ def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, spread, n
     assert np.abs(out["1"][1] - out["0"][1]).max() <= 1e-6
 
 
+@pytest.mark.parametrize("n,phases", [(2100, 2), (2100, 5), (1300, 3)])
+def test_phased_refresh_bit_identical(pkg, n, phases):
+    """SBO_OPT_TC_PHASES: the full refresh of the block-sparse walk as several launches over consecutive row-block pair
+    ranges, the running row sums carried in scratch between them -- same additions in the same order, so mu, sigma^2 and
+    the mask must equal the one-launch result bit for bit (odd pair counts, more phases than fit evenly)."""
+    p = S.make_problem("C3", n=n, W=384, H=7)
+    p.xy = p.xy * 8.0
+    p.rx, p.ry = p.rx * 8.0, p.ry * 8.0 * 9.0
+    out = {}
+    for f in (1, phases):
+        with make_ctx(pkg, p, kernel="tcgen05", options={"tc_phases": f, "tc_eager": 0}) as ctx:
+            ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+            ctx.set_observations(p.xy, p.y)
+            assert ctx.tc_plan()[1], "the block-sparse walk must be planned for this test"
+            l0 = ctx.launch_count
+            res, mask = ctx.step(p.beta, p.f_min)
+            out[f] = (ctx.mu(), ctx.sigma2(), mask, res.safe_count, ctx.launch_count - l0, ctx.tc_executed_flops())
+    assert out[phases][4] == out[1][4] + phases - 1, "one launch per phase"
+    assert out[phases][5] == out[1][5], "same executed tensor work"
+    assert np.array_equal(out[1][0], out[phases][0]) and np.array_equal(out[1][1], out[phases][1])
+    assert np.array_equal(out[1][2], out[phases][2]) and out[1][3] == out[phases][3]
+
+
 def test_full_size_c2_properties(pkg):
     """BASELINE config C2 at full size (1024 obs x 1M cells): size-independent properties."""
     p = S.make_problem("C2")
