@@ -80,8 +80,9 @@ def workload_config(name, p, world):
     return {"workload": f"{name}: {p.n} observations x {p.m} cells ({p.W}x{p.H} grid), RBF l={p.length} sigma_f={p.sigma_f} "
                         f"noise_var={p.noise_var}, {p.precision} mode",
             "l2": "flushed between timed steps (256 MiB write, outside the events); the L^-1 planes alone exceed the L2 at C4",
-            "parallelism": f"one grid cut into {world} band(s) of grid rows of equal estimated work, one GPU each, "
-                           f"replicated L^-1 / alpha, one NCCL all-gather of 56-byte argmax records"}
+            "parallelism": f"one grid cut into {world} band(s) of grid rows of equal estimated work, one GPU each; L^-1 / alpha on "
+                           f"every rank (the fp64 fit itself shared between the ranks from 8192 observations on: one panel "
+                           f"broadcast per step, one all-gather of L^-1); one NCCL all-gather of 56-byte argmax records per step"}
 
 
 class ClockSampler:
@@ -513,6 +514,7 @@ def run_workload(h: Harness, name: str, steps: int, warmup: int, primary: bool, 
                     "algorithmic_speedup": flops_c * 3.0 / executed,
                     "algorithmic_speedup_note": "dense 3-product walk / executed: block sparsity of K* (chunks below 2^-bits are "
                                                 "skipped) and graded split depth (ring visits issue 1 product of 3)",
+                    "frac_of_nominal_dense_f16": executed / (ms_post * 1e-3) / 1e12 / 2250.0,
                     "cta_group": cg, "plan": plan}
     elif p.precision == "fp64":
         peak = 37.1

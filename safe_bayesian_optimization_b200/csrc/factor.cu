@@ -7,8 +7,10 @@
 // hyper-parameters config/lpsc.yaml:35-37).  Everything is hand-written: no cuBLAS/cuSOLVER.
 //
 // Layout: row-major, leading dimension n_cap.  Blocks are NB = 128 square.  All O(n^3) work is
-// in one fp64 tile routine (128x128 output tile, 256 threads, 8x8 register tile per thread,
-// K staged through shared memory 16 deep):
+// in one fp64 tile routine per regime: small fits (n <= 2944) 64x64 output tiles on the FMA pipe (256 threads,
+// 4x4 register tile per thread, K staged through shared memory 16 deep, four CTAs per 128-block); large fits
+// 128x128 tiles on DMMA with cp.async double buffering (factor_dmma.cuh) under the look-ahead schedule of
+// factor_dist.cuh, on one GPU or shared between several:
 //   panel k:  L_kk = chol(A_kk), D_k = L_kk^-1            (one CTA, shared memory)
 //             L_ik = A_ik D_k^T                 i > k      (tile NT)
 //             A_ij -= L_ik L_jk^T           i >= j > k     (tile NT, lower blocks only)
@@ -563,6 +565,8 @@ trtri_update_kernel(double* __restrict__ X, int ld, const double* __restrict__ A
   tile_store<true, TM>(X, ld, r0, c0, acc, -1.0);
 }
 
+#include "factor_dmma.cuh"
+
 // Zero the identity padding of L^-1 (rows/cols in [n, np)) so padded rows contribute nothing.
 __global__ void clear_pad_kernel(double* __restrict__ X, int ld, int n, int np) {
   const int i = n + blockIdx.x * blockDim.x + threadIdx.x;
@@ -816,6 +820,10 @@ int32_t compute_alpha(sbo_ctx* ctx, int n) {
 static int32_t ensure_factor_attr(sbo_ctx* ctx) {
   if (ctx->attr_factor) return SBO_OK;
   SBO_CUDA(ctx, cudaFuncSetAttribute(diag_chol_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDiagSmem));
+  SBO_CUDA(ctx, cudaFuncSetAttribute(panel_trsm_dm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDmSmem));
+  SBO_CUDA(ctx, cudaFuncSetAttribute(syrk_dm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDmSmem));
+  SBO_CUDA(ctx, cudaFuncSetAttribute(trtri_row_dm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDmSmem));
+  SBO_CUDA(ctx, cudaFuncSetAttribute(trtri_update_dm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDmSmem));
   ctx->attr_factor = true;
   return SBO_OK;
 }
@@ -891,18 +899,16 @@ static int32_t factor_full_timed(sbo_ctx* ctx) {
     build_K_kernel<<<g, b, 0, st>>>(ctx->d_xy, n, np, ld, sf2, inv2l2, ctx->cfg.noise_var, ctx->d_A);
     SBO_LAUNCH_CHECK(ctx, "build_K_kernel");
   }
+  // Small n only (a launch has at most 2 x SMs 128-tiles: n <= 2944 on 148 SMs; larger fits ran in factor_full_dist above):
+  // 64 x 64 FMA tiles, four CTAs per 128-block -- a launch's duration is then one thread's serial FMA count.
   // Two chains: the Cholesky steps (diag -> panel -> trailing update) on the context's stream, the rows of
   // L^-1 (which only need D_k and the finished panel k) on an auxiliary stream, joined at the end.
-  // Small n: 64x64 tiles (four CTAs per 128-block) -- a launch then has fewer 128-tiles than SMs and its
-  // duration is one thread's serial FMA count.
-  const bool small = nblk * (nblk + 1) / 2 <= 2 * ctx->sm_count;
   SBO_TRY(ensure_factor_streams(ctx, nblk));
   cudaStream_t sb = ctx->aux_stream;
   double* scr_panel = ctx->d_small;                          // [rem * 128][128]
   double* scr_row = ctx->d_small + (size_t)kMaxAppend * ld;  // [128][ld]
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev_factor[0], st));
   SBO_CUDA(ctx, cudaStreamWaitEvent(sb, ctx->ev_factor[0], 0));
-  const dim3 sub(1, 1, small ? 4 : 1);
   // the first row-block pairs of the posterior start as soon as their rows of L^-1 are final (posterior_tc.cu)
   const int eager_pairs = tc_eager_pairs(ctx);
   const int eager_rows = eager_pairs * 512;
@@ -916,31 +922,20 @@ static int32_t factor_full_timed(sbo_ctx* ctx) {
     SBO_CUDA(ctx, cudaEventRecord(ev_d, st));
     const int rem = nblk - k - 1;
     if (rem > 0) {
-      if (small) {
-        panel_trsm_kernel<64><<<dim3(rem, 1, 4), kGemmThreads, 0, st>>>(ctx->d_A, ld, k, Dk, scr_panel, NB);
-        SBO_LAUNCH_CHECK(ctx, "panel_trsm_kernel");
-        panel_copy_kernel<<<(rem * NB + 7) / 8, dim3(NB, 8), 0, st>>>(ctx->d_A, ld, k, scr_panel, NB, rem * NB);
-        SBO_LAUNCH_CHECK(ctx, "panel_copy_kernel");
-      } else {
-        panel_trsm_kernel<128><<<rem, kGemmThreads, 0, st>>>(ctx->d_A, ld, k, Dk,
-                                                             ctx->d_A + (size_t)(k + 1) * NB * ld + (size_t)k * NB, ld);
-        SBO_LAUNCH_CHECK(ctx, "panel_trsm_kernel");
-      }
+      // (a 64-sub-tile reads the whole 128-wide row panel and writes half of it: result to scratch, then copied back)
+      panel_trsm_kernel<64><<<dim3(rem, 1, 4), kGemmThreads, 0, st>>>(ctx->d_A, ld, k, Dk, scr_panel, NB);
+      SBO_LAUNCH_CHECK(ctx, "panel_trsm_kernel");
+      panel_copy_kernel<<<(rem * NB + 7) / 8, dim3(NB, 8), 0, st>>>(ctx->d_A, ld, k, scr_panel, NB, rem * NB);
+      SBO_LAUNCH_CHECK(ctx, "panel_copy_kernel");
       SBO_CUDA(ctx, cudaEventRecord(ev_t, st));
-      if (small) syrk_kernel<64><<<dim3(rem * (rem + 1) / 2, 1, 4), kGemmThreads, 0, st>>>(ctx->d_A, ld, k);
-      else syrk_kernel<128><<<rem * (rem + 1) / 2, kGemmThreads, 0, st>>>(ctx->d_A, ld, k);
+      syrk_kernel<64><<<dim3(rem * (rem + 1) / 2, 1, 4), kGemmThreads, 0, st>>>(ctx->d_A, ld, k);
       SBO_LAUNCH_CHECK(ctx, "syrk_kernel");
     }
     SBO_CUDA(ctx, cudaStreamWaitEvent(sb, ev_d, 0));
-    if (small) {
-      trtri_row_kernel<64><<<dim3(k + 1, 1, 4), kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, k, Dk, scr_row, ld);
-      SBO_LAUNCH_CHECK(ctx, "trtri_row_kernel");
-      row_copy_kernel<<<dim3(((k + 1) * NB + 255) / 256, NB), 256, 0, sb>>>(ctx->d_Linv, ld, k, scr_row, ld, (k + 1) * NB);
-      SBO_LAUNCH_CHECK(ctx, "row_copy_kernel");
-    } else {
-      trtri_row_kernel<128><<<k + 1, kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, k, Dk, ctx->d_Linv + (size_t)k * NB * ld, ld);
-      SBO_LAUNCH_CHECK(ctx, "trtri_row_kernel");
-    }
+    trtri_row_kernel<64><<<dim3(k + 1, 1, 4), kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, k, Dk, scr_row, ld);
+    SBO_LAUNCH_CHECK(ctx, "trtri_row_kernel");
+    row_copy_kernel<<<dim3(((k + 1) * NB + 255) / 256, NB), 256, 0, sb>>>(ctx->d_Linv, ld, k, scr_row, ld, (k + 1) * NB);
+    SBO_LAUNCH_CHECK(ctx, "row_copy_kernel");
     if (eager_rows > 0 && (k + 1) * NB == eager_rows) {   // rows [0, eager_rows) of L^-1 are final on sb
       SBO_TRY(refresh_planes(ctx, 0, eager_rows, sb));
       cudaEvent_t ev_ready = ctx->ev_factor[2 + 2 * (nblk - 1)];   // the last block has no panel: its "panel done" event is free
@@ -953,8 +948,7 @@ static int32_t factor_full_timed(sbo_ctx* ctx) {
     }
     if (rem > 0) {
       SBO_CUDA(ctx, cudaStreamWaitEvent(sb, ev_t, 0));
-      if (small) trtri_update_kernel<64><<<dim3(k + 1, rem, 4), kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, ctx->d_A, k);
-      else trtri_update_kernel<128><<<dim3(k + 1, rem, 1), kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, ctx->d_A, k);
+      trtri_update_kernel<64><<<dim3(k + 1, rem, 4), kGemmThreads, 0, sb>>>(ctx->d_Linv, ld, ctx->d_A, k);
       SBO_LAUNCH_CHECK(ctx, "trtri_update_kernel");
     }
   }

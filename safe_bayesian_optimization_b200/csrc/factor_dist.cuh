@@ -16,8 +16,9 @@
 //   end:               every rank sends its block columns of L^-1 to every rank; alpha, the row norm and the fp16
 //                      planes are then computed from the full L^-1 on each rank as in the replicated fit.
 //
-// Every entry of L and L^-1 is produced by the same sequence of fp64 operations as in the replicated fit (same
-// 128 x 128 tile routine, same K order), so the result is bit-identical to it -- tests/test_gpu_group.py.
+// Every entry of L and L^-1 is produced by the same sequence of fp64 operations as in the replicated fit where that runs
+// the 128 x 128 DMMA tile routine too (n > 2944: factor_dmma.cuh; same kernels with W = 1), so the result is bit-identical
+// to it -- tests/test_gpu_group.py; against the 64 x 64 FMA tiles of a small replicated fit it agrees to rounding.
 //
 // Two transports behind the same schedule:
 //   * one process per GPU (sbo_comm_init):   ncclBroadcast of a packed panel message per step, ncclAllGather of the
@@ -54,63 +55,6 @@ void fit_peers_attach(FitPeers* p, sbo_ctx* ctx, int rank) {
 }
 
 namespace {
-
-// snake deal of block columns to ranks
-struct ColMap {
-  int W, me;
-  __host__ __device__ int col(int j) const { return 2 * W * (j >> 1) + ((j & 1) ? 2 * W - 1 - me : me); }   // j-th column of `me`
-  __host__ __device__ static int owner(int c, int W) {
-    const int t = c % (2 * W);
-    return t < W ? t : 2 * W - 1 - t;
-  }
-  __host__ int count_le(int k) const {   // how many of my columns are <= k
-    const int t = (k + 1) % (2 * W);
-    return 2 * ((k + 1) / (2 * W)) + (me < t ? 1 : 0) + (2 * W - 1 - me < t ? 1 : 0);
-  }
-};
-
-// A_ab -= L_ak L_bk^T for a = k + 1 + blockIdx.x >= b, b = the (j0 + blockIdx.y)-th block column of this rank (> k)
-__global__ void __launch_bounds__(kGemmThreads)
-syrk_cols_kernel(double* __restrict__ A, int ld, int k, ColMap map, int j0) {
-  __shared__ TileSmem<128> sm;
-  const int b = map.col(j0 + (int)blockIdx.y), a = k + 1 + (int)blockIdx.x;
-  if (a < b) return;
-  const int r0 = a * NB, c0 = b * NB, kc = k * NB;
-  double acc[8][8];
-  tile_zero(acc);
-  tile_gemm<true, 128>(sm, A, ld, r0, kc, A, ld, c0, kc, NB, acc);
-  tile_store<true, 128>(A, ld, r0, c0, acc, -1.0);
-}
-
-// X_kc = D_k B_kc (X_kk = D_k) for c = the blockIdx.x-th block column of this rank (<= k), in place
-__global__ void __launch_bounds__(kGemmThreads)
-trtri_row_cols_kernel(double* __restrict__ X, int ld, int k, const double* __restrict__ Dk, ColMap map) {
-  __shared__ TileSmem<128> sm;
-  const int c = map.col((int)blockIdx.x);
-  const int r0 = k * NB, c0 = c * NB;
-  if (c == k) {
-    for (int e = threadIdx.x; e < NB * NB; e += kGemmThreads) {
-      const int i = e / NB, j = e - i * NB;
-      X[(size_t)(r0 + i) * ld + c0 + j] = Dk[(size_t)i * NB + j];
-    }
-    return;
-  }
-  double acc[8][8];
-  tile_zero(acc);
-  tile_gemm<false, 128>(sm, Dk, NB, 0, 0, X, ld, c0, r0, NB, acc);
-  tile_store<false, 128>(X, ld, r0, c0, acc, 1.0);
-}
-
-// B_ic -= L_ik X_kc for i = k + 1 + blockIdx.y, c = the blockIdx.x-th block column of this rank (<= k)
-__global__ void __launch_bounds__(kGemmThreads)
-trtri_update_cols_kernel(double* __restrict__ X, int ld, const double* __restrict__ A, int k, ColMap map) {
-  __shared__ TileSmem<128> sm;
-  const int r0 = (k + 1 + (int)blockIdx.y) * NB, c0 = map.col((int)blockIdx.x) * NB, kc = k * NB;
-  double acc[8][8];
-  tile_zero(acc);
-  tile_gemm<false, 128>(sm, A, ld, r0, kc, X, ld, c0, kc, NB, acc);
-  tile_store<true, 128>(X, ld, r0, c0, acc, -1.0);
-}
 
 // panel message of step k (NCCL transport): [0] Cholesky status so far, [16 ..) D_k, then the rem x 128-row panel
 constexpr int kMsgHeader = 16;   // doubles
@@ -253,8 +197,10 @@ int32_t factor_full_dist_impl(sbo_ctx* ctx, int W) {
   const int np = (n + NB - 1) / NB * NB, nblk = np / NB;
   const double sf2 = ctx->cfg.sigma_f * ctx->cfg.sigma_f;
   const double inv2l2 = 1.0 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale);
-  FitPeers* peers = ctx->fit_peers;
-  const int me = peers ? ctx->fit_rank : ctx->rank;
+  // W = 1: the same schedule on one GPU (look-ahead of the next panel, prioritised streams), nothing to exchange
+  const bool solo = W == 1;
+  FitPeers* peers = solo ? nullptr : ctx->fit_peers;
+  const int me = solo ? 0 : (peers ? ctx->fit_rank : ctx->rank);
   const ColMap map{W, me};
   cudaStream_t st = ctx->stream;
 
@@ -263,7 +209,7 @@ int32_t factor_full_dist_impl(sbo_ctx* ctx, int W) {
   cudaStream_t hi = ctx->fit_hi, lo = ctx->fit_lo, cm = ctx->fit_cm;
   const size_t msg_max = kMsgHeader + (size_t)NB * NB * (size_t)nblk;
   size_t slot = 0;
-  if (!peers) {
+  if (!peers && !solo) {
     SBO_TRY(ensure_buffer(ctx, &ctx->d_fit_stage, &ctx->fit_stage_cap, msg_max));
     for (int r = 0; r < W; ++r) slot = std::max(slot, packed_size(W, r, nblk, np));
     SBO_TRY(ensure_buffer(ctx, &ctx->d_fit_send, &ctx->fit_send_cap, slot));
@@ -299,8 +245,8 @@ int32_t factor_full_dist_impl(sbo_ctx* ctx, int W) {
     SBO_LAUNCH_CHECK(ctx, "diag_chol_inv_kernel");
     const int rem = nblk - k - 1;
     if (rem > 0) {
-      panel_trsm_kernel<128><<<rem, kGemmThreads, 0, hi>>>(ctx->d_A, ld, k, Dk, ctx->d_A + (size_t)(k + 1) * NB * ld + (size_t)k * NB, ld);
-      SBO_LAUNCH_CHECK(ctx, "panel_trsm_kernel");
+      panel_trsm_dm_kernel<<<rem, kDmThreads, kDmSmem, hi>>>(ctx->d_A, ld, k, Dk);
+      SBO_LAUNCH_CHECK(ctx, "panel_trsm_dm_kernel");
     }
     SBO_CUDA(ctx, cudaEventRecord(ev_panel(k), hi));
     if (peers) peers_post(peers, k);
@@ -315,7 +261,9 @@ int32_t factor_full_dist_impl(sbo_ctx* ctx, int W) {
     // ---- the exchange of step k ----
     const size_t msg = kMsgHeader + (size_t)NB * NB * (size_t)(1 + rem);
     const unsigned msg_blocks = (unsigned)(((size_t)NB * NB * (size_t)(1 + rem) + 255) / 256);
-    if (!peers) {
+    if (solo) {
+      // nothing to exchange
+    } else if (!peers) {
       if (own == me) {
         SBO_CUDA(ctx, cudaStreamWaitEvent(cm, ev_panel(k), 0));
         pack_panel_kernel<<<msg_blocks, 256, 0, cm>>>(ctx->d_A, ld, k, rem, Dk, ctx->d_info, ctx->d_fit_stage);
@@ -348,32 +296,34 @@ int32_t factor_full_dist_impl(sbo_ctx* ctx, int W) {
       const int j_end = map.count_le(nblk - 1);
       int j0 = j_next;
       if (ColMap::owner(k + 1, W) == me) {                // my column j_next IS k + 1
-        syrk_cols_kernel<<<dim3(rem, 1), kGemmThreads, 0, hi>>>(ctx->d_A, ld, k, map, j_next);
-        SBO_LAUNCH_CHECK(ctx, "syrk_cols_kernel");
+        syrk_dm_kernel<<<dim3(rem, 1), kDmThreads, kDmSmem, hi>>>(ctx->d_A, ld, k, map, j_next);
+        SBO_LAUNCH_CHECK(ctx, "syrk_dm_kernel");
         SBO_TRY(diag_and_panel(k + 1));
         panel_done[(size_t)(k + 1)] = 1;
         j0 = j_next + 1;
       }
       if (j_end > j0) {
-        syrk_cols_kernel<<<dim3(rem, j_end - j0), kGemmThreads, 0, hi>>>(ctx->d_A, ld, k, map, j0);
-        SBO_LAUNCH_CHECK(ctx, "syrk_cols_kernel");
+        syrk_dm_kernel<<<dim3(rem, j_end - j0), kDmThreads, kDmSmem, hi>>>(ctx->d_A, ld, k, map, j0);
+        SBO_LAUNCH_CHECK(ctx, "syrk_dm_kernel");
       }
     }
     // ---- rows of L^-1 for my block columns <= k ----
     const int jc = map.count_le(k);
     if (jc > 0) {
-      trtri_row_cols_kernel<<<jc, kGemmThreads, 0, lo>>>(ctx->d_Linv, ld, k, Dk, map);
-      SBO_LAUNCH_CHECK(ctx, "trtri_row_cols_kernel");
+      trtri_row_dm_kernel<<<jc, kDmThreads, kDmSmem, lo>>>(ctx->d_Linv, ld, k, Dk, map);
+      SBO_LAUNCH_CHECK(ctx, "trtri_row_dm_kernel");
       if (rem > 0) {
-        trtri_update_cols_kernel<<<dim3(jc, rem), kGemmThreads, 0, lo>>>(ctx->d_Linv, ld, ctx->d_A, k, map);
-        SBO_LAUNCH_CHECK(ctx, "trtri_update_cols_kernel");
+        trtri_update_dm_kernel<<<dim3(jc, rem), kDmThreads, kDmSmem, lo>>>(ctx->d_Linv, ld, ctx->d_A, k, map);
+        SBO_LAUNCH_CHECK(ctx, "trtri_update_dm_kernel");
       }
     }
   }
   // ---- every rank's block columns of L^-1 to every rank ----
   const int jmine = map.count_le(nblk - 1);
   SBO_CUDA(ctx, cudaEventRecord(ev_lo, lo));
-  if (!peers) {
+  if (solo) {
+    // every column is here already
+  } else if (!peers) {
     if (jmine > 0) {
       linv_cols_kernel<true><<<dim3(256, jmine), 256, 0, lo>>>(ctx->d_Linv, ld, np, map, ctx->d_fit_send);
       SBO_LAUNCH_CHECK(ctx, "linv_cols_kernel");
@@ -442,11 +392,14 @@ int32_t factor_full_dist_impl(sbo_ctx* ctx, int W) {
 
 }  // namespace
 
-// 0: not shared (the caller runs the replicated fit); otherwise the shared fit ran and *status holds its result
+// 0: the caller runs the small-n fit (64 x 64 tiles, eager first pairs); otherwise this schedule ran -- shared between W ranks,
+// or on this GPU alone when the fit is large enough for 128 x 128 tiles -- and *status holds its result
 int factor_full_dist(sbo_ctx* ctx, int32_t* status) {
   const int W = dist_world(ctx);
+  const int nblk = (ctx->n + NB - 1) / NB;
+  const bool large = nblk * (nblk + 1) / 2 > 2 * ctx->sm_count;   // more 128-tiles per launch than 2 x SMs (n > 2944 on 148 SMs)
   ctx->fit_dist_used = 0;
-  if (W <= 1) return 0;
+  if (W <= 1 && !large) return 0;
   *status = factor_full_dist_impl(ctx, W);
   if (*status != SBO_OK && *status != SBO_ERR_NOT_POSDEF && ctx->fit_peers) peers_abort(ctx->fit_peers);
   if (*status != SBO_OK) {   // leave the side streams idle whatever happened
@@ -454,6 +407,6 @@ int factor_full_dist(sbo_ctx* ctx, int32_t* status) {
     cudaStreamSynchronize(ctx->fit_lo);
     cudaStreamSynchronize(ctx->fit_cm);
   }
-  ctx->fit_dist_used = W;
-  return W;
+  ctx->fit_dist_used = W > 1 ? W : 0;
+  return 1;
 }

@@ -144,7 +144,7 @@ extern "C" int32_t sbo_plan_row_bands(const sbo_config* cfg, const double* xy, i
     // the launcher walks densely when little can be skipped (tc_plan_skip): equal cost per row then.  Otherwise a fixed
     // cost per tile (mask build, pipeline fill and drain, epilogues, mu) rides on the MMA passes: calibrated on the two
     // bands of the 2-GPU C4 run of round 2 (t = a passes + b rows gave b H = 6.5 % of the step; profiles/bench_c4_2gpu_r02b.json).
-    if (sparse >= 0.85 * dense) std::fill(cost.begin(), cost.end(), 1.0);
+    if (sparse >= 0.90 * dense) std::fill(cost.begin(), cost.end(), 1.0);   // (the launcher's rule: posterior_tc.cu kSkipWorthIt)
     else {
       const double floor_c = 0.07 * sparse / nsamp;
       for (double& c : cost) c += floor_c;

@@ -51,26 +51,43 @@ def test_group_equals_single_context(pkg, precision, members):
             assert np.array_equal(mi, m1) and ri.safe_count == r1.safe_count and ri.n_obs == p.n + 1 and g.n_obs == p.n + 1
 
 
-@pytest.mark.parametrize("precision,members,n", [("fp64", 2, 700), ("fp32", 3, 1100), ("fp32", 8, 1500), ("fp64", 4, 129)])
-def test_shared_fit_bit_identical(pkg, precision, members, n):
+@pytest.mark.parametrize("precision,members,n", [("fp64", 2, 700), ("fp32", 3, 1100), ("fp32", 8, 1500), ("fp64", 4, 129),
+                                                 ("fp32", 2, 3100), ("fp64", 3, 3300)])
+def test_shared_fit_equals_replicated(pkg, precision, members, n):
     """SBO_OPT_DIST_FIT: block columns of the Cholesky / L^-1 work dealt to the members (snake order), panel exchange per
-    step, all-gather of L^-1 at the end -- every member must end with the replicated fit's L^-1 and alpha, bit for bit."""
+    step, all-gather of L^-1 at the end.  Every member must end with the same L^-1 and alpha as every other member, bit for
+    bit, and with the replicated fit's: bit for bit where that runs the same 128 x 128 DMMA tile routine (n > 2944), to
+    rounding where it runs the 64 x 64 FMA tiles (small n: a different summation order inside a tile)."""
     p = S.make_problem("C3", n=n, W=256, H=24)
     with make_ctx(pkg, p, precision=precision, max_obs=p.n + 4) as ctx:
         ctx.set_observations(p.xy, p.y)
         linv1, alpha1 = ctx.linv(), ctx.alpha()
         assert ctx.fit_info()[1] == 0
+    same_routine = n > 2944
+
+    def check(linv, alpha, who):
+        if same_routine:
+            assert np.array_equal(linv, linv1), f"{who}: L^-1 differs from the replicated fit"
+            assert np.array_equal(alpha, alpha1)
+        else:
+            assert np.abs(linv - linv1).max() <= 1e-11 * np.abs(linv1).max(), who
+            assert np.abs(alpha - alpha1).max() <= 1e-9 * np.abs(alpha1).max(), who
+
     with pkg.SboGroup(_devices(members), sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var,
                       prior_mean=p.prior_mean, precision=precision, max_obs=p.n + 4, max_cells=p.m) as g:
         g.set_option("dist_fit", 1)
         g.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
         for rep in range(2):                                 # twice: the rendezvous and the events are reused
             g.set_observations(p.xy, p.y)
+            first = None
             for i in range(members):
                 linv, alpha, (ms, shared) = g.member_factor(i)
                 assert shared == members and ms > 0
-                assert np.array_equal(linv, linv1), f"member {i}: L^-1 differs from the replicated fit"
-                assert np.array_equal(alpha, alpha1)
+                check(linv, alpha, f"member {i}")
+                if first is None:
+                    first = (linv, alpha)
+                else:
+                    assert np.array_equal(linv, first[0]) and np.array_equal(alpha, first[1]), f"member {i} != member 0"
         g.set_option("dist_fit", 0)
         g.set_observations(p.xy, p.y)
         assert g.member_factor(members - 1)[2][1] == 0 and np.array_equal(g.member_factor(0)[0], linv1)
