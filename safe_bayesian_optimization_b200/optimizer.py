@@ -445,6 +445,18 @@ def shard_rows(H: int, rank: int, world: int):
     return r0, r0 + base + (1 if rank < rem else 0)
 
 
+def fit_column_owner(c: int, world: int) -> int:
+    """Rank that owns block column ``c`` of a shared fit: the snake deal 0 1 .. W-1 W-1 .. 1 0 of ``csrc/factor_dmma.cuh:
+    ColMap`` (column c costs ~ nblk - c tiles per step of the factorisation; the snake evens that out between ranks)."""
+    t = c % (2 * world)
+    return t if t < world else 2 * world - 1 - t
+
+
+def fit_columns_of(rank: int, world: int, nblk: int):
+    """Block columns of ``rank`` in increasing order (``ColMap::col`` for j = 0 .. ``ColMap::count_le(nblk - 1)`` - 1)."""
+    return [c for c in range(nblk) if fit_column_owner(c, world) == rank]
+
+
 def plan_row_bands(p, parts: int, max_rows: int = 0, precision=None, kernel="auto"):
     """Cost-balanced row bands for problem ``p`` (anything with xy, x0, y0, rx, ry, W, H and the hyper-parameters) over
     ``parts`` GPUs: (row_cuts list[parts + 1], cost_share list[parts]).  Host arithmetic (sbo_plan_row_bands)."""

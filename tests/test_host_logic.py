@@ -111,6 +111,81 @@ def test_two_rank_gloo_sharding_equals_single(oracle, coracle):
     assert merged.argmax_width == coracle.argmax_safe(q1 - q0, mask)
 
 
+def _shared_fit_worker(rank, world, port, q, n, nb):
+    """The schedule of csrc/factor_dist.cuh restated in numpy over gloo: blocked right-looking Cholesky + blocked forward
+    substitution for L^-1 with the block columns dealt in snake order; ONE broadcast per step (D_k and panel k from the
+    owner of column k), one all-gather of the block columns of L^-1 at the end.  A rank only ever touches the block
+    columns it owns plus what the broadcasts delivered -- everything else stays NaN, so a read of somebody else's stale
+    data would poison the result."""
+    import torch
+    import torch.distributed as dist
+    from oracle import oracle as O
+    from safe_bayesian_optimization_b200.optimizer import fit_column_owner, fit_columns_of
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    p = S.make_problem("C2", n=n, W=8, H=8)
+    hp = O.Hyper(p.sigma_f, p.length, p.noise_var, p.prior_mean)
+    K = O.rbf_np(p.xy, p.xy, hp) + hp.noise_var * np.eye(n)
+    nblk = n // nb
+    mine = fit_columns_of(rank, world, nblk)
+    blk = lambda i: slice(i * nb, (i + 1) * nb)
+    A = np.full((n, n), np.nan)                       # trailing matrix: only my block columns are real
+    for c in mine:
+        A[:, blk(c)] = K[:, blk(c)]
+    X = np.full((n, n), np.nan)                       # L^-1: only my block columns
+    for c in mine:
+        X[:, blk(c)] = 0.0
+    for k in range(nblk):
+        own = fit_column_owner(k, world)
+        rem = nblk - k - 1
+        msg = torch.zeros((1 + rem) * nb, nb, dtype=torch.float64)
+        if own == rank:
+            Lkk = np.linalg.cholesky(A[blk(k), blk(k)])
+            Dk = np.linalg.inv(Lkk)
+            panel = A[(k + 1) * nb:, blk(k)] @ Dk.T
+            msg[:nb] = torch.from_numpy(Dk); msg[nb:] = torch.from_numpy(panel)
+        dist.broadcast(msg, src=own)                  # the one exchange of step k
+        Dk, panel = msg[:nb].numpy(), msg[nb:].numpy()
+        for b in (c for c in mine if c > k):          # trailing update of MY columns
+            rows = slice(b * nb, n)
+            A[rows, blk(b)] -= panel[(b - k - 1) * nb:] @ panel[(b - k - 1) * nb:(b - k) * nb].T
+        for c in (c for c in mine if c <= k):         # row block k of L^-1, my columns; then the running right-hand side
+            X[blk(k), blk(c)] = Dk if c == k else Dk @ X[blk(k), blk(c)]
+            if rem:
+                X[(k + 1) * nb:, blk(c)] -= panel @ X[blk(k), blk(c)]
+    cols = [None] * world
+    dist.all_gather_object(cols, {c: X[:, blk(c)] for c in mine})   # every rank's block columns to every rank
+    Linv = np.zeros((n, n))
+    for part in cols:
+        for c, v in part.items():
+            Linv[:, blk(c)] = v
+    q.put((rank, Linv))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n,nb", [(2, 96, 8), (3, 80, 8)])
+def test_shared_fit_schedule_over_gloo(oracle, coracle, world, n, nb):
+    """N > 1 host logic of the shared fit, on CPU: every rank ends with the oracle's L^-1."""
+    import torch.multiprocessing as mp
+    from safe_bayesian_optimization_b200.optimizer import fit_column_owner, fit_columns_of
+    assert [fit_column_owner(c, 3) for c in range(8)] == [0, 1, 2, 2, 1, 0, 0, 1]
+    assert fit_columns_of(1, 4, 20) == [1, 6, 9, 14, 17] and sorted(sum((fit_columns_of(r, 4, 20) for r in range(4)), [])) == list(range(20))
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_shared_fit_worker, args=(r, world, port, q, n, nb)) for r in range(world)]
+    [p.start() for p in procs]
+    got = dict(q.get(timeout=90) for _ in range(world))
+    [p.join(60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    p = S.make_problem("C2", n=n, W=8, H=8)
+    hp = oracle.Hyper(p.sigma_f, p.length, p.noise_var, p.prior_mean)
+    _, Linv, _ = coracle.gp_fit(p.xy, p.y, hp)
+    for r in range(world):
+        assert np.isfinite(got[r]).all() and np.abs(got[r] - Linv).max() <= 1e-10 * np.abs(Linv).max()
+        assert np.array_equal(got[r], got[0])
+
+
 def test_compact_cells_known_answers(oracle):
     """Hand-checked cases of the safe / border cell lists (the checker of tests/test_gpu_frontier.py)."""
     g = oracle.Grid(0.0, 0.0, 1.0, 1.0, 5, 4)
