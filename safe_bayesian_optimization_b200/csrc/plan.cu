@@ -109,6 +109,11 @@ extern "C" int32_t sbo_plan_row_bands(const sbo_config* cfg, const double* xy, i
   using namespace sbo;
   if (!cfg || !row_cuts || parts < 1 || W < 1 || H < 1 || n < 0 || (n > 0 && !xy)) return SBO_ERR_INVALID_ARG;
   if (max_rows > 0 && (int64_t)max_rows * parts < H) return SBO_ERR_CAPACITY;
+  if (parts == 1) {   // nothing to cut
+    row_cuts[0] = 0; row_cuts[1] = H;
+    if (cost_share) cost_share[0] = 1.0;
+    return SBO_OK;
+  }
   // cost of one grid row: estimated on every `stride`-th row (the cost varies on the scale of a length-scale, i.e. many rows)
   const int nsamp = std::min(H, 512);
   std::vector<double> cost((size_t)nsamp, 1.0);
@@ -126,20 +131,41 @@ extern "C" int32_t sbo_plan_row_bands(const sbo_config* cfg, const double* xy, i
     const double bits = tc_skip_bits_of(*cfg, n, 0.0), ring = tc_ring_bits_of(*cfg, n, 0.0, shift_a);
     const int tiles_per_row = (W + kBM - 1) / kBM;
     const int tstep = std::max(1, tiles_per_row / 64);
+    // The box test of tile_visit_cost, separated: the x distance depends on (tile column, chunk), the y distance on (row,
+    // chunk), and the chunks are banded in y, so most of them fail on dy alone for a given row.  Every term is a small
+    // integer (row blocks that walk the chunk, times 1 or 3), so the sums are exact whatever their order.
+    const int nchunks = (n + kBK - 1) / kBK, nblocks = (n + kBN - 1) / kBN;
+    std::vector<double> wgt((size_t)nchunks);
+    double wsum = 0.0;
+    for (int c = 0; c < nchunks; ++c) { wgt[c] = nblocks - c / (kBN / kBK); wsum += wgt[c]; }
+    std::vector<int> tcols;
+    for (int b = 0; b < tiles_per_row; b += tstep) tcols.push_back(b);
+    std::vector<double> dx2(tcols.size() * (size_t)nchunks);
+    for (size_t t = 0; t < tcols.size(); ++t) {
+      const double tx0 = (x0 + (double)tcols[t] * kBM * rx) * xs, tx1 = tx0 + (kBM - 1) * rx * xs;
+      const double xlo = std::min(tx0, tx1), xhi = std::max(tx0, tx1);
+      for (int c = 0; c < nchunks; ++c) {
+        const double dx = std::max(std::max(box[4 * c] - xhi, xlo - box[4 * c + 1]), 0.0);
+        dx2[t * nchunks + c] = dx * dx;
+      }
+    }
     double dense = 0.0, sparse = 0.0;
     for (int a = 0; a < nsamp; ++a) {
       const int row = (int)(((2LL * a + 1) * H) / (2LL * nsamp));
       const double y = (y0 + row * ry) * xs;
-      double c = 0.0;
-      for (int b = 0; b < tiles_per_row; b += tstep) {
-        const double tx0 = (x0 + (double)b * kBM * rx) * xs, tx1 = tx0 + (kBM - 1) * rx * xs;
-        double t, k, p;
-        tile_visit_cost(box, n, std::min(tx0, tx1), std::max(tx0, tx1), y, bits, ring, &t, &k, &p);
-        c += p;
-        dense += 3.0 * t;
-        sparse += p;
+      double cst = 0.0;
+      for (int c = 0; c < nchunks; ++c) {
+        const double dy = std::max(std::max(box[4 * c + 2] - y, y - box[4 * c + 3]), 0.0);
+        const double dy2 = dy * dy;
+        if (dy2 > bits + 0.5) continue;
+        for (size_t t = 0; t < tcols.size(); ++t) {
+          const double d2 = dx2[t * nchunks + c] + dy2;
+          if (d2 <= bits + 0.5) cst += d2 <= ring + 0.5 ? 3.0 * wgt[c] : wgt[c];
+        }
       }
-      cost[a] = c;
+      cost[a] = cst;
+      dense += 3.0 * wsum * (double)tcols.size();
+      sparse += cst;
     }
     // the launcher walks densely when little can be skipped (tc_plan_skip): equal cost per row then.  Otherwise a fixed
     // cost per tile (mask build, pipeline fill and drain, epilogues, mu) rides on the MMA passes: calibrated on the two
