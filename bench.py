@@ -615,6 +615,7 @@ def main():
                               "(hi.hi + hi.lo + lo.hi), fp32 accumulation in TMEM, fp64 factorisation",
                 "data": "synthetic", "config": main_out["config"], "phases_ms": main_out["phases_ms"],
                 "per_rank": main_out["per_rank"], "ms_posterior_spread": main_out["ms_posterior_spread"],
+                "band_plan_ms": main_out["band_plan_ms"],
                 "roofline": main_out["roofline"], "cpu_baseline": cpu, "clocks": main_out["clocks"], "e2e": e2e,
                 "sustained": main_out.get("sustained"), "e2e_incremental": main_out["e2e_incremental"],
                 "parity": main_out["parity"], "checksums": main_out["checksums"], "limiter": limiter,
