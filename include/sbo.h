@@ -35,7 +35,8 @@
 extern "C" {
 #endif
 
-#define SBO_ABI_VERSION 2   /* 2: sbo_step_out gained low_sigma2 / refreshed / drift; options; row-band planner; device groups */
+#define SBO_ABI_VERSION 2   /* 2: sbo_step_out gained low_sigma2 / refreshed / drift; options; row-band planner; device groups.
+                               Additive since (same version): sbo_fit_info, SBO_OPT_DIST_FIT, SBO_OPT_TC_PHASES, sbo_compute_sets_noalloc */
 
 typedef enum {
   SBO_OK = 0,

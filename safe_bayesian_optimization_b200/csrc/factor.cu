@@ -609,15 +609,6 @@ gemv_lower_t_kernel(const double* __restrict__ X, int ld, int n, const double* _
   }
 }
 
-__global__ void fill_kernel(double* p, double v, int count) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < count) p[i] = v;
-}
-__global__ void fill_f32_kernel(float* p, float v, int count) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < count) p[i] = v;
-}
-
 // ---------------------------------------------------------------------------------------------
 // fp16 operand planes of L^-1 for the tcgen05 contraction: xs = 2^shift x, hi = rn_f16(xs),
 // lo = rn_f16(xs - hi); rows [r0, r1), all n_cap columns.  |xs| <= 2^15 by tc_plane_shifts' bound.
