@@ -133,7 +133,8 @@ int32_t sbo_synchronize(sbo_ctx* ctx);
  * shipped libsbo.so computes the same thing whatever the caller's environment holds. */
 typedef enum {
   SBO_OPT_TC_CTA_GROUP = 1,      /* 2 (default): CTA pairs, tcgen05 cta_group::2; 1: single CTAs                         */
-  SBO_OPT_TC_SKIP = 2,           /* 1 (default): block-sparse walk of K* where the planner finds enough to skip; 0: dense  */
+  SBO_OPT_TC_SKIP = 2,           /* 1 (default): block-sparse walk of K* where the planner finds enough to skip (SBO_FP64:
+                                    always, with its own cut-off: what is left out moves sigma^2 by < 1e-12 sigma_f^2); 0: dense */
   SBO_OPT_TC_PAIR = 3,           /* 1 (default): K*-stationary pair kernel for the full refresh; 0: row-block kernel      */
   SBO_OPT_TC_EAGER = 4,          /* 1 (default): first row-block pairs start inside the factorisation                    */
   SBO_OPT_TC_INC = 5,            /* 1 (default): incremental steps on large grids as a tensor-core GEMM                  */
@@ -409,7 +410,8 @@ int32_t sbo_tc_plan(sbo_ctx* ctx, int32_t* cta_group, int32_t* skipping, double*
 int32_t sbo_tc_plan_detail(sbo_ctx* ctx, double out[6]);
 /* Tensor-core flops the last full tcgen05 refresh of this context EXECUTED (counted by the MMA issuers: every split
  * product, block-triangular padding included, skipped chunks excluded): the numerator of a pipe-utilisation figure, as
- * opposed to the credited m n (n + 1) of SURVEY M4.  0 when the last step ran another kernel. */
+ * opposed to the credited m n (n + 1) of SURVEY M4.  In SBO_FP64 the same for the DMMA kernel (visited stages of 128 cells x
+ * 128 rows x 32 observations).  0 when the last step ran another kernel. */
 int32_t sbo_tc_executed_flops(sbo_ctx* ctx, double* flops);
 /* Device properties the library sees: SM count, and 1 if tcgen05 path usable. */
 int32_t sbo_device_info(const sbo_ctx* ctx, int32_t* sm_count, int32_t* tcgen05_ok);

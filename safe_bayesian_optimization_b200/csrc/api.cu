@@ -40,7 +40,7 @@ void free_all(sbo_ctx* c) {
   void* dev[] = {c->d_xy, c->d_r, c->d_A, c->d_Linv, c->d_Dinv, c->d_alpha, c->d_w, c->d_small, c->d_info,
                  c->d_planes, c->d_alpha_f32, c->d_obs_f32, c->d_chunk_bbox, c->d_exec_cols, c->d_fr_img, c->d_fr_lut, c->d_cp_idx, c->d_cp_counts, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
                  c->d_partials, c->d_result, c->d_ticket, c->d_frontier, c->d_sel_keys, c->d_sel_width, c->d_sel_out,
-                 c->d_gather, c->d_drift_mu, c->d_drift_s2, c->d_drift_out, c->d_fit_stage, c->d_fit_send, c->d_fit_recv};
+                 c->d_gather, c->d_chunk_bbox64, c->d_drift_mu, c->d_drift_s2, c->d_drift_out, c->d_fit_stage, c->d_fit_send, c->d_fit_recv};
   for (void* p : dev)
     if (p) cudaFree(p);
   if (c->h_result) cudaFreeHost(c->h_result);
@@ -347,11 +347,11 @@ int32_t sbo_create(const sbo_config* cfg, sbo_ctx** out) {
     CREATE_CUDA(cudaMalloc(&c->d_obs_f32, sizeof(float) * 4 * nc));
     CREATE_CUDA(cudaMemset(c->d_obs_f32, 0, sizeof(float) * 4 * nc));
     CREATE_CUDA(cudaMalloc(&c->d_chunk_bbox, sizeof(float) * 4 * (nc / 64 + 1)));
-    CREATE_CUDA(cudaMalloc(&c->d_exec_cols, sizeof(unsigned long long)));
-    CREATE_CUDA(cudaMemset(c->d_exec_cols, 0, sizeof(unsigned long long)));
     CREATE_CUDA(cudaMalloc(&c->d_alpha_f32, sizeof(float) * nc));
     CREATE_CUDA(cudaMemset(c->d_alpha_f32, 0, sizeof(float) * nc));
   }
+  CREATE_CUDA(cudaMalloc(&c->d_exec_cols, sizeof(unsigned long long)));   // executed-work counter of the last full refresh
+  CREATE_CUDA(cudaMemset(c->d_exec_cols, 0, sizeof(unsigned long long)));
   CREATE_CUDA(cudaMalloc(&c->d_mu, es * mc));
   CREATE_CUDA(cudaMalloc(&c->d_s2, es * mc));
   CREATE_CUDA(cudaMalloc(&c->d_mask, mc + 16));
@@ -499,7 +499,8 @@ int32_t sbo_tc_executed_flops(sbo_ctx* ctx, double* flops) {
   SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   SBO_CUDA(ctx, cudaMemcpyAsync(&cols, ctx->d_exec_cols, sizeof(cols), cudaMemcpyDeviceToHost, ctx->stream));
   SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  *flops = 2.0 * 256.0 * 16.0 * (double)cols;   // every counted MMA is M 256 (CTA pair) x N x K 16
+  if (ctx->cfg.precision == SBO_FP64) *flops = 2.0 * 128.0 * 128.0 * 32.0 * (double)cols;   // DMMA kernel: (tile, row block, stage) visits of 128 cells x 128 rows x 32 observations
+  else *flops = 2.0 * 256.0 * 16.0 * (double)cols;   // every counted MMA is M 256 (CTA pair) x N x K 16
   return SBO_OK;
 }
 

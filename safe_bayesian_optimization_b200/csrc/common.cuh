@@ -102,6 +102,7 @@ struct sbo_ctx {
   std::vector<double> h_xy_sorted;  // host copy of d_xy (internal order), for the skip planner
   unsigned long long* d_exec_cols = nullptr;   // executed-work counter of the last full tcgen05 refresh (sbo_tc_executed_flops)
   float* d_chunk_bbox = nullptr; // [n_cap / 64] float4 scaled bounding boxes of the observation chunks
+  void* d_chunk_bbox64 = nullptr; // [n_cap / 64] double4 boxes in the caller's coordinates (fp64 kernel, lazy)
   float* d_alpha_f32 = nullptr;  // [n_cap]
   float* d_obs_f32 = nullptr;    // [n_cap] float4: scaled observation coordinates as fp32 (hi, lo) pairs (posterior_tc.cu)
   void* tmap_planes = nullptr;   // host copy of the CUtensorMap (128 B), 256-row box
@@ -220,6 +221,7 @@ void tile_visit_cost(const std::vector<double>& box, int n, double xlo, double x
                      double* total, double* kept, double* passes);
 double tc_skip_bits_of(const sbo_config& cfg, int n, double r1);
 double tc_ring_bits_of(const sbo_config& cfg, int n, double r1, int shift_a);
+double f64_skip_bits_of(const sbo_config& cfg, int n, double r1);
 
 // posterior_simt.cu
 int32_t launch_posterior_simt(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);

@@ -90,6 +90,15 @@ double tc_skip_bits_of(const sbo_config& cfg, int n, double r1) {
   return std::min(60.0, std::max(30.0, std::ceil(-std::log2(tc_term_budget(cfg, n, r1)))));
 }
 
+// The same cut-off for the fp64 kernel (posterior_f64.cu): per-term budget for 1e-12 sigma_f^2 on sigma^2 (1 % of the fp64
+// tolerance 1e-10); R1 measured by the fit, else its a-priori bound.
+double f64_skip_bits_of(const sbo_config& cfg, int n, double r1) {
+  const double nn = std::max(n, 1);
+  if (!(r1 > 0.0)) r1 = std::sqrt(nn / std::max(cfg.noise_var, 1e-300));
+  const double e = 1e-12 / (2.0 * std::sqrt(nn) * cfg.sigma_f * r1);
+  return std::min(90.0, std::max(40.0, std::ceil(-std::log2(e))));
+}
+
 // Graded split depth: visits whose K* entries are all < 2^-ring sigma_f^2 issue hi.hi only.  Leaving out A_lo.B_hi and
 // A_hi.B_lo costs, per term, at most (max(2^-11 K*, q) + 2^-11 K*) |L^-1[j][k]| with q = the fp16 subnormal quantum of the
 // scaled K* plane (2^-25 2^-shift_a / sigma_f^2: far entries are subnormal in the hi plane); ring is the smallest integer
@@ -117,7 +126,8 @@ extern "C" int32_t sbo_plan_row_bands(const sbo_config* cfg, const double* xy, i
   // cost of one grid row: estimated on every `stride`-th row (the cost varies on the scale of a length-scale, i.e. many rows)
   const int nsamp = std::min(H, 512);
   std::vector<double> cost((size_t)nsamp, 1.0);
-  const bool tensor_path = cfg->precision == SBO_FP32 && cfg->kernel != SBO_KERNEL_SIMT && n > 8 * kBK && cfg->noise_var > 0.0;
+  const bool f64_path = cfg->precision == SBO_FP64 && cfg->kernel != SBO_KERNEL_SIMT;
+  const bool tensor_path = (cfg->precision == SBO_FP32 || f64_path) && cfg->kernel != SBO_KERNEL_SIMT && n > 8 * kBK && cfg->noise_var > 0.0;
   if (tensor_path) {
     std::vector<int32_t> order;
     spatial_order(cfg->length_scale, xy, n, order);
@@ -128,7 +138,10 @@ extern "C" int32_t sbo_plan_row_bands(const sbo_config* cfg, const double* xy, i
     chunk_boxes(sxy.data(), n, xs, box);
     int shift_a, shift_b;
     tc_plane_shifts(*cfg, &shift_a, &shift_b);
-    const double bits = tc_skip_bits_of(*cfg, n, 0.0), ring = tc_ring_bits_of(*cfg, n, 0.0, shift_a);
+    // (fp64: the DMMA kernel walks the same chunks, no ring, its own cut-off; row blocks of 128 instead of 256 change the
+    //  weights by a constant factor only)
+    const double bits = f64_path ? f64_skip_bits_of(*cfg, n, 0.0) : tc_skip_bits_of(*cfg, n, 0.0);
+    const double ring = f64_path ? bits : tc_ring_bits_of(*cfg, n, 0.0, shift_a);
     const int tiles_per_row = (W + kBM - 1) / kBM;
     const int tstep = std::max(1, tiles_per_row / 64);
     // The box test of tile_visit_cost, separated: the x distance depends on (tile column, chunk), the y distance on (row,

@@ -46,6 +46,9 @@ struct F64Params {
   double x0, y0, rx, ry;
   int W, rows_local, row0;
   double sf2, inv2l2, prior_mean;
+  const double4* bbox;            // [ceil(n / 64)] (xmin, xmax, ymin, ymax) of the 64-observation chunks; null: dense walk
+  double skip_r2;                 // chunks farther than this (squared distance to the patch of cells) are left out
+  unsigned long long* exec_stages;   // executed (tile, row block, 32-observation stage) visits of the launch
 };
 
 struct F64Smem {
@@ -56,6 +59,7 @@ struct F64Smem {
   double al[3][FK];          // alpha; 0 beyond n
   double red[4][FM];         // row sums of the four warp columns
   double mu_part[4][FM];
+  uint32_t cmask[FT / 32];   // chunks (64 observations) within reach of this tile's patch: bit c of word c / 32
 };
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, int src_bytes) {
@@ -70,7 +74,29 @@ __device__ __forceinline__ void dmma(double (&c)[2], double a, double b) {
                : "d"(a), "d"(b));
 }
 
-// (row block, first observation) of a stage; row block jb walks k0 = 0, 16, .. < kd(jb)
+// Bounding box of every 64-observation chunk of the (spatially ordered) observations, in the caller's coordinates.
+__global__ void chunk_bbox_f64_kernel(const double* __restrict__ xy, int n, int nchunks, double4* __restrict__ bbox) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (c >= nchunks) return;
+  double xmin = INFINITY, xmax = -INFINITY, ymin = INFINITY, ymax = -INFINITY;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int k = c * 64 + h * 32 + lane;
+    if (k < n) {
+      const double x = xy[2 * (size_t)k], y = xy[2 * (size_t)k + 1];
+      xmin = fmin(xmin, x); xmax = fmax(xmax, x);
+      ymin = fmin(ymin, y); ymax = fmax(ymax, y);
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    xmin = fmin(xmin, __shfl_xor_sync(0xffffffffu, xmin, d)); xmax = fmax(xmax, __shfl_xor_sync(0xffffffffu, xmax, d));
+    ymin = fmin(ymin, __shfl_xor_sync(0xffffffffu, ymin, d)); ymax = fmax(ymax, __shfl_xor_sync(0xffffffffu, ymax, d));
+  }
+  if (lane == 0) bbox[c] = make_double4(xmin, xmax, ymin, ymax);
+}
+
+// (row block, first observation) of a stage; row block jb walks the kept stages k0 = 0, 32, .. < kd(jb)
 struct Cursor {
   int jb, k0;
 };
@@ -89,13 +115,42 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
   const int n_pad = (p.n + FK - 1) / FK * FK;
   const int jb_lo = p.j_lo / FN, jb_hi = (p.j_hi + FN - 1) / FN;   // row blocks [jb_lo, jb_hi)
   auto kd = [&](int jb) { return min(n_pad, (jb + 1) * FN); };
+  // Block-sparse walk (the fp64 counterpart of posterior_tc.cu's chunk masks): a stage is visited only if its
+  // 64-observation chunk has a point within skip_r2 of the tile's patch of cells, i.e. can hold a K* entry above the
+  // cut-off (plan.cu: f64_skip_bits_of -- what is left out moves sigma^2 by < 1e-12 sigma_f^2).  Row blocks without a
+  // kept stage are not visited at all.  All threads walk the same mask: uniform control flow.
+  const bool masked = p.bbox != nullptr;
+  auto kept = [&](int k0) { const int c = k0 >> 6; return !masked || ((sm.cmask[c >> 5] >> (c & 31)) & 1u) != 0u; };
+  auto seek = [&](Cursor& c) {   // first kept stage at or after c (c.jb == jb_hi: none)
+    while (c.jb < jb_hi) {
+      const int end = kd(c.jb);
+      while (c.k0 < end && !kept(c.k0)) c.k0 += FK;
+      if (c.k0 < end) return;
+      c.jb += 1; c.k0 = 0;
+    }
+  };
   auto advance = [&](Cursor& c) {
     c.k0 += FK;
-    if (c.k0 >= kd(c.jb)) { c.jb += 1; c.k0 = 0; }
+    seek(c);
   };
+  unsigned long long stages_done = 0;
 
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int col0 = (int)(tile % tiles_x) * PC, r0 = (int)(tile / tiles_x) * PR;
+    if (masked) {   // chunk mask of this tile: thread c tests chunk c (FT = 512 chunks = 32 768 observations at most)
+      bool on = tid < (n_pad + 63) / 64;
+      if (on) {
+        const double xa = cell_coord(p.x0, p.rx, col0), xb = cell_coord(p.x0, p.rx, min(col0 + PC, p.W) - 1);
+        const double ya = cell_coord(p.y0, p.ry, p.row0 + r0), yb = cell_coord(p.y0, p.ry, p.row0 + min(r0 + PR, p.rows_local) - 1);
+        const double4 b = p.bbox[tid];
+        const double dx = fmax(fmax(b.x - fmax(xa, xb), fmin(xa, xb) - b.y), 0.0);
+        const double dy = fmax(fmax(b.z - fmax(ya, yb), fmin(ya, yb) - b.w), 0.0);
+        on = dx * dx + dy * dy <= p.skip_r2;
+      }
+      const uint32_t bits = __ballot_sync(0xffffffffu, on);
+      if (lane == 0) sm.cmask[warp] = bits;
+      __syncthreads();
+    }
 
     // ---- per-stage producers -------------------------------------------------------------------------
     // factor tables of the stage that starts at observation k0: the global loads are issued by table_load (early
@@ -176,17 +231,20 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
 
       // ---- prologue: tables of stages 0 and 1, table inputs of stage 2, K* and L^-1 of stage 0 ----
       Cursor cur{jb_lo, 0};                       // stage being contracted
-      Cursor nxt = cur; advance(nxt);             // its successors (jb == jb_hi: beyond the end)
+      seek(cur);
+      Cursor nxt = cur; if (cur.jb < jb_hi) advance(nxt);   // its successors (jb == jb_hi: beyond the end)
       Cursor nx2 = nxt; if (nxt.jb < jb_hi) advance(nx2);
       Cursor nx3 = nx2; if (nx2.jb < jb_hi) advance(nx3);
-      table_store(cur.k0, 0, table_load(cur.k0));
-      if (nxt.jb < jb_hi) table_store(nxt.k0, 1, table_load(nxt.k0));
       TabIn tab_cur = table_load(nx2.jb < jb_hi ? nx2.k0 : 0);   // inputs of the tables stored during iteration s = 0
-      load_b(cur, 0);
-      __syncthreads();
-      make_a(0, 0, cur.jb == jb_hi - 1);
-      cp_async_wait_all();
-      __syncthreads();
+      if (cur.jb < jb_hi) {                       // (a tile out of reach of every observation walks nothing)
+        table_store(cur.k0, 0, table_load(cur.k0));
+        if (nxt.jb < jb_hi) table_store(nxt.k0, 1, table_load(nxt.k0));
+        load_b(cur, 0);
+        __syncthreads();
+        make_a(0, 0, cur.jb == jb_hi - 1);
+        cp_async_wait_all();
+        __syncthreads();
+      }
 
       int s = 0;   // stage counter: A/B buffer s & 1, table buffer s % 3
       while (cur.jb < jb_hi) {
@@ -219,7 +277,8 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
         }
         tab_cur = tab_new;
         // ---- end of a row block: squared row sums of this 128 x 128 block of V ----
-        if (cur.k0 + FK >= kd(cur.jb)) {
+        ++stages_done;
+        if (nxt.jb != cur.jb) {   // the last kept stage of this row block
 #pragma unroll
           for (int mi = 0; mi < MI; ++mi) {
             double q = 0.0;
@@ -260,8 +319,9 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
         mu_out[lc] = p.prior_mean + ((sm.mu_part[0][tid] + sm.mu_part[1][tid]) + (sm.mu_part[2][tid] + sm.mu_part[3][tid]));
       }
     }
-    __syncthreads();   // red / mu_part / stage buffers are reused by the next tile
+    __syncthreads();   // red / mu_part / stage buffers / the chunk mask are reused by the next tile
   }
+  if (p.exec_stages && tid == 0 && stages_done) atomicAdd(p.exec_stages, stages_done);
 }
 
 }  // namespace
@@ -281,6 +341,22 @@ int32_t launch_posterior_f64(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) 
   p.inv2l2 = 1.0 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale);
   p.prior_mean = ctx->cfg.prior_mean;
   if (p.ld % 2 != 0) return fail(ctx, SBO_ERR_STATE, "posterior_f64: odd leading dimension of L^-1");
+  // block-sparse walk: boxes of the 64-observation chunks (the observations are spatially ordered in every precision) and
+  // the reach beyond which K* < 2^-bits sigma_f^2 (bits: plan.cu, from the measured row norm of L^-1)
+  p.bbox = nullptr;
+  p.skip_r2 = 0.0;
+  p.exec_stages = ctx->d_exec_cols;
+  const int nchunks = (ctx->n + 63) / 64;
+  if (ctx->tc_skip && ctx->n >= 512 && nchunks <= FT) {
+    if (!ctx->d_chunk_bbox64) SBO_CUDA(ctx, cudaMalloc(&ctx->d_chunk_bbox64, sizeof(double4) * (size_t)(ctx->n_cap / 64 + 1)));
+    chunk_bbox_f64_kernel<<<(nchunks * 32 + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_xy, ctx->n, nchunks,
+                                                                                 static_cast<double4*>(ctx->d_chunk_bbox64));
+    SBO_LAUNCH_CHECK(ctx, "chunk_bbox_f64_kernel");
+    p.bbox = static_cast<const double4*>(ctx->d_chunk_bbox64);
+    const double bits = f64_skip_bits_of(ctx->cfg, ctx->n, ctx->linv_r1);
+    p.skip_r2 = (bits + 0.5) * 0.6931471805599453 * 2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale;
+  }
+  if (ctx->d_exec_cols && !accumulate) SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_exec_cols, 0, sizeof(unsigned long long), ctx->stream));
   if (!ctx->attr_f64) {   // the attribute is per device: kept per context, not in a process-wide flag
     SBO_CUDA(ctx, cudaFuncSetAttribute(posterior_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F64Smem)));
     ctx->attr_f64 = true;

@@ -388,6 +388,32 @@ def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, spread, n
     assert np.abs(out["1"][1] - out["0"][1]).max() <= 1e-6
 
 
+@pytest.mark.parametrize("spread,n", [(1.0, 900), (6.0, 1500), (14.0, 2100)])
+def test_f64_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, spread, n):
+    """fp64 mode walks the same 64-observation chunk boxes as the tcgen05 kernel (posterior_f64.cu), with a cut-off that
+    keeps the left-out terms under 1e-12 sigma_f^2: results must meet the oracle at the fp64 tolerance and agree with the
+    dense walk (SBO_OPT_TC_SKIP = 0) far below it; on a stretched domain most stages, whole row blocks and for some
+    tiles everything is left out, and the executed-flop counter must say so."""
+    p = S.make_problem("C3", n=n, W=200, H=9)
+    p.xy = p.xy * spread
+    p.rx, p.ry = p.rx * spread, p.ry * spread * 9.0
+    ref = reference(oracle, coracle, p)
+    out = {}
+    for skip in (1, 0):
+        with make_ctx(pkg, p, precision="fp64", options={"tc_skip": skip}) as ctx:
+            ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+            ctx.set_observations(p.xy, p.y)
+            res, mask = ctx.step(p.beta, p.f_min)
+            assert res.kernel_used == 4
+            out[skip] = (ctx.mu(), ctx.sigma2(), ctx.tc_executed_flops(), res.ms_posterior)
+            band = check_step(p, ref, res, mask, out[skip][0], out[skip][1], "fp64", label=f"f64 spread {spread} skip={skip}")
+            check_argmax(res, ref, band, mask, p.f_min)
+    print(f"    executed flops: skipping {out[1][2]:.3e}, dense {out[0][2]:.3e}; ms {out[1][3]:.3f} vs {out[0][3]:.3f}")
+    assert np.abs(out[1][0] - out[0][0]).max() <= 1e-11 * max(1.0, np.abs(ref["mu"]).max())
+    assert np.abs(out[1][1] - out[0][1]).max() <= 1e-11
+    assert out[1][2] <= out[0][2] and (spread < 6.0 or out[1][2] < 0.7 * out[0][2])
+
+
 @pytest.mark.parametrize("n,phases", [(2100, 2), (2100, 5), (1300, 3)])
 def test_phased_refresh_bit_identical(pkg, n, phases):
     """SBO_OPT_TC_PHASES: the full refresh of the block-sparse walk as several launches over consecutive row-block pair
