@@ -243,6 +243,7 @@ int32_t tc_pack_observations(sbo_ctx* ctx, cudaStream_t stream = nullptr);      
 
 // posterior_thin.cu
 int32_t launch_posterior_f64(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate);   // fp64 mode, DMMA
+int32_t f64_chunk_boxes(sbo_ctx* ctx, int max_chunks, const void** boxes, double* skip_r2);   // posterior_f64.cu: chunk boxes + reach of the fp64 block-sparse walk
 int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo);   // incremental step, n - row_lo <= kThinMaxRows
 
 // frontier.cu

@@ -326,6 +326,25 @@ posterior_f64_kernel(F64Params p, double* __restrict__ mu_out, double* __restric
 
 }  // namespace
 
+// Block-sparse walk of the fp64 kernels: boxes of the 64-observation chunks (the observations are spatially ordered in
+// every precision; appended ones sit behind in arrival order, their chunks simply have large boxes) and the squared reach
+// beyond which K* < 2^-bits sigma_f^2 (bits: plan.cu f64_skip_bits_of, from the measured row norm of L^-1).  *boxes = null:
+// dense walk (switched off, few observations, or more chunks than the caller's mask holds).
+int32_t f64_chunk_boxes(sbo_ctx* ctx, int max_chunks, const void** boxes, double* skip_r2) {
+  *boxes = nullptr;
+  *skip_r2 = 0.0;
+  const int nchunks = (ctx->n + 63) / 64;
+  if (!ctx->tc_skip || ctx->n < 512 || nchunks > max_chunks) return SBO_OK;
+  if (!ctx->d_chunk_bbox64) SBO_CUDA(ctx, cudaMalloc(&ctx->d_chunk_bbox64, sizeof(double4) * (size_t)(ctx->n_cap / 64 + 1)));
+  chunk_bbox_f64_kernel<<<(nchunks * 32 + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_xy, ctx->n, nchunks,
+                                                                               static_cast<double4*>(ctx->d_chunk_bbox64));
+  SBO_LAUNCH_CHECK(ctx, "chunk_bbox_f64_kernel");
+  *boxes = ctx->d_chunk_bbox64;
+  const double bits = f64_skip_bits_of(ctx->cfg, ctx->n, ctx->linv_r1);
+  *skip_r2 = (bits + 0.5) * 0.6931471805599453 * 2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale;
+  return SBO_OK;
+}
+
 int32_t launch_posterior_f64(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) {
   if (ctx->cfg.precision != SBO_FP64) return fail(ctx, SBO_ERR_STATE, "posterior_f64: context is not in fp64 mode");
   if (ctx->m_local == 0) return SBO_OK;
@@ -341,21 +360,10 @@ int32_t launch_posterior_f64(sbo_ctx* ctx, int j_lo, int j_hi, bool accumulate) 
   p.inv2l2 = 1.0 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale);
   p.prior_mean = ctx->cfg.prior_mean;
   if (p.ld % 2 != 0) return fail(ctx, SBO_ERR_STATE, "posterior_f64: odd leading dimension of L^-1");
-  // block-sparse walk: boxes of the 64-observation chunks (the observations are spatially ordered in every precision) and
-  // the reach beyond which K* < 2^-bits sigma_f^2 (bits: plan.cu, from the measured row norm of L^-1)
-  p.bbox = nullptr;
-  p.skip_r2 = 0.0;
   p.exec_stages = ctx->d_exec_cols;
-  const int nchunks = (ctx->n + 63) / 64;
-  if (ctx->tc_skip && ctx->n >= 512 && nchunks <= FT) {
-    if (!ctx->d_chunk_bbox64) SBO_CUDA(ctx, cudaMalloc(&ctx->d_chunk_bbox64, sizeof(double4) * (size_t)(ctx->n_cap / 64 + 1)));
-    chunk_bbox_f64_kernel<<<(nchunks * 32 + 255) / 256, 256, 0, ctx->stream>>>(ctx->d_xy, ctx->n, nchunks,
-                                                                                 static_cast<double4*>(ctx->d_chunk_bbox64));
-    SBO_LAUNCH_CHECK(ctx, "chunk_bbox_f64_kernel");
-    p.bbox = static_cast<const double4*>(ctx->d_chunk_bbox64);
-    const double bits = f64_skip_bits_of(ctx->cfg, ctx->n, ctx->linv_r1);
-    p.skip_r2 = (bits + 0.5) * 0.6931471805599453 * 2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale;
-  }
+  const void* boxes = nullptr;
+  SBO_TRY(f64_chunk_boxes(ctx, FT, &boxes, &p.skip_r2));
+  p.bbox = static_cast<const double4*>(boxes);
   if (ctx->d_exec_cols && !accumulate) SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_exec_cols, 0, sizeof(unsigned long long), ctx->stream));
   if (!ctx->attr_f64) {   // the attribute is per device: kept per context, not in a process-wide flag
     SBO_CUDA(ctx, cudaFuncSetAttribute(posterior_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(F64Smem)));

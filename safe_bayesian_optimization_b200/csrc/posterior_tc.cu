@@ -1268,6 +1268,7 @@ bool tc_inc_applicable(sbo_ctx* ctx, int k) {
   const bool off = !ctx->opt.tc_inc;
   if (off || !ctx->tc_ok || ctx->tc_cg != 2 || ctx->cfg.precision != SBO_FP32 || !g_encode_tiled) return false;
   if (k < 1 || k > 16 || ctx->m_local == 0 || ctx->n < 1) return false;
+  if ((ctx->n + BK - 1) / BK > kMaskWords * 32) return false;   // chunk mask capacity (32 768 observations)
   int lq, nslabs;
   long long nitems;
   tc_inc_shape(ctx, k, &lq, &nslabs, &nitems);
@@ -1307,6 +1308,10 @@ int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo) {
   p.n = ctx->n; p.row_lo = row_lo; p.k = k;
   p.W = ctx->W; p.rows_local = ctx->row1 - ctx->row0;
   p.x0 = ctx->x0; p.rx = ctx->rx;
+  p.y0 = ctx->y0; p.ry = ctx->ry; p.row0 = ctx->row0;
+  p.bbox = reinterpret_cast<const float4*>(ctx->d_chunk_bbox);   // written by tc_pack_observations above
+  p.skip = (ctx->tc_skip && ctx->n >= 8 * BK) ? 1 : 0;           // block-sparse walk of the items (posterior_tc_inc.cuh)
+  p.skip_bits = tc_skip_bits(ctx);
   p.xscale = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
   p.a_scale = (float)std::ldexp(ctx->cfg.sigma_f * ctx->cfg.sigma_f, ctx->shift_a);
   p.u_unscale = std::ldexp(1.0, -(ctx->shift_a + ctx->shift_b));

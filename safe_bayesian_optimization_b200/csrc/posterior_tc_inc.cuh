@@ -28,7 +28,40 @@ struct IncParams {
   int tiles_x;         // 128-column tiles per grid row
   int rp;              // rows of P (multiple of 256); the lo plane starts at row rp of the tensor map
   int lr_base;         // first (local) grid row of this band: P is generated and contracted band by band to bound its size
+  // block-sparse walk: an item (256 grid columns x 256 / KP grid rows) only visits the 64-observation chunks within reach
+  double y0, ry;       // grid rows in the caller's coordinates (x0, rx above)
+  int row0;            // first grid row of this shard
+  const float4* bbox;  // [nchunks] scaled chunk boxes (chunk_bbox_kernel)
+  int skip;            // 0: every chunk
+  float skip_bits;     // chunks whose K* entries are all < 2^-skip_bits sigma_f^2 for the whole item are left out
 };
+
+// Chunk mask of one work item (every role of both CTAs derives the same bits: one compiled copy, as build_chunk_mask).
+// u_q = sum_j ex ey Linv[q][j]: a left-out term is < 2^-bits sigma_f^2 |Linv[q][j]|, so |du| < 2^-bits sigma_f^2 R1 and
+// sigma^2 -= u^2 moves by < 2 sigma_f du -- with the full refresh's cut-off (36 bits at C4) 4e-10 sigma_f^2 per step,
+// 1e-7 over the 256 steps between two refreshes.
+__device__ __noinline__ void build_item_mask(uint32_t* mask, const IncParams p, int col_first, int col_last, int lr_first,
+                                             int lr_last, int nchunks) {
+  const int lane = threadIdx.x & 31;
+  const double xa = cell_coord(p.x0, p.rx, col_first) * p.xscale, xb = cell_coord(p.x0, p.rx, col_last) * p.xscale;
+  const double ya = cell_coord(p.y0, p.ry, p.row0 + lr_first) * p.xscale, yb = cell_coord(p.y0, p.ry, p.row0 + lr_last) * p.xscale;
+  const float xlo = (float)fmin(xa, xb) - 1e-3f, xhi = (float)fmax(xa, xb) + 1e-3f;   // margin: the box test runs in fp32
+  const float ylo = (float)fmin(ya, yb) - 1e-3f, yhi = (float)fmax(ya, yb) + 1e-3f;
+  __syncwarp();  // the previous item's walks of this warp's mask are over
+#pragma unroll 1
+  for (int w = 0; w < kMaskWords; ++w) {
+    const int c = w * 32 + lane;
+    bool on = c < nchunks;
+    if (on && p.skip) {
+      const float4 b = p.bbox[c];
+      const float dx = fmaxf(fmaxf(b.x - xhi, xlo - b.y), 0.f), dy = fmaxf(fmaxf(b.z - yhi, ylo - b.w), 0.f);
+      on = __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) <= p.skip_bits + 0.5f;
+    }
+    const uint32_t bits = __ballot_sync(0xffffffffu, on);
+    if (lane == 0) mask[w] = bits;
+  }
+  __syncwarp();
+}
 
 // fp16 hi/lo planes of P: row rho = lr * KP + q holds 2^shift_b ey(lr, j) Linv[row_lo + q][j]  (sigma_f^2 rides on A).
 // One thread per (grid row, observation): the fp64 exp is computed once and serves the KP rows of that grid row.
@@ -77,6 +110,13 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
   const long long nitems = (long long)p.nslabs * ncp;        // item = slab * ncp + column pair: neighbours share the slab's P tiles
   const long long group = blockIdx.x / CG, ngroups = gridDim.x / CG;
   const int nchunks = (p.n + BK - 1) / BK;
+  uint32_t* cmask = sh->cmask[warp];
+  auto item_mask = [&](long long item) {   // the chunks this item visits (all of them when p.skip == 0)
+    const int sb = (int)(item / ncp), cp = (int)(item % ncp);
+    const int lr_first = min(p.lr_base + ((sb * BN) >> LQ), p.rows_local - 1);
+    const int lr_last = min(p.lr_base + (((sb + 1) * BN) >> LQ) - 1, p.rows_local - 1);
+    build_item_mask(cmask, p, 2 * cp * BM, min(2 * cp * BM + 2 * BM, p.W) - 1, lr_first, lr_last, nchunks);
+  };
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -101,7 +141,10 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
     for (long long item = group; item < nitems; item += ngroups) {
       const int sb = (int)(item / ncp);
       const int row = sb * BN + (int)rank * (int)Cfg::kBRows;
-      for (int kc = 0; kc < nchunks; ++kc, ++it) {
+      item_mask(item);
+      ChunkIter<true> ci;
+      ci.reset(cmask);
+      for (int kc = ci.next(); kc < nchunks; kc = ci.next(), ++it) {
         const int s = it % kStages;
         const uint32_t ph = (it / kStages) & 1u;
         mbar_wait(&sh->empty[s], ph ^ 1u);
@@ -118,13 +161,20 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
     // =============================== MMA issuer (leader CTA) ===============================
     uint32_t it = 0, acc_it = 0;
     for (long long item = group; rank == 0 && item < nitems; item += ngroups) {
+      item_mask(item);
+      ChunkIter<true> ci;
+      ci.reset(cmask);
+      int kc = ci.next();
+      if (kc >= nchunks) continue;   // nothing within reach: u = 0, the epilogue skips the item too
       const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
       ++acc_it;
       mbar_wait(&sh->tmem_empty[as], aph ^ 1u);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + as * BN;
       const uint32_t idesc = idesc_f16<CG>(BN);
-      for (int kc = 0; kc < nchunks; ++kc, ++it) {
+      bool first = true;
+      for (int kn; kc < nchunks; kc = kn, ++it, first = false) {
+        kn = ci.next();   // the next visited chunk: tells whether this visit is the item's last
         const int s = it % kStages;
         mbar_wait(&sh->full[s], (it / kStages) & 1u);
         tc_fence_after();
@@ -134,12 +184,12 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
 #pragma unroll
           for (int ks = 0; ks < BK / UK; ++ks) {
             const uint64_t adv = (uint64_t)((ks * UK * 2) >> 4);
-            umma_f16<CG>(d_tmem, dal + adv, dbh + adv, idesc, (kc == 0 && ks == 0) ? 0u : 1u);
+            umma_f16<CG>(d_tmem, dal + adv, dbh + adv, idesc, (first && ks == 0) ? 0u : 1u);
             umma_f16<CG>(d_tmem, dah + adv, dbl + adv, idesc, 1u);
             umma_f16<CG>(d_tmem, dah + adv, dbh + adv, idesc, 1u);
           }
           umma_commit<CG>(&sh->empty[s]);
-          if (kc == nchunks - 1) umma_commit<CG>(&sh->tmem_full[as]);
+          if (kn >= nchunks) umma_commit<CG>(&sh->tmem_full[as]);
         }
         __syncwarp();
       }
@@ -157,6 +207,12 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
       const int sb = (int)(item / ncp), ct = 2 * (int)(item % ncp) + (int)rank;
       const int col = ct * BM + c;
       const bool live = ct < p.tiles_x && col < p.W;
+      {
+        item_mask(item);
+        ChunkIter<true> ci;
+        ci.reset(cmask);
+        if (ci.next() >= nchunks) continue;   // no chunk within reach of this item: nothing was accumulated, nothing changes
+      }
       const uint32_t as = acc_it & 1u, aph = (acc_it >> 1) & 1u;
       ++acc_it;
       mbar_wait(&sh->tmem_full[as], aph);
@@ -210,18 +266,24 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
       const int ct = min(2 * (int)(item % ncp) + (int)rank, p.tiles_x - 1);  // an odd last column tile: the peer regenerates it
       const double ox0 = cell_coord(p.x0, p.rx, ct * BM) * p.xscale;
       const float oxh = (float)ox0, oxl = (float)(ox0 - (double)oxh);
-      for (int kc = 0; kc < nchunks; ++kc, ++it) {
+      item_mask(item);
+      ChunkIter<true> ci, scout;
+      ci.reset(cmask);
+      scout.reset(cmask);
+      scout.next();
+      scout.next();
+      for (int kc = ci.next(); kc < nchunks; kc = ci.next(), ++it) {
+        const int kn = scout.next();   // the chunk two visits ahead = this warp's next visit inside the item
         if ((it & 1u) != (uint32_t)grp) continue;
         const int s = it % kStages;
         const uint32_t ph = (it / kStages) & 1u;
         {
           const int kobs = kc * BK + oh * 32 + lane;
-          if (c_next != kc) o_next = p.obs[kobs];
+          if (c_next != kc) o_next = p.obs[kobs];   // (first visits of an item: the look-ahead does not cross items)
           ox[lane] = (o_next.x - oxh) + (o_next.y - oxl);
           oy[lane] = kobs < p.n ? p.a_scale : 0.f;
-          c_next = kc + 2 < nchunks ? kc + 2 : kc + 2 - nchunks;   // this warp's next visit (the next item starts at chunk 0 again)
-          if (c_next >= nchunks) c_next = 0;                        // (a single chunk)
-          o_next = p.obs[c_next * BK + oh * 32 + lane];
+          c_next = kn < nchunks ? kn : -1;
+          if (c_next >= 0) o_next = p.obs[c_next * BK + oh * 32 + lane];
         }
         __syncwarp();
         uint8_t* pa_hi = a_hi(s) + row_off;

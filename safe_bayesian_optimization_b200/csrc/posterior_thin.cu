@@ -43,6 +43,8 @@ struct ThinParams {
   double x0, y0, rx, ry;
   double xscale;           // fp32 mode: sqrt(log2(e) / 2 l^2)
   double sf2, inv2l2, prior_mean;
+  const double4* bbox;     // fp64 2-D tile kernel: boxes of the 64-observation chunks (null: every chunk is staged)
+  double skip_r2;          // ... and the squared reach beyond which a chunk is left out for a tile
 };
 
 __device__ __forceinline__ float ex2f(float x) {
@@ -245,6 +247,7 @@ posterior_thin2d_f64_kernel(ThinParams p, double* __restrict__ mu_out, double* _
   extern __shared__ __align__(16) double sm2[];
   double* a_s = sm2;                        // [kT2Chunk][kT2Ld]
   double* b_s = sm2 + kT2Chunk * kT2Ld;     // [kT2Chunk][kT2Ld]
+  __shared__ uint32_t cmask[kThinThreads / 32];   // 256 chunks = 16 384 observations
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int sg = tid & 7, jj = tid >> 3;    // staging role: observation jj of the chunk, cells sg + 8 i of the tile edge
   const int tiles_x = (p.W + kT2 - 1) / kT2, tiles_y = (p.rows_local + kT2 - 1) / kT2;
@@ -256,6 +259,21 @@ posterior_thin2d_f64_kernel(ThinParams p, double* __restrict__ mu_out, double* _
 
   for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int r0 = (int)(tile / tiles_x) * kT2, col0 = (int)(tile % tiles_x) * kT2;
+    if (p.bbox) {   // chunks within reach of this 128 x 128 patch (same box test and cut-off as posterior_f64.cu)
+      __syncthreads();   // the previous tile's reads of the mask are over
+      bool on = tid < (p.n + 63) / 64;
+      if (on) {
+        const double xa = cell_coord(p.x0, p.rx, col0), xb = cell_coord(p.x0, p.rx, min(col0 + kT2, p.W) - 1);
+        const double ya = cell_coord(p.y0, p.ry, p.row0 + r0), yb = cell_coord(p.y0, p.ry, p.row0 + min(r0 + kT2, p.rows_local) - 1);
+        const double4 b = p.bbox[tid];
+        const double dx = fmax(fmax(b.x - fmax(xa, xb), fmin(xa, xb) - b.y), 0.0);
+        const double dy = fmax(fmax(b.z - fmax(ya, yb), fmin(ya, yb) - b.w), 0.0);
+        on = dx * dx + dy * dy <= p.skip_r2;
+      }
+      const uint32_t bits = __ballot_sync(0xffffffffu, on);
+      if ((tid & 31) == 0) cmask[tid >> 5] = bits;
+      __syncthreads();
+    }
     const double cx0 = cell_coord(p.x0, p.rx, col0 + sg), cy0 = cell_coord(p.y0, p.ry, p.row0 + r0 + sg);
     double acc[8][8];
 #pragma unroll
@@ -264,6 +282,7 @@ posterior_thin2d_f64_kernel(ThinParams p, double* __restrict__ mu_out, double* _
       for (int c = 0; c < 8; ++c) acc[r][c] = 0.0;
 
     for (int k0 = 0; k0 < p.n; k0 += kT2Chunk) {
+      if (p.bbox && !((cmask[k0 >> 11] >> ((k0 >> 6) & 31)) & 1u)) continue;   // out of reach: K* < 2^-bits sigma_f^2 for the whole patch
       {
         const int j = k0 + jj;
         double ox = 0.0, oy = 0.0, ol = 0.0;  // observations beyond n: Linv = 0, so b = 0
@@ -343,6 +362,8 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
   const int k_new = ctx->n - row_lo;
   if (k_new < 0 || k_new > kThinMaxRows) return fail(ctx, SBO_ERR_STATE, "posterior_thin: more than 8 new rows");
   ThinParams p;
+  p.bbox = nullptr;
+  p.skip_r2 = 0.0;
   p.obs_f32 = reinterpret_cast<const float4*>(ctx->d_obs_f32);
   p.xy = ctx->d_xy; p.Linv = ctx->d_Linv; p.w = ctx->d_w;
   p.n = ctx->n; p.ld = ctx->n_cap; p.row_lo = row_lo; p.k_new = k_new;
@@ -364,7 +385,12 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
   } else {
     const long long tiles2d = (long long)((p.W + kT2 - 1) / kT2) * ((p.rows_local + kT2 - 1) / kT2);
     const bool span_ok = kT2 * std::max(std::fabs(p.rx), std::fabs(p.ry)) <= 4.0 * ctx->cfg.length_scale;  // see the staging recurrence
+    p.bbox = nullptr;
+    p.skip_r2 = 0.0;
     if (kr == 1 && tiles2d >= ctx->sm_count && span_ok && ctx->opt.thin_2d) {   // enough 128 x 128 tiles for every SM
+      const void* boxes = nullptr;
+      SBO_TRY(f64_chunk_boxes(ctx, kThinThreads, &boxes, &p.skip_r2));
+      p.bbox = static_cast<const double4*>(boxes);
       const size_t smem = (size_t)2 * kT2Chunk * kT2Ld * sizeof(double);
       // per device, so not cached in a process-wide flag (a process may hold contexts on several GPUs); a few microseconds
       const cudaError_t ea = cudaFuncSetAttribute(posterior_thin2d_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -363,6 +363,36 @@ def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, precision):
     assert np.abs(out["1"][0] - mu_f).max() <= loose * scale and np.abs(out["1"][1] - s2_f).max() <= loose
 
 
+def test_thin_2d_tile_kernel_block_sparse(pkg):
+    """fp64 steady state on a domain wider than the kernel's reach: the 2-D tile kernel stages only the 64-observation
+    chunks within reach of its 128 x 128 patch (posterior_thin.cu; cut-off of posterior_f64.cu).  Against the same kernel
+    walking every chunk (SBO_OPT_TC_SKIP = 0) and against a full refresh."""
+    n0, spread = 700, 4.0
+    p = S.make_problem("C5", n=n0 + 3, W=1990, H=1250)
+    p.xy = p.xy * spread
+    p.rx, p.ry = p.rx * spread, p.ry * spread
+    out = {}
+    for skip in (1, 0):
+        with make_ctx(pkg, p, precision="fp64", max_obs=n0 + 3, options={"tc_skip": skip}) as ctx:
+            ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
+            ctx.set_observations(p.xy[:n0], p.y[:n0])
+            ctx.step(p.beta, p.f_min, want_mask=False)
+            ms = []
+            for t in range(3):
+                ctx.append_observations(p.xy[n0 + t:n0 + t + 1], p.y[n0 + t:n0 + t + 1])
+                res, _ = ctx.step(p.beta, p.f_min, incremental=True, want_mask=False)
+                assert res.kernel_used == 3
+                ms.append(res.ms_posterior)
+            out[skip] = (ctx.mu(), ctx.sigma2(), min(ms))
+            if skip:
+                ctx.step(p.beta, p.f_min, want_mask=False)
+                mu_f, s2_f = ctx.mu(), ctx.sigma2()
+    print(f"    incremental posterior ms: block-sparse {out[1][2]:.3f}, every chunk {out[0][2]:.3f}")
+    scale = np.abs(mu_f).max()
+    assert np.abs(out[1][0] - out[0][0]).max() <= 1e-12 * scale and np.abs(out[1][1] - out[0][1]).max() <= 1e-12
+    assert np.abs(out[1][0] - mu_f).max() <= 1e-10 * scale and np.abs(out[1][1] - s2_f).max() <= 1e-10
+
+
 @pytest.mark.parametrize("spread,n", [(1.0, 1500), (4.0, 1500), (12.0, 1500), (4.0, 1100), (12.0, 2100)])  # 6, 5 and 9 row blocks
 def test_chunk_skipping_matches_oracle_and_dense(pkg, oracle, coracle, spread, n):
     """The tcgen05 kernel leaves out 64-observation chunks whose K* entries are all < 2^-b sigma_f^2 for a cell tile (b from tc_skip_bits: sigma^2 moves by < 1e-7 sigma_f^2)
