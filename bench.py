@@ -369,7 +369,7 @@ def run_workload(h: Harness, name: str, steps: int, warmup: int, primary: bool, 
 
     ctx = pkg.SboContext(sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean,
                          precision=p.precision, kernel=args.kernel, device=h.local_rank,
-                         max_obs=p.n + k_inc * (inc_steps + 2), max_cells=max(m_local, 1))
+                         max_obs=p.n + k_inc * (inc_steps + min(inc_steps, 10) + 4), max_cells=max(m_local, 1))
     for kv in filter(None, args.options.split(",")):
         k, v = kv.split("=")
         ctx.set_option(k, int(v))
@@ -507,6 +507,26 @@ def run_workload(h: Harness, name: str, steps: int, warmup: int, primary: bool, 
         dm = float(np.abs(mu_i - mu_f).max() / max(1.0, np.abs(mu_f).max())); ds = float(np.abs(s2_i - s2_f).max() / p.sigma_f ** 2)
         incremental["end_parity"] = {"vs": "full refresh (refit not needed: same factor) of the same observations on the GPU",
                                      "mu_rel_max": h.max_over_ranks(dm), "s2_abs_max_over_sf2": h.max_over_ranks(ds)}
+    # the same loop with SBO_OPT_MASK_DELTA: only the 64 KiB mask segments in which a byte changed travel to the host
+    # (the warm-up step is the one full copy that makes mask_host the mirror of the device mask)
+    ctx.set_option("mask_delta", 1)
+    d2h_delta = []
+
+    def inc_step_delta():
+        out = inc_step()
+        d2h_delta.append(ctx.mask_copy_info())
+        return out
+    inc2 = min(inc_steps, 10)
+    ms_d_total, d_outs, _, d_per = h.timed_loop(inc_step_delta, inc2, 1)
+    d_per = np.array(d_per)
+    incremental["changed_segments_only"] = {
+        "option": "SBO_OPT_MASK_DELTA = 1 (opt-in: the caller keeps the previous mask in the same host buffer)",
+        "steps": inc2, "ms_per_step": ms_d_total / inc2, "p50_ms": float(np.percentile(d_per, 50)),
+        "p99_ms": float(np.percentile(d_per, 99)),
+        "mask_d2h_bytes_per_step": float(np.mean([b for b, _ in d2h_delta[1:]])), "mask_bytes_full": int(m_local),
+        "copies_per_step": float(np.mean([r for _, r in d2h_delta[1:]])),
+        "mask_equals_device_mask": bool(np.array_equal(mask_host, ctx.mask()))}
+    ctx.set_option("mask_delta", 0)
     n_after = ctx.n_obs
     ctx.close()
 

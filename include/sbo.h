@@ -36,7 +36,8 @@ extern "C" {
 #endif
 
 #define SBO_ABI_VERSION 2   /* 2: sbo_step_out gained low_sigma2 / refreshed / drift; options; row-band planner; device groups.
-                               Additive since (same version): sbo_fit_info, SBO_OPT_DIST_FIT, SBO_OPT_TC_PHASES, sbo_compute_sets_noalloc */
+                               Additive since (same version): sbo_fit_info, SBO_OPT_DIST_FIT, SBO_OPT_TC_PHASES, sbo_compute_sets_noalloc,
+                               SBO_OPT_MASK_DELTA, sbo_mask_copy_info */
 
 typedef enum {
   SBO_OK = 0,
@@ -155,9 +156,19 @@ typedef enum {
                                     order, one panel broadcast per step, one all-gather of L^-1 at the end -- bit-identical
                                     to the replicated fit.  2 (default): from 8192 observations on; 1: always; 0: never.
                                     Every rank must hold the same value and call sbo_set_observations with the same data  */
-  SBO_OPT_TC_PHASES = 14         /* full refresh of the block-sparse walk as this many launches over consecutive row-block
+  SBO_OPT_TC_PHASES = 14,        /* full refresh of the block-sparse walk as this many launches over consecutive row-block
                                     pair ranges (running row sums carried between them, bit-identical): keeps the rows of
                                     L^-1 in flight inside the L2.  0 (default): by size (1 below 8192 observations)         */
+  SBO_OPT_MASK_DELTA = 15        /* 0 (default): every step copies its whole mask to `mask_host`.  1: a step given the SAME
+                                    `mask_host` as the step before (same grid / band) copies only the 64 KiB segments of the
+                                    mask in which a byte changed since that copy -- the CI / mask pass compares against the
+                                    previous mask and raises one flag per segment.  The caller must leave the buffer as the
+                                    library wrote it between the two calls (the reference rebuilds S_ and its image every
+                                    step, :409, :444-456; this is its steady state without the 1 byte/cell transfer: after one
+                                    new observation the mask changes near that observation only).  The first step, a step
+                                    with another buffer, or one after sbo_set_grid / sbo_compute_sets copies everything.
+                                    Steps without a host buffer (sbo_step_device) keep accumulating flags.  Costs one byte
+                                    read per cell in the pass and one extra stream synchronisation per step.              */
 } sbo_option;
 int32_t sbo_set_option(sbo_ctx* ctx, int32_t option, int32_t value);
 int32_t sbo_get_option(const sbo_ctx* ctx, int32_t option, int32_t* value);
@@ -206,6 +217,10 @@ int32_t sbo_copy_alpha(sbo_ctx* ctx, double* host_dst);
  * ComputeSets (:399-416) + the rasterise loop of FindSafetyContourIndices
  * (:444-456). */
 int32_t sbo_step(sbo_ctx* ctx, double beta, double f_min, uint8_t* mask_host, sbo_step_out* out);
+/* Mask bytes the last sbo_step / sbo_step_incremental of this context copied to the host, and in how many contiguous
+ * runs (1 run of n_cells bytes unless SBO_OPT_MASK_DELTA is on; 0 / 0 when nothing changed or mask_host was NULL).
+ * replaces: nothing (bookkeeping for the changed-segment copy). */
+int32_t sbo_mask_copy_info(const sbo_ctx* ctx, int64_t* bytes, int32_t* runs);
 
 /* Same step after a rank-k append, in O(m n k): only the k newest rows of
  * L^-1 are contracted (sigma^2 -= |rows_new k*|^2) and mu is recomputed with

@@ -19,7 +19,7 @@ SBO_KERNEL_AUTO, SBO_KERNEL_SIMT, SBO_KERNEL_TCGEN05 = 0, 1, 2
 # sbo_option
 OPTIONS = {"tc_cta_group": 1, "tc_skip": 2, "tc_pair": 3, "tc_eager": 4, "tc_inc": 5, "thin": 6, "thin_2d": 7, "tc_graded": 8,
            "tc_strip": 9, "refresh_every": 10, "drift_check_every": 11, "drift_rows": 12,
-           "dist_fit": 13, "tc_phases": 14}
+           "dist_fit": 13, "tc_phases": 14, "mask_delta": 15}
 
 SBO_OK = 0
 SBO_ERR_INVALID_ARG, SBO_ERR_NO_DEVICE, SBO_ERR_CUDA, SBO_ERR_NOT_POSDEF = -1, -2, -3, -4
@@ -75,6 +75,7 @@ SYMBOLS = {
     "sbo_append_observations": (C.c_int32, [_P, _D, _D, C.c_int32]),
     "sbo_num_observations": (C.c_int32, [_P]),
     "sbo_fit_info": (C.c_int32, [_P, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
+    "sbo_mask_copy_info": (C.c_int32, [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "sbo_copy_order": (C.c_int32, [_P, C.POINTER(C.c_int32)]),
     "sbo_copy_linv": (C.c_int32, [_P, _D]),
     "sbo_copy_alpha": (C.c_int32, [_P, _D]),

@@ -40,11 +40,13 @@ void free_all(sbo_ctx* c) {
   void* dev[] = {c->d_xy, c->d_r, c->d_A, c->d_Linv, c->d_Dinv, c->d_alpha, c->d_w, c->d_small, c->d_info,
                  c->d_planes, c->d_alpha_f32, c->d_obs_f32, c->d_chunk_bbox, c->d_exec_cols, c->d_fr_img, c->d_fr_lut, c->d_cp_idx, c->d_cp_counts, c->d_mu, c->d_s2, c->d_mask, c->d_mu64, c->d_std64, c->d_q0, c->d_q1,
                  c->d_partials, c->d_result, c->d_ticket, c->d_frontier, c->d_sel_keys, c->d_sel_width, c->d_sel_out,
-                 c->d_gather, c->d_chunk_bbox64, c->d_drift_mu, c->d_drift_s2, c->d_drift_out, c->d_fit_stage, c->d_fit_send, c->d_fit_recv};
+                 c->d_gather, c->d_chunk_bbox64, c->d_drift_mu, c->d_drift_s2, c->d_drift_out, c->d_fit_stage, c->d_fit_send, c->d_fit_recv,
+                 c->d_mask_dirty};
   for (void* p : dev)
     if (p) cudaFree(p);
   if (c->h_result) cudaFreeHost(c->h_result);
   if (c->h_sel_out) cudaFreeHost(c->h_sel_out);
+  if (c->h_mask_dirty) cudaFreeHost(c->h_mask_dirty);
   for (auto& e : c->ev)
     if (e) cudaEventDestroy(e);
   for (auto& e : c->ev_factor) cudaEventDestroy(e);
@@ -421,6 +423,7 @@ int32_t sbo_set_grid(sbo_ctx* ctx, double x0, double y0, double rx, double ry, i
   ctx->tc_skip_plan = -1;
   ctx->posterior_valid = false;
   ctx->source = PosteriorSource::kNone;
+  ctx->mask_mirror = nullptr;   // another shard / layout: the next step copies the whole mask
   return SBO_OK;
 }
 
@@ -452,6 +455,7 @@ static int* option_slot(sbo_ctx* c, int32_t option) {
     case SBO_OPT_DRIFT_ROWS: return &c->opt.drift_rows;
     case SBO_OPT_DIST_FIT: return &c->opt.dist_fit;
     case SBO_OPT_TC_PHASES: return &c->opt.tc_phases;
+    case SBO_OPT_MASK_DELTA: return &c->opt.mask_delta;
     default: return nullptr;
   }
 }
@@ -475,6 +479,17 @@ int32_t sbo_set_option(sbo_ctx* ctx, int32_t option, int32_t value) {
   }
   if (option == SBO_OPT_TC_EAGER && value == 0) tc_eager_cancel(ctx);
   if (option == SBO_OPT_TC_GRADED) ctx->tc_skip_plan = -1;
+  if (option == SBO_OPT_MASK_DELTA) {
+    ctx->mask_mirror = nullptr;   // flags were not kept while the option was off: the next step copies the whole mask
+    if (value && !ctx->d_mask_dirty) {
+      const size_t nseg = ((size_t)ctx->cfg.max_cells >> kMaskSegShift) + 2;
+      SBO_CUDA(ctx, cudaSetDevice(ctx->device));
+      SBO_CUDA(ctx, cudaMalloc(&ctx->d_mask_dirty, nseg * sizeof(unsigned int)));
+      SBO_CUDA(ctx, cudaMemset(ctx->d_mask_dirty, 0, nseg * sizeof(unsigned int)));
+      SBO_CUDA(ctx, cudaMallocHost(&ctx->h_mask_dirty, nseg * sizeof(unsigned int)));
+    }
+    value = value != 0;
+  }
   *slot = value;
   return SBO_OK;
 }
@@ -508,6 +523,13 @@ int32_t sbo_fit_info(const sbo_ctx* ctx, float* ms, int32_t* shared_ranks) {
   if (!ctx) return SBO_ERR_INVALID_ARG;
   if (ms) *ms = ctx->fit_ms;
   if (shared_ranks) *shared_ranks = ctx->fit_dist_used;
+  return SBO_OK;
+}
+
+int32_t sbo_mask_copy_info(const sbo_ctx* ctx, int64_t* bytes, int32_t* runs) {
+  if (!ctx) return SBO_ERR_INVALID_ARG;
+  if (bytes) *bytes = ctx->mask_copied_bytes;
+  if (runs) *runs = ctx->mask_copied_runs;
   return SBO_OK;
 }
 
@@ -738,13 +760,63 @@ int32_t sbo_copy_order(sbo_ctx* ctx, int32_t* host_dst) {
 // ---------------------------------------------------------------------------------------------
 // the BO step
 // ---------------------------------------------------------------------------------------------
+// The step's mask on its way to the host.  Default: the whole shard.  SBO_OPT_MASK_DELTA: when `mask_host` is the buffer
+// the previous copy went to (and the shard is the same), only the 64 KiB segments the sets pass flagged as changed since
+// then -- contiguous flagged segments travel as one copy; the flags accumulate on the device over steps that copy nothing
+// (sbo_step_device) and are cleared by the copy that consumes them.  One extra stream synchronisation (the flags).
+static int32_t copy_mask_out(sbo_ctx* ctx, uint8_t* mask_host) {
+  const size_t m = (size_t)ctx->m_local;
+  ctx->mask_copied_bytes = 0;
+  ctx->mask_copied_runs = 0;
+  if (!mask_host || m == 0) return SBO_OK;
+  if (!ctx->opt.mask_delta) {
+    SBO_CUDA(ctx, cudaMemcpyAsync(mask_host, ctx->d_mask, m, cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->mask_copied_bytes = (int64_t)m;
+    ctx->mask_copied_runs = 1;
+    return SBO_OK;
+  }
+  const size_t seg = (size_t)1 << kMaskSegShift, nseg = (m + seg - 1) >> kMaskSegShift;
+  const bool mirrored = ctx->mask_mirror == mask_host && ctx->mask_mirror_m == (int64_t)m;
+  ctx->mask_mirror = nullptr;   // until this copy is known to have completed (step_common)
+  if (!mirrored) {
+    SBO_CUDA(ctx, cudaMemcpyAsync(mask_host, ctx->d_mask, m, cudaMemcpyDeviceToHost, ctx->stream));
+    SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_mask_dirty, 0, nseg * sizeof(unsigned int), ctx->stream));
+    ctx->mask_copied_bytes = (int64_t)m;
+    ctx->mask_copied_runs = 1;
+    return SBO_OK;
+  }
+  SBO_CUDA(ctx, cudaMemcpyAsync(ctx->h_mask_dirty, ctx->d_mask_dirty, nseg * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
+  SBO_CUDA(ctx, cudaMemsetAsync(ctx->d_mask_dirty, 0, nseg * sizeof(unsigned int), ctx->stream));
+  SBO_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  size_t s = 0;
+  while (s < nseg) {
+    if (!ctx->h_mask_dirty[s]) { ++s; continue; }
+    size_t e = s + 1;
+    while (e < nseg && ctx->h_mask_dirty[e]) ++e;
+    const size_t off = s << kMaskSegShift, len = std::min(m, e << kMaskSegShift) - off;
+    SBO_CUDA(ctx, cudaMemcpyAsync(mask_host + off, ctx->d_mask + off, len, cudaMemcpyDeviceToHost, ctx->stream));
+    ctx->mask_copied_bytes += (int64_t)len;
+    ctx->mask_copied_runs++;
+    s = e;
+  }
+  return SBO_OK;
+}
+
 static int32_t step_common(sbo_ctx* ctx, double beta, double f_min, uint8_t* mask_host, sbo_step_out* out, bool incremental) {
   if (!ctx) return SBO_ERR_INVALID_ARG;
   int used = 0;
-  SBO_TRY(run_step(ctx, beta, f_min, incremental, &used));
-  if (mask_host && ctx->m_local > 0)
-    SBO_CUDA(ctx, cudaMemcpyAsync(mask_host, ctx->d_mask, (size_t)ctx->m_local, cudaMemcpyDeviceToHost, ctx->stream));
-  return finish_step(ctx, used, out);
+  const int32_t st = run_step(ctx, beta, f_min, incremental, &used);
+  if (st != SBO_OK) {
+    ctx->mask_mirror = nullptr;   // d_mask may or may not have been rewritten
+    return st;
+  }
+  SBO_TRY(copy_mask_out(ctx, mask_host));
+  SBO_TRY(finish_step(ctx, used, out));
+  if (ctx->opt.mask_delta && mask_host && ctx->m_local > 0) {   // the copy has completed: mask_host mirrors d_mask
+    ctx->mask_mirror = mask_host;
+    ctx->mask_mirror_m = ctx->m_local;
+  }
+  return SBO_OK;
 }
 
 int32_t sbo_step(sbo_ctx* ctx, double beta, double f_min, uint8_t* mask_host, sbo_step_out* out) {
@@ -786,6 +858,7 @@ int32_t sbo_compute_sets(sbo_ctx* ctx, const double* mu, const double* std_dev, 
     SBO_CUDA(ctx, cudaMemcpyAsync(ctx->d_std64, std_dev, sizeof(double) * (size_t)m, cudaMemcpyHostToDevice, ctx->stream));
   }
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  ctx->mask_mirror = nullptr;   // d_mask is rewritten without changed-segment flags
   SBO_TRY(launch_sets_arrays(ctx, ctx->d_mu64, ctx->d_std64, m, beta, f_min, ctx->d_mask, q0 ? ctx->d_q0 : nullptr,
                              q1 ? ctx->d_q1 : nullptr));
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
@@ -806,6 +879,7 @@ int32_t sbo_compute_sets_device(sbo_ctx* ctx, const double* mu_dev, const double
   SBO_CUDA(ctx, cudaSetDevice(ctx->device));
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  if (!mask_dev) ctx->mask_mirror = nullptr;   // d_mask is rewritten without changed-segment flags
   SBO_TRY(launch_sets_arrays(ctx, mu_dev, std_dev, m, beta, f_min, mask_dev ? mask_dev : ctx->d_mask, nullptr, nullptr));
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
   SBO_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));

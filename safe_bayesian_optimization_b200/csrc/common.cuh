@@ -36,7 +36,10 @@ struct Options {
   int drift_rows = 2;           // sample blocks per check (a block = 1 grid row; 8 rows for the DMMA kernel's 16 x 8 cell patches)
   int tc_phases = 0;            // full refresh in this many launches over consecutive row-block pair ranges (0: by size)
   int dist_fit = 2;             // fit shared between the ranks / group members: 0 never, 1 always, 2 from 8192 observations on
+  int mask_delta = 0;           // steps copy back only the mask segments that changed since the last copy into the same host buffer
 };
+
+constexpr int kMaskSegShift = 16;   // SBO_OPT_MASK_DELTA: one changed-flag per 2^16 cells (64 KiB of mask bytes)
 
 struct FitPeers;   // factor.cu: rendezvous of the members of a same-process group during a shared fit
 
@@ -122,6 +125,13 @@ struct sbo_ctx {
   void* d_mu = nullptr;      // [max_cells] float or double
   void* d_s2 = nullptr;      // [max_cells]
   uint8_t* d_mask = nullptr; // [max_cells]
+  // SBO_OPT_MASK_DELTA (api.cu: copy_mask_out): flags of the mask segments whose bytes changed since the host last received them
+  unsigned int* d_mask_dirty = nullptr;   // [max_cells >> kMaskSegShift, + 2] (allocated when the option is switched on)
+  unsigned int* h_mask_dirty = nullptr;   // pinned, same length
+  const uint8_t* mask_mirror = nullptr;   // the host buffer that holds d_mask as of the last copy (null: none / unknown)
+  int64_t mask_mirror_m = 0;              // m_local at that copy
+  int64_t mask_copied_bytes = 0;          // mask bytes the last step copied to the host
+  int32_t mask_copied_runs = 0;           // ... in this many contiguous runs (1: the whole mask)
   double* d_mu64 = nullptr;  // compute_sets staging (lazy) [max_cells]
   double* d_std64 = nullptr;
   double* d_q0 = nullptr;

@@ -711,6 +711,75 @@ append_t_kernel(const double* __restrict__ X, int ld, int n, int k, const double
   }
 }
 
+// One new row (the node's steady state appends one observation per step): the two passes over L^-1 above carry eight
+// predicated accumulators (78-80 registers, four 8-byte loads in flight per thread: ~24 KB per SM, 2.5 TB/s at
+// n = 16 384).  These keep eight 16-byte loads in flight per thread.  Entries beyond the diagonal are masked, not trusted.
+__global__ void __launch_bounds__(256)
+append_l21_one_kernel(const double* __restrict__ X, int ld, int n, const double* __restrict__ K21, double* __restrict__ L21) {
+  const int j = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (j >= n) return;
+  const double2* row = reinterpret_cast<const double2*>(X + (size_t)j * ld);
+  const double2* kk = reinterpret_cast<const double2*>(K21);
+  const int npairs = (j + 2) >> 1;   // double2 pairs that hold entries 0 .. j
+  double s0 = 0.0, s1 = 0.0;
+  int q = lane;
+  for (; q + 96 < npairs; q += 128) {   // four pairs of loads issued before the first use
+    double2 x[4], c[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { x[u] = __ldcs(row + q + 32 * u); c[u] = __ldg(kk + q + 32 * u); }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const bool in = 2 * (q + 32 * u) + 1 <= j;
+      s0 = fma(c[u].x, x[u].x, s0);
+      s1 = fma(in ? c[u].y : 0.0, in ? x[u].y : 0.0, s1);
+    }
+  }
+  for (; q < npairs; q += 32) {
+    const double2 x = __ldcs(row + q), c = __ldg(kk + q);
+    const bool in = 2 * q + 1 <= j;
+    s0 = fma(c.x, x.x, s0);
+    s1 = fma(in ? c.y : 0.0, in ? x.y : 0.0, s1);
+  }
+  double s = s0 + s1;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+  if (lane == 0) L21[j] = s;
+}
+
+// T[c] += sum_{p in split, p >= c} L21[p] Linv[p][c]; a thread owns two neighbouring columns, gridDim.y row splits.
+__global__ void __launch_bounds__(128)
+append_t_one_kernel(const double* __restrict__ X, int ld, int n, const double* __restrict__ L21, double* __restrict__ T) {
+  const int c0 = 2 * (blockIdx.x * 128 + threadIdx.x);
+  const int per = (n + gridDim.y - 1) / gridDim.y;
+  const int p_lo = blockIdx.y * per, p_hi = min(n, p_lo + per);
+  if (c0 >= n || p_hi <= c0) return;
+  const double* col = X + c0;
+  double s0 = 0.0, s1 = 0.0;
+  int p = max(p_lo, c0);
+  for (; p + 3 < p_hi; p += 4) {   // four rows' loads issued before the first use
+    double2 x[4];
+    double l[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      x[u] = __ldcs(reinterpret_cast<const double2*>(col + (size_t)(p + u) * ld));
+      l[u] = __ldg(L21 + p + u);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      s0 = fma(l[u], x[u].x, s0);
+      s1 = fma(l[u], p + u > c0 ? x[u].y : 0.0, s1);   // (row c0 holds nothing in column c0 + 1)
+    }
+  }
+  for (; p < p_hi; ++p) {
+    const double2 x = __ldcs(reinterpret_cast<const double2*>(col + (size_t)p * ld));
+    const double l = __ldg(L21 + p);
+    s0 = fma(l, x.x, s0);
+    s1 = fma(l, p > c0 ? x.y : 0.0, s1);
+  }
+  atomicAdd(&T[c0], s0);
+  if (c0 + 1 < n) atomicAdd(&T[c0 + 1], s1);
+}
+
 // New rows of L^-1: X[n+i][c] = -sum_{q<=i} X22[i][q] T[q][c] (c < n), X[n+i][n+q] = X22[i][q].
 __global__ void __launch_bounds__(256)
 append_rows_kernel(double* __restrict__ X, int ld, int n, int k, const double* __restrict__ T,
@@ -978,7 +1047,8 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
     SBO_LAUNCH_CHECK(ctx, "append_cov_kernel");
   }
   if (n > 0) {
-    append_l21_kernel<<<(n * 32 + 255) / 256, 256, 0, st>>>(ctx->d_Linv, ld, n, k, K21, L21);
+    if (k == 1) append_l21_one_kernel<<<(n * 32 + 255) / 256, 256, 0, st>>>(ctx->d_Linv, ld, n, K21, L21);
+    else append_l21_kernel<<<(n * 32 + 255) / 256, 256, 0, st>>>(ctx->d_Linv, ld, n, k, K21, L21);
     SBO_LAUNCH_CHECK(ctx, "append_l21_kernel");
     append_schur_kernel<<<(k * k * 32 + 255) / 256, 256, 0, st>>>(L21, ld, n, k, S);
     SBO_LAUNCH_CHECK(ctx, "append_schur_kernel");
@@ -993,8 +1063,14 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
     int splits = (ctx->sm_count * 16) / ((n + 127) / 128);   // ~2048 resident threads per SM: one load in flight each
     if (splits < 1) splits = 1;
     if (splits > 64) splits = 64;
-    dim3 g((n + 127) / 128, splits);
-    append_t_kernel<<<g, 128, 0, st>>>(ctx->d_Linv, ld, n, k, L21, T);
+    if (k == 1) {   // two columns per thread: half the column blocks, the same number of CTAs
+      const int bx = (n + 255) / 256;
+      splits = std::max(1, std::min(64, (ctx->sm_count * 16) / bx));
+      append_t_one_kernel<<<dim3(bx, splits), 128, 0, st>>>(ctx->d_Linv, ld, n, L21, T);
+    } else {
+      dim3 g((n + 127) / 128, splits);
+      append_t_kernel<<<g, 128, 0, st>>>(ctx->d_Linv, ld, n, k, L21, T);
+    }
     SBO_LAUNCH_CHECK(ctx, "append_t_kernel");
   }
   {

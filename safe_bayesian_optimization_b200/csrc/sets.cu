@@ -116,11 +116,15 @@ __device__ __forceinline__ void store_q(double* q, long long base, double v0, do
   __stcs(reinterpret_cast<double2*>(q + base) + 1, make_double2(v2, v3));
 }
 
-template <typename T, bool kStd, bool kVec>
+// kDelta (SBO_OPT_MASK_DELTA): `mask` still holds the previous step's bytes; a thread that is about to change any of them
+// raises the flag of the 64 KiB segment they lie in (dirty[cell >> kMaskSegShift]; plain stores of 1, every writer agrees).
+// The host copies back only the flagged segments.  One extra byte read per cell.
+template <typename T, bool kStd, bool kVec, bool kDelta = false>
 __global__ void __launch_bounds__(kThreads)
 sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long long cell0, double beta, double f_min,
             double noise_add, double low_thr, uint8_t* __restrict__ mask, double* __restrict__ q0out, double* __restrict__ q1out,
-            SetsResult* __restrict__ partials, SetsResult* __restrict__ result, unsigned int* __restrict__ ticket) {
+            SetsResult* __restrict__ partials, SetsResult* __restrict__ result, unsigned int* __restrict__ ticket,
+            unsigned int* __restrict__ dirty = nullptr) {
   Acc acc;
   const long long tid = (long long)blockIdx.x * kThreads + threadIdx.x;
   const long long nthreads = (long long)gridDim.x * kThreads;
@@ -150,6 +154,9 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
                                      a1[e])
                      << (8 * e);
           }
+          if (kDelta) {
+            if (__ldcs(reinterpret_cast<const unsigned int*>(mask + base)) != bytes) dirty[base >> kMaskSegShift] = 1u;
+          }
           __stcs(reinterpret_cast<unsigned int*>(mask + base), bytes);
           if (q0out) store_q(q0out, base, a0[0], a0[1], a0[2], a0[3]);
           if (q1out) store_q(q1out, base, a1[0], a1[1], a1[2], a1[3]);
@@ -162,6 +169,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
       const long long c = tail0 + tid;
       double a0, a1;
       const uint32_t b = eval_cell<kStd>((double)mu[c], (double)s[c], beta, f_min, noise_add, low_thr, cell0 + c, acc, a0, a1);
+      if (kDelta && mask[c] != (uint8_t)b) dirty[c >> kMaskSegShift] = 1u;
       mask[c] = (uint8_t)b;
       if (q0out) q0out[c] = a0;
       if (q1out) q1out[c] = a1;
@@ -170,6 +178,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
     for (long long c = tid; c < m; c += nthreads) {
       double a0, a1;
       const uint32_t b = eval_cell<kStd>((double)mu[c], (double)s[c], beta, f_min, noise_add, low_thr, cell0 + c, acc, a0, a1);
+      if (kDelta && mask[c] != (uint8_t)b) dirty[c >> kMaskSegShift] = 1u;
       mask[c] = (uint8_t)b;
       if (q0out) q0out[c] = a0;
       if (q1out) q1out[c] = a1;
@@ -248,7 +257,7 @@ sets_kernel(const T* __restrict__ mu, const T* __restrict__ s, long long m, long
 
 template <typename T, bool kStd>
 int32_t launch(sbo_ctx* ctx, const T* mu, const T* s, int64_t m, int64_t cell0, double beta, double f_min,
-               double noise_add, uint8_t* mask, double* q0, double* q1) {
+               double noise_add, uint8_t* mask, double* q0, double* q1, unsigned int* dirty = nullptr) {
   const double low_thr = kStd ? 0.0 : 0.02 * ctx->cfg.sigma_f * ctx->cfg.sigma_f;
   auto aligned = [](const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
   const bool vec = aligned(mu, 16) && aligned(s, 16) && aligned(mask, 4) && (!q0 || aligned(q0, 16)) &&
@@ -258,6 +267,18 @@ int32_t launch(sbo_ctx* ctx, const T* mu, const T* s, int64_t m, int64_t cell0, 
   const int64_t cap = sets_grid_size(ctx);
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
+  if constexpr (!kStd) {
+    if (dirty) {   // the step's pass with changed-segment flags (SBO_OPT_MASK_DELTA)
+      if (vec)
+        sets_kernel<T, kStd, true, true><<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(
+            mu, s, m, cell0, beta, f_min, noise_add, low_thr, mask, q0, q1, ctx->d_partials, ctx->d_result, ctx->d_ticket, dirty);
+      else
+        sets_kernel<T, kStd, false, true><<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(
+            mu, s, m, cell0, beta, f_min, noise_add, low_thr, mask, q0, q1, ctx->d_partials, ctx->d_result, ctx->d_ticket, dirty);
+      SBO_LAUNCH_CHECK(ctx, "sets_kernel(delta)");
+      return SBO_OK;
+    }
+  }
   if (vec) {
     sets_kernel<T, kStd, true><<<(unsigned)blocks, kThreads, 0, ctx->stream>>>(
         mu, s, m, cell0, beta, f_min, noise_add, low_thr, mask, q0, q1, ctx->d_partials, ctx->d_result, ctx->d_ticket);
@@ -275,12 +296,13 @@ int sets_grid_size(const sbo_ctx* ctx) { return ctx->sm_count * 8; }  // 8 x 256
 
 int32_t launch_sets_step(sbo_ctx* ctx, double beta, double f_min) {
   const double noise_add = ctx->cfg.include_noise_in_sigma ? ctx->cfg.noise_var : 0.0;
+  unsigned int* dirty = ctx->opt.mask_delta ? ctx->d_mask_dirty : nullptr;
   if (ctx->cfg.precision == SBO_FP64) {
     return launch<double, false>(ctx, static_cast<const double*>(ctx->d_mu), static_cast<const double*>(ctx->d_s2),
-                                 ctx->m_local, ctx->cell0, beta, f_min, noise_add, ctx->d_mask, nullptr, nullptr);
+                                 ctx->m_local, ctx->cell0, beta, f_min, noise_add, ctx->d_mask, nullptr, nullptr, dirty);
   }
   return launch<float, false>(ctx, static_cast<const float*>(ctx->d_mu), static_cast<const float*>(ctx->d_s2),
-                              ctx->m_local, ctx->cell0, beta, f_min, noise_add, ctx->d_mask, nullptr, nullptr);
+                              ctx->m_local, ctx->cell0, beta, f_min, noise_add, ctx->d_mask, nullptr, nullptr, dirty);
 }
 
 int32_t launch_sets_arrays(sbo_ctx* ctx, const double* d_mu, const double* d_std, int64_t m, double beta, double f_min,

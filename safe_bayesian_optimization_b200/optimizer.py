@@ -185,6 +185,12 @@ class SboContext:
         self._check(self.lib.sbo_fit_info(self._h, C.byref(ms), C.byref(w)))
         return float(ms.value), int(w.value)
 
+    def mask_copy_info(self):
+        """(mask bytes the last step copied to the host, contiguous runs) -- sbo_mask_copy_info (option ``mask_delta``)."""
+        b, r = C.c_int64(0), C.c_int32(0)
+        self._check(self.lib.sbo_mask_copy_info(self._h, C.byref(b), C.byref(r)))
+        return int(b.value), int(r.value)
+
     def order(self):
         """order[pos] = caller index of the observation stored at internal position pos."""
         out = np.zeros(self.n_obs, dtype=np.int32)
