@@ -208,7 +208,7 @@ __device__ long long g_diag_t[16];
 // and 1000 of them paced the first version of this kernel).  Entries right of the diagonal hold garbage that
 // is never read.  Column j:  a[c] -= a[j] cb[c] / d  (d = pivot, cb = column j before scaling), then
 // a[j] *= d^-1/2.
-__device__ __forceinline__ void warp_chol_inv32(DiagSmem& sm, int base, int row_base, int* info) {
+__device__ __forceinline__ void warp_chol_inv32(DiagSmem& sm, int base, int row_base, int* info, double min_pivot) {
   const int lane = threadIdx.x & 31;
   double a[SB], rinv[SB];
 #pragma unroll
@@ -219,7 +219,7 @@ __device__ __forceinline__ void warp_chol_inv32(DiagSmem& sm, int base, int row_
     cb[lane] = a[j];
     __syncwarp();
     double d = cb[j];
-    if (!(d > 0.0)) {  // uniform
+    if (!(d > min_pivot)) {  // uniform
       if (lane == 0) { sm.bad = 1; atomicCAS(info, 0, row_base + base + j + 1); }
       d = 1.0;
     }
@@ -258,7 +258,7 @@ __device__ __forceinline__ void warp_chol_inv32(DiagSmem& sm, int base, int row_
 
 __global__ void __launch_bounds__(kDiagThreads)
 diag_chol_inv_kernel(double* __restrict__ Ablk, int ld, int nb, double* __restrict__ Dinv, int ldd, int row_base,
-                     int* __restrict__ info) {
+                     int* __restrict__ info, double min_pivot = 0.0) {   // a pivot must exceed min_pivot (0: LAPACK's test)
   extern __shared__ __align__(16) unsigned char smem_diag[];
   DiagSmem& sm = *reinterpret_cast<DiagSmem*>(smem_diag);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -273,7 +273,7 @@ diag_chol_inv_kernel(double* __restrict__ Ablk, int ld, int nb, double* __restri
       bool bad = false;
       for (int j = 0; j < nb && !bad; ++j) {
         double d = a[j][j];
-        if (!(d > 0.0)) {
+        if (!(d > min_pivot)) {
           atomicCAS(info, 0, row_base + j + 1);
           bad = true;
           break;
@@ -311,7 +311,7 @@ diag_chol_inv_kernel(double* __restrict__ Ablk, int ld, int nb, double* __restri
       sm.S[i][j] = v;
     }
     __syncthreads();
-    if (warp == 0) warp_chol_inv32(sm, 0, row_base, info);
+    if (warp == 0) warp_chol_inv32(sm, 0, row_base, info, min_pivot);
     __syncthreads();
     if (sm.bad) return;
     for (int e = tid; e < nb * nb; e += kDiagThreads) {
@@ -334,7 +334,7 @@ diag_chol_inv_kernel(double* __restrict__ Ablk, int ld, int nb, double* __restri
   for (int kb = 0; kb < NB / SB; ++kb) {
     const int base = kb * SB;
     if (kb == 1) DIAG_T(6);
-    if (warp == 0) warp_chol_inv32(sm, base, row_base, info);
+    if (warp == 0) warp_chol_inv32(sm, base, row_base, info, min_pivot);
     if (kb == 0) DIAG_T(3);
     __syncthreads();
     if (kb == 0) DIAG_T(4);
@@ -672,18 +672,26 @@ append_l21_kernel(const double* __restrict__ X, int ld, int n, int k, const doub
   }
 }
 
-// S[i][j] -= L21[i] . L21[j] for j <= i; one warp per pair.
+// S[i][j] -= L21[i] . L21[j] for j <= i; one CTA per pair (one warp over n = 16 384 entries took 114 us).
 __global__ void __launch_bounds__(256)
 append_schur_kernel(const double* __restrict__ L21, int ld, int n, int k, double* __restrict__ S) {
-  const int w = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (w >= k * k) return;
-  const int i = w / k, j = w - i * k;
+  __shared__ double red[8];
+  const int i = blockIdx.x / k, j = blockIdx.x - i * k;
   if (j > i) return;
+  const double* a = L21 + (size_t)i * ld;
+  const double* b = L21 + (size_t)j * ld;
   double s = 0.0;
-  for (int p = lane; p < n; p += 32) s = fma(L21[(size_t)i * ld + p], L21[(size_t)j * ld + p], s);
+  for (int p = threadIdx.x; p < n; p += 256) s = fma(a[p], b[p], s);
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
-  if (lane == 0) S[i * kMaxAppend + j] -= s;
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) t += red[q];
+    S[i * kMaxAppend + j] -= t;
+  }
 }
 
 // T[i][c] += sum_{p in split, p >= c} L21[i][p] Linv[p][c]; thread per column, gridDim.y row splits.
@@ -844,6 +852,26 @@ row_l1_max_kernel(const double* __restrict__ X, int ld, int row_begin, int row_e
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
   if (lane == 0) atomicMax(reinterpret_cast<unsigned long long*>(out), (unsigned long long)__double_as_longlong(s));
+}
+
+// The same for the few rows of an append: one CTA per row.
+__global__ void __launch_bounds__(256)
+row_l1_max_rows_kernel(const double* __restrict__ X, int ld, int row_begin, double* __restrict__ out) {
+  __shared__ double red[8];
+  const int row = row_begin + blockIdx.x;
+  const double* x = X + (size_t)row * ld;
+  double s = 0.0;
+  for (int c = threadIdx.x; c <= row; c += 256) s += fabs(x[c]);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) t += red[q];
+    atomicMax(reinterpret_cast<unsigned long long*>(out), (unsigned long long)__double_as_longlong(t));
+  }
 }
 
 // d_info: [0] Cholesky status (int), [8] max row 1-norm of L^-1 over the rows of a full fit, [16] over the rows of an append
@@ -1050,10 +1078,15 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
     if (k == 1) append_l21_one_kernel<<<(n * 32 + 255) / 256, 256, 0, st>>>(ctx->d_Linv, ld, n, K21, L21);
     else append_l21_kernel<<<(n * 32 + 255) / 256, 256, 0, st>>>(ctx->d_Linv, ld, n, k, K21, L21);
     SBO_LAUNCH_CHECK(ctx, "append_l21_kernel");
-    append_schur_kernel<<<(k * k * 32 + 255) / 256, 256, 0, st>>>(L21, ld, n, k, S);
+    append_schur_kernel<<<k * k, 256, 0, st>>>(L21, ld, n, k, S);
     SBO_LAUNCH_CHECK(ctx, "append_schur_kernel");
   }
-  diag_chol_inv_kernel<<<1, kDiagThreads, kDiagSmem, st>>>(S, kMaxAppend, k, X22, kMaxAppend, n, ctx->d_info);
+  // A Schur-complement pivot K22 - |l21|^2 below a few hundred roundings of K22 is cancellation noise, whatever its
+  // sign: the new observation is numerically a combination of those held (a duplicate under a vanishing noise_var),
+  // and the rows of L^-1 it would produce are garbage.  Rejected as not positive definite, independent of the summation
+  // order of the passes above.  (noise_var >= 1e-13 sigma_f^2 never comes near: the pivot is >= noise_var.)
+  const double min_pivot = 256.0 * 2.220446049250313e-16 * (sf2 + ctx->cfg.noise_var);
+  diag_chol_inv_kernel<<<1, kDiagThreads, kDiagSmem, st>>>(S, kMaxAppend, k, X22, kMaxAppend, n, ctx->d_info, min_pivot);
   SBO_LAUNCH_CHECK(ctx, "diag_chol_inv_kernel(append)");
   // The positive-definiteness verdict is read once, at the end (one host synchronisation per append instead of two):
   // until then only rows >= n of L^-1 (not part of the state) and alpha are written, and alpha is restored below.
@@ -1087,7 +1120,7 @@ int32_t factor_append(sbo_ctx* ctx, int k) {
     SBO_TRY(compute_alpha(ctx, n + k));
   }
   SBO_TRY(refresh_planes(ctx, n, n + k));
-  row_l1_max_kernel<<<(k * 32 + 255) / 256, 256, 0, st>>>(ctx->d_Linv, ld, n, n + k, reinterpret_cast<double*>(ctx->d_info) + 2);
+  row_l1_max_rows_kernel<<<k, 256, 0, st>>>(ctx->d_Linv, ld, n, reinterpret_cast<double*>(ctx->d_info) + 2);
   SBO_LAUNCH_CHECK(ctx, "row_l1_max_kernel");
   InfoRecord rec;
   const int32_t verdict = check_info(ctx, "sbo_append_observations", &rec);   // synchronises the stream

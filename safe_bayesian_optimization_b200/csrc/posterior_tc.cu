@@ -241,6 +241,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // UMMA shared-memory descriptor: K-major operand, 128-byte swizzle, rows 128 B apart, 8-row groups
@@ -1322,7 +1331,8 @@ int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo) {
     p.nslabs = bs; p.rp = rp; p.lr_base = (s0 * BN) >> lq;
     pplanes_kernel<<<dim3((unsigned)(rp >> lq), (unsigned)((ld + 255) / 256)), 256, 0, ctx->stream>>>(
         ctx->d_xy, ctx->d_Linv, ld, ctx->n, row_lo, k, lq, p.rows_local, ctx->row0, ctx->y0, ctx->ry, inv2l2,
-        std::ldexp(1.0, ctx->shift_b), rp, p.lr_base, reinterpret_cast<__half*>(ctx->d_pplanes));
+        std::ldexp(1.0, ctx->shift_b), rp, p.lr_base, reinterpret_cast<__half*>(ctx->d_pplanes), p.bbox, p.skip, p.skip_bits,
+        p.xscale);
     SBO_LAUNCH_CHECK(ctx, "pplanes_kernel");
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = {(cuuint64_t)ld, (cuuint64_t)2 * rp};

@@ -65,14 +65,28 @@ __device__ __noinline__ void build_item_mask(uint32_t* mask, const IncParams p, 
 
 // fp16 hi/lo planes of P: row rho = lr * KP + q holds 2^shift_b ey(lr, j) Linv[row_lo + q][j]  (sigma_f^2 rides on A).
 // One thread per (grid row, observation): the fp64 exp is computed once and serves the KP rows of that grid row.
+// Block-sparse walk: a 64-observation chunk that is out of reach in y of a whole slab of 256 rows of P is visited by none of
+// the slab's items (build_item_mask adds dx^2 >= 0 to the same dy^2, in the same fp32 arithmetic), so its entries are
+// neither computed nor written -- the buffer keeps whatever it held there and nobody reads it.  At C4 (reach 7 length-
+// scales of a 45 length-scale domain) that is ~60 % of the fp64 exponentials and of the 512 MiB of stores.
 __global__ void __launch_bounds__(256)
 pplanes_kernel(const double* __restrict__ xy, const double* __restrict__ Linv, int ld, int n, int row_lo, int k, int lq,
                int rows_local, int row0, double y0, double ry, double inv2l2, double scale, int rp, int lr_base,
-               __half* __restrict__ planes) {
+               __half* __restrict__ planes, const float4* __restrict__ bbox, int skip, float skip_bits, double xscale) {
   const int j = blockIdx.y * 256 + threadIdx.x;
   const int lb = blockIdx.x;   // row of the band, incl. the padding up to a whole slab
   const int lr = lr_base + lb;
   if (j >= ld) return;
+  if (skip && j < n) {
+    const int sb = (lb << lq) / BN;   // the slab this row of the band belongs to, and the grid rows that slab spans
+    const int lr_first = min(lr_base + ((sb * BN) >> lq), rows_local - 1);
+    const int lr_last = min(lr_base + (((sb + 1) * BN) >> lq) - 1, rows_local - 1);
+    const double ya = cell_coord(y0, ry, row0 + lr_first) * xscale, yb = cell_coord(y0, ry, row0 + lr_last) * xscale;
+    const float ylo = (float)fmin(ya, yb) - 1e-3f, yhi = (float)fmax(ya, yb) + 1e-3f;
+    const float4 b = bbox[j / BK];
+    const float dy = fmaxf(fmaxf(b.z - yhi, ylo - b.w), 0.f);
+    if (__fmul_rn(dy, dy) > skip_bits + 0.5f) return;
+  }
   double e = 0.0;
   if (j < n && lr < rows_local) {
     const double dy = xy[2 * (size_t)j + 1] - cell_coord(y0, ry, row0 + lr);
@@ -219,27 +233,45 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q4 * 32) << 16) + as * BN;
 #pragma unroll 1
-      for (int g = 0; g < BN / 32; ++g) {
-        uint32_t v[32];
-        tmem_ld32(taddr + g * 32, v);
+      for (int g = 0; g < BN / 16; ++g) {
+        uint32_t v[16];
+        tmem_ld16(taddr + g * 16, v);
         tmem_ld_wait();
-        const int lr0 = p.lr_base + ((sb * BN + g * 32) >> LQ);  // first grid row of this group of 32 rows of P
+        const int lr0 = p.lr_base + ((sb * BN + g * 16) >> LQ);  // first grid row of this group of 16 rows of P
+        // The stored sigma^2 / mu of the group's grid rows are fetched before the first of them is rewritten: written as one
+        // read-modify-write per row the loads cannot pass the stores (mu and s2 may alias as far as the compiler knows)
+        // and a thread's 256 rows of an item become 256 dependent DRAM round trips -- 180 us per item against 45 us of
+        // MMAs at C4 with one new row, 3.7 ms per step.
+        constexpr int kRows = 16 >> LQ;                  // grid rows in this group of 16 TMEM columns (LQ <= 4)
+        constexpr int kBatch = kRows < 8 ? kRows : 8;    // 8 rows = 16 loads in flight per thread (16 rows spill their addresses)
 #pragma unroll
-        for (int t = 0; t < (32 >> LQ); ++t) {
-          float usq = 0.f;
-          double dmu = 0.0;
+        for (int t0 = 0; t0 < kRows; t0 += kBatch) {
+          float s2v[kBatch], muv[kBatch];
 #pragma unroll
-          for (int q = 0; q < KP; ++q) {
-            const float d = __uint_as_float(v[(t << LQ) + q]);
-            const float u = d * uu;
-            usq = fmaf(u, u, usq);
-            dmu = fma(wq[q], (double)d, dmu);
-          }
-          const int lr = lr0 + t;
-          if (live && lr < p.rows_local) {
+          for (int b = 0; b < kBatch; ++b) {
+            const int lr = lr0 + t0 + b;
+            const bool ok = live && lr < p.rows_local;
             const long long lc = (long long)lr * p.W + col;
-            p.s2[lc] = (float)((double)p.s2[lc] - (double)usq);
-            p.mu[lc] = (float)((double)p.mu[lc] + dmu);
+            s2v[b] = ok ? p.s2[lc] : 0.f;
+            muv[b] = ok ? p.mu[lc] : 0.f;
+          }
+#pragma unroll
+          for (int b = 0; b < kBatch; ++b) {
+            float usq = 0.f;
+            double dmu = 0.0;
+#pragma unroll
+            for (int q = 0; q < KP; ++q) {
+              const float d = __uint_as_float(v[((t0 + b) << LQ) + q]);
+              const float u = d * uu;
+              usq = fmaf(u, u, usq);
+              dmu = fma(wq[q], (double)d, dmu);
+            }
+            const int lr = lr0 + t0 + b;
+            if (live && lr < p.rows_local) {
+              const long long lc = (long long)lr * p.W + col;
+              p.s2[lc] = (float)((double)s2v[b] - (double)usq);
+              p.mu[lc] = (float)((double)muv[b] + dmu);
+            }
           }
         }
       }
