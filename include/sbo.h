@@ -140,7 +140,8 @@ typedef enum {
   SBO_OPT_TC_EAGER = 4,          /* 1 (default): first row-block pairs start inside the factorisation                    */
   SBO_OPT_TC_INC = 5,            /* 1 (default): incremental steps on large grids as a tensor-core GEMM                  */
   SBO_OPT_THIN = 6,              /* 1 (default): <= 8 new rows through the O(m n k) FMA kernel                            */
-  SBO_OPT_THIN_2D = 7,           /* 1 (default): fp64 one-new-row step through the 2-D register tile                      */
+  SBO_OPT_THIN_2D = 7,           /* 1 (default): fp64 one-new-row step as a 128 x 128-cell tile on the fp64 tensor path (DMMA);
+                                    2: the same tile as DFMA register tiles; 0: the column-strip kernel                     */
   SBO_OPT_TC_GRADED = 8,         /* 1 (default): distance-graded split depth -- (tile, chunk) visits whose K* entries are
                                     all < 2^-(b-10) sigma_f^2 issue hi.hi only (same error bound as the skipped chunks)   */
   SBO_OPT_TC_STRIP = 9,          /* tile pairs per strip of the strip-major tile order (default 4; 0 = raster order)       */

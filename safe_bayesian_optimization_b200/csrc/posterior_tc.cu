@@ -1329,7 +1329,7 @@ int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo) {
   for (int s0 = 0; s0 < nslabs; s0 += band_slabs) {   // bands run back to back on the stream and reuse the planes buffer
     const int bs = std::min(band_slabs, nslabs - s0), rp = bs * BN;
     p.nslabs = bs; p.rp = rp; p.lr_base = (s0 * BN) >> lq;
-    pplanes_kernel<<<dim3((unsigned)(rp >> lq), (unsigned)((ld + 255) / 256)), 256, 0, ctx->stream>>>(
+    pplanes_kernel<<<dim3((unsigned)((rp >> lq) / kPplaneRows), (unsigned)((ld + 255) / 256)), 256, 0, ctx->stream>>>(
         ctx->d_xy, ctx->d_Linv, ld, ctx->n, row_lo, k, lq, p.rows_local, ctx->row0, ctx->y0, ctx->ry, inv2l2,
         std::ldexp(1.0, ctx->shift_b), rp, p.lr_base, reinterpret_cast<__half*>(ctx->d_pplanes), p.bbox, p.skip, p.skip_bits,
         p.xscale);

@@ -69,16 +69,17 @@ __device__ __noinline__ void build_item_mask(uint32_t* mask, const IncParams p, 
 // the slab's items (build_item_mask adds dx^2 >= 0 to the same dy^2, in the same fp32 arithmetic), so its entries are
 // neither computed nor written -- the buffer keeps whatever it held there and nobody reads it.  At C4 (reach 7 length-
 // scales of a 45 length-scale domain) that is ~60 % of the fp64 exponentials and of the 512 MiB of stores.
+// One thread per observation and 16 grid rows (one thread per (row, observation) spent most of its 0.5 ms starting threads).
+constexpr int kPplaneRows = 16;   // grid rows per CTA of pplanes_kernel: divides the 256 >> lq rows of a slab (lq <= 4)
 __global__ void __launch_bounds__(256)
 pplanes_kernel(const double* __restrict__ xy, const double* __restrict__ Linv, int ld, int n, int row_lo, int k, int lq,
                int rows_local, int row0, double y0, double ry, double inv2l2, double scale, int rp, int lr_base,
                __half* __restrict__ planes, const float4* __restrict__ bbox, int skip, float skip_bits, double xscale) {
   const int j = blockIdx.y * 256 + threadIdx.x;
-  const int lb = blockIdx.x;   // row of the band, incl. the padding up to a whole slab
-  const int lr = lr_base + lb;
+  const int lb0 = blockIdx.x * kPplaneRows;   // first row of the band this CTA writes, incl. the padding up to a whole slab
   if (j >= ld) return;
   if (skip && j < n) {
-    const int sb = (lb << lq) / BN;   // the slab this row of the band belongs to, and the grid rows that slab spans
+    const int sb = (lb0 << lq) / BN;   // the slab these rows of the band belong to, and the grid rows that slab spans
     const int lr_first = min(lr_base + ((sb * BN) >> lq), rows_local - 1);
     const int lr_last = min(lr_base + (((sb + 1) * BN) >> lq) - 1, rows_local - 1);
     const double ya = cell_coord(y0, ry, row0 + lr_first) * xscale, yb = cell_coord(y0, ry, row0 + lr_last) * xscale;
@@ -87,19 +88,31 @@ pplanes_kernel(const double* __restrict__ xy, const double* __restrict__ Linv, i
     const float dy = fmaxf(fmaxf(b.z - yhi, ylo - b.w), 0.f);
     if (__fmul_rn(dy, dy) > skip_bits + 0.5f) return;
   }
-  double e = 0.0;
-  if (j < n && lr < rows_local) {
-    const double dy = xy[2 * (size_t)j + 1] - cell_coord(y0, ry, row0 + lr);
-    e = exp(-dy * dy * inv2l2) * scale;
-  }
+  // one thread = one observation: its y and its entries of the new rows of L^-1 are read once for the CTA's grid rows
   const int kp = 1 << lq;
-  for (int q = 0; q < kp; ++q) {
-    const double x = (q < k && e != 0.0) ? e * Linv[(size_t)(row_lo + q) * ld + j] : 0.0;
-    const __half hi = __float2half_rn((float)x);
-    const __half lo = __float2half_rn((float)(x - (double)__half2float(hi)));
-    const size_t rho = (size_t)lb * kp + q;
-    planes[rho * ld + j] = hi;
-    planes[((size_t)rp + rho) * ld + j] = lo;
+  const double yj = j < n ? xy[2 * (size_t)j + 1] : 0.0;
+  double lq_[16];
+#pragma unroll
+  for (int q = 0; q < 16; ++q) lq_[q] = (q < k && q < kp && j < n) ? Linv[(size_t)(row_lo + q) * ld + j] : 0.0;
+#pragma unroll 2
+  for (int r = 0; r < kPplaneRows; ++r) {
+    const int lb = lb0 + r, lr = lr_base + lb;
+    double e = 0.0;
+    if (j < n && lr < rows_local) {
+      const double dy = yj - cell_coord(y0, ry, row0 + lr);
+      e = exp(-dy * dy * inv2l2) * scale;
+    }
+#pragma unroll
+    for (int q = 0; q < 16; ++q) {
+      if (q < kp) {
+        const double x = (q < k && e != 0.0) ? e * lq_[q] : 0.0;
+        const __half hi = __float2half_rn((float)x);
+        const __half lo = __float2half_rn((float)(x - (double)__half2float(hi)));
+        const size_t rho = (size_t)lb * kp + q;
+        planes[rho * ld + j] = hi;
+        planes[((size_t)rp + rho) * ld + j] = lo;
+      }
+    }
   }
 }
 

@@ -340,6 +340,184 @@ posterior_thin2d_f64_kernel(ThinParams p, double* __restrict__ mu_out, double* _
   }
 }
 
+// ---- the same tile on the fp64 tensor path (mma.sync m8n8k4): what the fp64 one-new-row step runs by default ----------
+// u[r][c] = sum_j b[j][r] a[j][c] is a GEMM over the observations (M = 128 grid rows, N = 128 grid columns, K = the 64
+// observations of a chunk per stage).  The register tile above issues 64 DFMA + 8 LDS.128 per observation and thread and
+// holds 57 % of the fp64 pipe; one DMMA is 256 FMAs behind two 8-byte fragment loads (posterior_f64.cu holds 77-79 % with
+// the same instruction).  512 threads = 16 warps as 4 (rows) x 4 (columns), warp tile 32 x 32 = 4 x 4 DMMA tiles, 32
+// accumulators per thread.  Staged rows are 132 doubles long: the (k = lane % 4, cell = lane / 4) fragment reads of a
+// half-warp then cover all 32 banks once.
+// Staging costs three exp per (observation, factor) instead of two per 16 staged values: with d0 = X_0 - x_j at the first
+// cell of the tile edge and pitch h,
+//   e(c) = exp(-d0^2 / 2l^2) * g^c * T[c],      g = exp(-2 d0 h / 2l^2),  T[c] = exp(-c^2 h^2 / 2l^2)   (c = 0 .. 15),
+//   e(c + 16 (i + 1)) = e(c + 16 i) * G_i,      G_0 = exp(-(32 d0 h + 256 h^2) / 2l^2) * R[c],  R[c] = exp(-32 c h^2 / 2l^2),
+//   G_(i+1) = G_i * exp(-512 h^2 / 2l^2);
+// 128 threads compute (e(0), g, g^2, g^4, g^8, G_0 without R) per (observation, factor) into shared memory, then every
+// thread forms its anchors with <= 6 multiplications (g^c from the bits of c; T, R from two 16-entry tables) and runs
+// eight recurrence steps: ~30 roundings per staged value, 3e-15 relative.  An anchor that underflows sits >= 34
+// length-scales from every cell of the edge (the host requires 128 h <= 4 l); its ratios are zeroed with it so that a huge
+// ratio cannot meet the zero.
+constexpr int kD2Threads = 512;
+constexpr int kD2Ld = kT2 + 4;
+constexpr int kD2Chunk = 64;
+
+__device__ __forceinline__ void dmma8x8x4(double (&c)[2], double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(kD2Threads, 1)
+posterior_thin2d_dmma_kernel(ThinParams p, double* __restrict__ mu_out, double* __restrict__ s2_out) {
+  extern __shared__ __align__(16) double sm2[];
+  double* a_s = sm2;                         // [kD2Chunk][kD2Ld]: a_s[j][c] = ex(column c, observation j)
+  double* b_s = sm2 + kD2Chunk * kD2Ld;      // [kD2Chunk][kD2Ld]: b_s[j][r] = sigma_f^2 ey(row r, j) Linv[new row][j]
+  __shared__ __align__(16) double anc[2][kD2Chunk][8];   // per (factor, observation): e(0), g, g^2, g^4, g^8, G_0
+  __shared__ double tab_t[2][16], tab_r[2][16];
+  __shared__ uint32_t cmask[kD2Threads / 32];            // 512 chunks = 32 768 observations
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = lane >> 2, t = lane & 3, wm = warp >> 2, wn = warp & 3;
+  const int sg = tid & 15, jq = tid >> 4;   // staging role: cells sg + 16 i of the edge, observations jq and jq + 32 of the chunk
+  const int tiles_x = (p.W + kT2 - 1) / kT2, tiles_y = (p.rows_local + kT2 - 1) / kT2;
+  const long long ntiles = (long long)tiles_x * tiles_y;
+  const double w = p.w[p.row_lo];
+  const double* lrow = p.Linv + (size_t)p.row_lo * p.ld;
+  const double q16[2] = {exp(-512.0 * p.rx * p.rx * p.inv2l2), exp(-512.0 * p.ry * p.ry * p.inv2l2)};
+  if (tid < 32) {
+    const int f = tid >> 4, c = tid & 15;
+    const double h = f ? p.ry : p.rx;
+    tab_t[f][c] = exp(-(double)(c * c) * h * h * p.inv2l2);
+    tab_r[f][c] = exp(-32.0 * (double)c * h * h * p.inv2l2);
+  }
+  __syncthreads();
+  const double tt[2] = {tab_t[0][sg], tab_t[1][sg]}, tr[2] = {tab_r[0][sg], tab_r[1][sg]};
+
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int r0 = (int)(tile / tiles_x) * kT2, col0 = (int)(tile % tiles_x) * kT2;
+    if (p.bbox) {   // chunks within reach of this 128 x 128 patch (same box test and cut-off as posterior_f64.cu)
+      __syncthreads();   // the previous tile's reads of the mask are over
+      bool on = tid < (p.n + 63) / 64;
+      if (on) {
+        const double xa = cell_coord(p.x0, p.rx, col0), xb = cell_coord(p.x0, p.rx, min(col0 + kT2, p.W) - 1);
+        const double ya = cell_coord(p.y0, p.ry, p.row0 + r0), yb = cell_coord(p.y0, p.ry, p.row0 + min(r0 + kT2, p.rows_local) - 1);
+        const double4 b = p.bbox[tid];
+        const double dx = fmax(fmax(b.x - fmax(xa, xb), fmin(xa, xb) - b.y), 0.0);
+        const double dy = fmax(fmax(b.z - fmax(ya, yb), fmin(ya, yb) - b.w), 0.0);
+        on = dx * dx + dy * dy <= p.skip_r2;
+      }
+      const uint32_t bits = __ballot_sync(0xffffffffu, on);
+      if (lane == 0) cmask[warp] = bits;
+      __syncthreads();
+    }
+    const double base[2] = {cell_coord(p.x0, p.rx, col0), cell_coord(p.y0, p.ry, p.row0 + r0)};
+    double acc[4][4][2];
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+      for (int ni = 0; ni < 4; ++ni) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
+
+    for (int k0 = 0; k0 < p.n; k0 += kD2Chunk) {
+      if (p.bbox && !((cmask[k0 >> 11] >> ((k0 >> 6) & 31)) & 1u)) continue;   // out of reach: K* < 2^-bits sigma_f^2 for the whole patch
+      if (tid < 2 * kD2Chunk) {   // anchors of the chunk: one thread per (factor, observation)
+        const int f = tid >> 6, q = tid & (kD2Chunk - 1), j = k0 + q;
+        const double h = f ? p.ry : p.rx;
+        double d0 = 0.0, scale = 0.0;   // observations beyond n: b = 0 (Linv = 0); a = the harmless exp(0) table
+        if (j < p.n) {
+          d0 = base[f] - p.xy[2 * (size_t)j + f];
+          scale = f ? p.sf2 * lrow[j] : 1.0;
+        } else if (!f) {
+          scale = 1.0;
+        }
+        const double e0 = exp(-d0 * d0 * p.inv2l2) * scale;
+        double g1 = exp(-2.0 * d0 * h * p.inv2l2), g16 = exp(-(32.0 * d0 * h + 256.0 * h * h) * p.inv2l2);
+        if (e0 == 0.0) g1 = g16 = 0.0;
+        const double g2 = g1 * g1, g4 = g2 * g2, g8 = g4 * g4;
+        double2* dst = reinterpret_cast<double2*>(anc[f][q]);
+        dst[0] = make_double2(e0, g1);
+        dst[1] = make_double2(g2, g4);
+        dst[2] = make_double2(g8, g16);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int rep = 0; rep < 2; ++rep) {
+        const int q = jq + 32 * rep;
+#pragma unroll
+        for (int f = 0; f < 2; ++f) {
+          const double2* an = reinterpret_cast<const double2*>(anc[f][q]);
+          const double2 v0 = an[0], v1 = an[1], v2 = an[2];
+          double e = v0.x * tt[f];
+          if (sg & 1) e *= v0.y;
+          if (sg & 2) e *= v1.x;
+          if (sg & 4) e *= v1.y;
+          if (sg & 8) e *= v2.x;
+          double gg = v2.y * tr[f];
+          double* dst = (f ? b_s : a_s) + q * kD2Ld + sg;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            dst[16 * i] = e;
+            e *= gg;
+            gg *= q16[f];
+          }
+        }
+      }
+      __syncthreads();
+      const double* As = b_s + t * kD2Ld + wm * 32 + g;   // A[m = grid row][k = observation]
+      const double* Bs = a_s + t * kD2Ld + wn * 32 + g;   // B[k = observation][n = grid column]
+#pragma unroll 4
+      for (int k4 = 0; k4 < kD2Chunk / 4; ++k4) {
+        double a[4], b[4];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi) a[mi] = As[k4 * 4 * kD2Ld + mi * 8];
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) b[ni] = Bs[k4 * 4 * kD2Ld + ni * 8];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+          for (int ni = 0; ni < 4; ++ni) dmma8x8x4(acc[mi][ni], a[mi], b[ni]);
+      }
+      __syncthreads();
+    }
+
+    // accumulator (mi, ni) of a lane = u at row wm 32 + mi 8 + g, columns wn 32 + ni 8 + 2 t + {0, 1}.  The stored values
+    // of a row of four tiles are fetched before the first is rewritten.
+    const bool vec = (p.W & 1) == 0;
+#pragma unroll
+    for (int mi = 0; mi < 4; ++mi) {
+      const int row = r0 + wm * 32 + mi * 8 + g;
+      if (row >= p.rows_local) continue;
+      double s2v[4][2], muv[4][2];
+#pragma unroll
+      for (int ni = 0; ni < 4; ++ni) {
+        const int col = col0 + wn * 32 + ni * 8 + 2 * t;
+        const long long lc = (long long)row * p.W + col;
+        if (vec && col + 1 < p.W) {
+          const double2 sv = *reinterpret_cast<const double2*>(s2_out + lc), mv = *reinterpret_cast<const double2*>(mu_out + lc);
+          s2v[ni][0] = sv.x; s2v[ni][1] = sv.y; muv[ni][0] = mv.x; muv[ni][1] = mv.y;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            s2v[ni][e] = col + e < p.W ? s2_out[lc + e] : 0.0;
+            muv[ni][e] = col + e < p.W ? mu_out[lc + e] : 0.0;
+          }
+        }
+      }
+#pragma unroll
+      for (int ni = 0; ni < 4; ++ni) {
+        const int col = col0 + wn * 32 + ni * 8 + 2 * t;
+        const long long lc = (long long)row * p.W + col;
+        const double u0 = acc[mi][ni][0], u1 = acc[mi][ni][1];
+        const double n0 = s2v[ni][0] - u0 * u0, n1 = s2v[ni][1] - u1 * u1;
+        const double m0 = fma(w, u0, muv[ni][0]), m1 = fma(w, u1, muv[ni][1]);
+        if (vec && col + 1 < p.W) {
+          *reinterpret_cast<double2*>(s2_out + lc) = make_double2(n0, n1);
+          *reinterpret_cast<double2*>(mu_out + lc) = make_double2(m0, m1);
+        } else {
+          if (col < p.W) { s2_out[lc] = n0; mu_out[lc] = m0; }
+          if (col + 1 < p.W) { s2_out[lc + 1] = n1; mu_out[lc + 1] = m1; }
+        }
+      }
+    }
+  }
+}
+
 // (An fp32 form of this tile -- 64 FFMA per 4 LDS.128, MUFU staging, fp64 flush every 64 observations -- measured 12.3e12
 // against the strip kernel's 11.7e12 cell-observations/s at n = 16 384: 255 registers, one CTA per SM, no room to prefetch the
 // next observation's factors.  Not kept.)
@@ -389,15 +567,25 @@ int32_t launch_posterior_thin(sbo_ctx* ctx, int row_lo) {
     p.skip_r2 = 0.0;
     if (kr == 1 && tiles2d >= ctx->sm_count && span_ok && ctx->opt.thin_2d) {   // enough 128 x 128 tiles for every SM
       const void* boxes = nullptr;
-      SBO_TRY(f64_chunk_boxes(ctx, kThinThreads, &boxes, &p.skip_r2));
-      p.bbox = static_cast<const double4*>(boxes);
-      const size_t smem = (size_t)2 * kT2Chunk * kT2Ld * sizeof(double);
-      // per device, so not cached in a process-wide flag (a process may hold contexts on several GPUs); a few microseconds
-      const cudaError_t ea = cudaFuncSetAttribute(posterior_thin2d_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (ea != cudaSuccess) return cuda_fail(ctx, ea, "posterior_thin2d_f64_kernel: cudaFuncSetAttribute(max dynamic smem)");
       const unsigned grid = (unsigned)std::min<long long>(tiles2d, ctx->sm_count);
-      posterior_thin2d_f64_kernel<<<grid, kThinThreads, smem, ctx->stream>>>(p, static_cast<double*>(ctx->d_mu), static_cast<double*>(ctx->d_s2));
-      SBO_LAUNCH_CHECK(ctx, "posterior_thin2d_f64_kernel");
+      // (the attributes are per device, so not cached in a process-wide flag: a process may hold contexts on several GPUs)
+      if (ctx->opt.thin_2d == 2) {   // the DFMA register tile, kept for A/B
+        SBO_TRY(f64_chunk_boxes(ctx, kThinThreads, &boxes, &p.skip_r2));
+        p.bbox = static_cast<const double4*>(boxes);
+        const size_t smem = (size_t)2 * kT2Chunk * kT2Ld * sizeof(double);
+        const cudaError_t ea = cudaFuncSetAttribute(posterior_thin2d_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (ea != cudaSuccess) return cuda_fail(ctx, ea, "posterior_thin2d_f64_kernel: cudaFuncSetAttribute(max dynamic smem)");
+        posterior_thin2d_f64_kernel<<<grid, kThinThreads, smem, ctx->stream>>>(p, static_cast<double*>(ctx->d_mu), static_cast<double*>(ctx->d_s2));
+        SBO_LAUNCH_CHECK(ctx, "posterior_thin2d_f64_kernel");
+        return SBO_OK;
+      }
+      SBO_TRY(f64_chunk_boxes(ctx, kD2Threads, &boxes, &p.skip_r2));
+      p.bbox = static_cast<const double4*>(boxes);
+      const size_t smem = (size_t)2 * kD2Chunk * kD2Ld * sizeof(double);
+      const cudaError_t ea = cudaFuncSetAttribute(posterior_thin2d_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (ea != cudaSuccess) return cuda_fail(ctx, ea, "posterior_thin2d_dmma_kernel: cudaFuncSetAttribute(max dynamic smem)");
+      posterior_thin2d_dmma_kernel<<<grid, kD2Threads, smem, ctx->stream>>>(p, static_cast<double*>(ctx->d_mu), static_cast<double*>(ctx->d_s2));
+      SBO_LAUNCH_CHECK(ctx, "posterior_thin2d_dmma_kernel");
       return SBO_OK;
     }
     switch (kr) {

@@ -8,17 +8,20 @@ import torch
 import safe_bayesian_optimization_b200 as pkg
 from safe_bayesian_optimization_b200 import synthetic as S
 
-names = sys.argv[1:] or ["C4"]
+names = [a for a in sys.argv[1:] if "=" not in a] or ["C4"]
+opts = dict(a.split("=") for a in sys.argv[1:] if "=" in a)      # e.g. thin_2d=2: sbo_set_option by name
 for name in names:
     p = S.make_problem(name)
     k = max(S.CONFIGS[name].get("append", 0), 1)
     with pkg.SboContext(sigma_f=p.sigma_f, length_scale=p.length, noise_var=p.noise_var, prior_mean=p.prior_mean,
                         precision=p.precision, max_obs=p.n + 16 * k, max_cells=p.m) as ctx:
+        for key, val in opts.items():
+            ctx.set_option(key, int(val))
         ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
         ctx.set_observations(p.xy, p.y)
         mask = torch.empty(p.m, dtype=torch.uint8).pin_memory().numpy()
         res, _ = ctx.step(p.beta, p.f_min, mask_out=mask)
-        print(f"{name}: full step {res.ms_total:.1f} ms, fit {ctx.fit_info()[0]:.1f} ms", flush=True)
+        print(f"{name} {opts}: full step {res.ms_total:.1f} ms, fit {ctx.fit_info()[0]:.1f} ms", flush=True)
         t = 0
         for delta in (0, 1):
             ctx.set_option("mask_delta", delta)

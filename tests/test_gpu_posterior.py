@@ -335,15 +335,16 @@ def test_eager_first_pairs_bit_identical(pkg, oracle, coracle, n, W, H):
     assert np.abs(res["1"]["s2"] - ref["s2"]).max() <= TOL["fp32"] * p.sigma_f ** 2
 
 
-@pytest.mark.parametrize("precision", ["fp64"])
-def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, precision):
-    """One new row, >= one 128 x 128 tile per SM: the 2-D register-tile kernels.  Same projections as the column-strip
-    kernel (SBO_OPT_THIN_2D = 0), different summation order: agreement to rounding; ragged tile edges; and against a full
-    refresh of the same observation set."""
+@pytest.mark.parametrize("precision,W", [("fp64", 1990), ("fp64", 1989)])
+def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, precision, W):
+    """One new row, >= one 128 x 128 tile per SM: the 2-D tile kernels -- on the fp64 tensor path (DMMA, the default) and as
+    DFMA register tiles (SBO_OPT_THIN_2D = 2).  Same projections as the column-strip kernel (SBO_OPT_THIN_2D = 0),
+    different summation order: agreement to rounding; ragged tile edges, an odd row length (no 16-byte row alignment); and
+    against a full refresh of the same observation set."""
     n0 = 130
-    p = S.make_problem("C5", n=n0 + 2, W=1990, H=1250)
+    p = S.make_problem("C5", n=n0 + 2, W=W, H=1250)
     out = {}
-    for flag in ("0", "1"):
+    for flag in ("0", "2", "1"):
         with make_ctx(pkg, p, precision=precision, kernel="auto" if precision == "fp64" else "tcgen05", max_obs=n0 + 2,
                       options={"thin_2d": int(flag)}) as ctx:
             ctx.set_grid(p.x0, p.y0, p.rx, p.ry, p.W, p.H)
@@ -359,7 +360,8 @@ def test_thin_2d_tile_kernel_matches_thin_kernel(pkg, precision):
                 mu_f, s2_f = ctx.mu().astype(np.float64), ctx.sigma2().astype(np.float64)
     scale = np.abs(mu_f).max()
     tight, loose = (1e-12, 1e-10) if precision == "fp64" else (2e-6, 1e-5)
-    assert np.abs(out["1"][0] - out["0"][0]).max() <= tight * scale and np.abs(out["1"][1] - out["0"][1]).max() <= tight
+    for flag in ("1", "2"):
+        assert np.abs(out[flag][0] - out["0"][0]).max() <= tight * scale and np.abs(out[flag][1] - out["0"][1]).max() <= tight, flag
     assert np.abs(out["1"][0] - mu_f).max() <= loose * scale and np.abs(out["1"][1] - s2_f).max() <= loose
 
 
