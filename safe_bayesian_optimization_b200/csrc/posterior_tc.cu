@@ -1324,6 +1324,7 @@ int32_t launch_posterior_tc_inc(sbo_ctx* ctx, int row_lo) {
   p.xscale = std::sqrt(1.4426950408889634 / (2.0 * ctx->cfg.length_scale * ctx->cfg.length_scale));
   p.a_scale = (float)std::ldexp(ctx->cfg.sigma_f * ctx->cfg.sigma_f, ctx->shift_a);
   p.u_unscale = std::ldexp(1.0, -(ctx->shift_a + ctx->shift_b));
+  p.u_unscale_f = (float)p.u_unscale;
   p.tiles_x = (ctx->W + BM - 1) / BM;
   const int ncp = (p.tiles_x + 1) / 2;
   for (int s0 = 0; s0 < nslabs; s0 += band_slabs) {   // bands run back to back on the stream and reuse the planes buffer

@@ -24,6 +24,7 @@ struct IncParams {
   double x0, rx, xscale;
   float a_scale;       // sigma_f^2 2^shift_a
   double u_unscale;    // 2^-(shift_a + shift_b)
+  float u_unscale_f;   // ... as fp32 (exact: a power of two)
   int nslabs;          // slabs of 256 rows of P
   int tiles_x;         // 128-column tiles per grid row
   int rp;              // rows of P (multiple of 256); the lo plane starts at row rp of the tensor map
@@ -228,10 +229,12 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
     // =============================== epilogue: sigma^2 -= sum_q u_q^2, mu += sum_q w_q u_q ===============================
     const int q4 = warp & 3;
     const int c = q4 * 32 + lane;  // TMEM lane == column of the tile
-    double wq[KP];
+    float wq[KP];
 #pragma unroll
-    for (int q = 0; q < KP; ++q) wq[q] = q < p.k ? p.w[p.row_lo + q] * p.u_unscale : 0.0;
-    const float uu = (float)p.u_unscale;
+    for (int q = 0; q < KP; ++q) wq[q] = q < p.k ? (float)(p.w[p.row_lo + q] * p.u_unscale) : 0.f;
+    const float uu = p.u_unscale_f;
+    const long long row_bytes = (long long)p.W * (long long)sizeof(float);
+    const long long mu_minus_s2 = reinterpret_cast<const char*>(p.mu) - reinterpret_cast<const char*>(p.s2);
     uint32_t acc_it = 0;
     for (long long item = group; item < nitems; item += ngroups) {
       const int sb = (int)(item / ncp), ct = 2 * (int)(item % ncp) + (int)rank;
@@ -264,52 +267,72 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
           if (pit < nitems) {
             const int psb = (int)(pit / ncp), pct = 2 * (int)(pit % ncp) + (int)rank;
             const int pcol = pct * BM + c;
-            if (pct < p.tiles_x && pcol < p.W) {
-              const int plr0 = p.lr_base + ((psb * BN + pg * 16) >> LQ);
+            const int plr0 = p.lr_base + ((psb * BN + pg * 16) >> LQ);
+            if (pct < p.tiles_x && pcol < p.W && plr0 + (16 >> LQ) <= p.rows_local) {   // (ragged ends go without)
+              const char* ps = reinterpret_cast<const char*>(p.s2 + (long long)plr0 * p.W + pcol);
 #pragma unroll
               for (int r = 0; r < (16 >> LQ); ++r) {
-                if (plr0 + r < p.rows_local) {
-                  const long long lc = (long long)(plr0 + r) * p.W + pcol;
-                  prefetch_l2(p.s2 + lc);
-                  prefetch_l2(p.mu + lc);
-                }
+                prefetch_l2(ps);
+                prefetch_l2(ps + mu_minus_s2);
+                ps += row_bytes;
               }
             }
           }
         }
         // The stored sigma^2 / mu of the group's grid rows are fetched before the first of them is rewritten: written as one
         // read-modify-write per row the loads cannot pass the stores (mu and s2 may alias as far as the compiler knows)
-        // and a thread's 256 rows of an item become 256 dependent DRAM round trips -- 180 us per item against 45 us of
-        // MMAs at C4 with one new row, 3.7 ms per step.
+        // and a thread's 256 rows of an item become 256 dependent DRAM round trips.  The arithmetic is fp32: one warp per
+        // scheduler does this work, and with fp64 conversions and adds it issued one instruction per 12 cycles (ncu r02p/q:
+        // 56 instructions per row, fp64-pipe and scoreboard stalls) -- the increment's own rounding (2^-24 of |w u|, of
+        // u^2) is below that of the fp32 value it is added to.
         constexpr int kRows = 16 >> LQ;                  // grid rows in this group of 16 TMEM columns (LQ <= 4)
-        constexpr int kBatch = kRows < 8 ? kRows : 8;    // 8 rows = 16 loads in flight per thread (16 rows spill their addresses)
+        const int nrows = min(kRows, p.rows_local - lr0);   // (< kRows only in the last slab of the shard)
+        if (live && nrows == kRows) {   // every row of the group exists: no predicates, addresses by increment
+          constexpr int kSub = kRows < 8 ? kRows : 8;   // rows whose loads are in flight together (16 spill)
+          char* base = reinterpret_cast<char*>(p.s2 + (long long)lr0 * p.W + col);
 #pragma unroll
-        for (int t0 = 0; t0 < kRows; t0 += kBatch) {
-          float s2v[kBatch], muv[kBatch];
+          for (int r0 = 0; r0 < kRows; r0 += kSub) {
+            float s2v[kSub], muv[kSub];
+            {
+              const char* ps = base;
 #pragma unroll
-          for (int b = 0; b < kBatch; ++b) {
-            const int lr = lr0 + t0 + b;
-            const bool ok = live && lr < p.rows_local;
-            const long long lc = (long long)lr * p.W + col;
-            s2v[b] = ok ? p.s2[lc] : 0.f;
-            muv[b] = ok ? p.mu[lc] : 0.f;
+              for (int r = 0; r < kSub; ++r) {
+                s2v[r] = *reinterpret_cast<const float*>(ps);
+                muv[r] = *reinterpret_cast<const float*>(ps + mu_minus_s2);
+                ps += row_bytes;
+              }
+            }
+#pragma unroll
+            for (int r = 0; r < kSub; ++r) {
+              float usq = 0.f, dmu = 0.f;
+#pragma unroll
+              for (int q = 0; q < KP; ++q) {
+                const float d = __uint_as_float(v[((r0 + r) << LQ) + q]);
+                const float u = d * uu;
+                usq = fmaf(u, u, usq);
+                dmu = fmaf(wq[q], d, dmu);
+              }
+              *reinterpret_cast<float*>(base) = s2v[r] - usq;
+              *reinterpret_cast<float*>(base + mu_minus_s2) = muv[r] + dmu;
+              base += row_bytes;
+            }
           }
+        } else if (live) {
+          float* s2p = p.s2 + (long long)lr0 * p.W + col;
+          float* mup = p.mu + (long long)lr0 * p.W + col;
 #pragma unroll
-          for (int b = 0; b < kBatch; ++b) {
-            float usq = 0.f;
-            double dmu = 0.0;
+          for (int r = 0; r < kRows; ++r) {   // (unrolled: a dynamic index would put the accumulator slice in local memory)
+            float usq = 0.f, dmu = 0.f;
 #pragma unroll
             for (int q = 0; q < KP; ++q) {
-              const float d = __uint_as_float(v[((t0 + b) << LQ) + q]);
+              const float d = __uint_as_float(v[(r << LQ) + q]);
               const float u = d * uu;
               usq = fmaf(u, u, usq);
-              dmu = fma(wq[q], (double)d, dmu);
+              dmu = fmaf(wq[q], d, dmu);
             }
-            const int lr = lr0 + t0 + b;
-            if (live && lr < p.rows_local) {
-              const long long lc = (long long)lr * p.W + col;
-              p.s2[lc] = (float)((double)s2v[b] - (double)usq);
-              p.mu[lc] = (float)((double)muv[b] + dmu);
+            if (r < nrows) {
+              s2p[(long long)r * p.W] -= usq;
+              mup[(long long)r * p.W] += dmu;
             }
           }
         }
