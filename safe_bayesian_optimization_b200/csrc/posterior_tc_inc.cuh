@@ -257,9 +257,10 @@ posterior_tc_inc_kernel(const __grid_constant__ CUtensorMap tmap, IncParams p) {
         tmem_ld16(taddr + g * 16, v);
         tmem_ld_wait();
         const int lr0 = p.lr_base + ((sb * BN + g * 16) >> LQ);  // first grid row of this group of 16 rows of P
-        // The read-modify-write below is bound by DRAM latency (measured: ~2.2 us per batch of loads, 93 us per item against
-        // 55 us of MMAs at C4 -- the MMA issuer waited for an accumulator 45 % of the time): the lines of the group
-        // kPrefetchGroups ahead (this item's, or the first ones of this CTA pair's next item) are pulled into the L2 now.
+        // The read-modify-write below waits on its loads (long-scoreboard stalls were 40 % of the epilogue's samples): the lines
+        // of the group kPrefetchGroups ahead (this item's, or the first ones of this CTA pair's next item) are pulled into the
+        // L2 now.  On its own this changed nothing (the epilogue was issue-latency-bound, see below); it is kept because the
+        // slimmed epilogue has little else to hide a DRAM round trip behind.
         {
           int pg = g + kPrefetchGroups;
           long long pit = item;

@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 echo "== pytest -m gpu -x"; timeout 2400 python -m pytest tests -x -q -m gpu 2>&1 | tail -4 | tee gpurun_out/pytest_gpu_r02r.log
 echo "== smoke"; timeout 600 python __graft_entry__.py smoke 2>&1 | tail -5 | tee gpurun_out/smoke_r02r.log
-echo "== default bench"; /usr/bin/time -v timeout 1500 python bench.py > gpurun_out/bench_default_r02r.json 2> gpurun_out/bench_default_r02r.err; echo "rc=$?"; grep -E "Elapsed|Maximum resident" gpurun_out/bench_default_r02r.err
+echo "== default bench"; SECONDS=0; timeout 1500 python bench.py > gpurun_out/bench_default_r02r.json 2> gpurun_out/bench_default_r02r.err; echo "rc=$?"; echo "wall ${SECONDS} s"
 python - <<'PY'
 import json
 d = json.loads(open("gpurun_out/bench_default_r02r.json").read().strip().splitlines()[-1])
