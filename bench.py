@@ -500,13 +500,14 @@ def run_workload(h: Harness, name: str, steps: int, warmup: int, primary: bool, 
                    "host_wall_p50_ms": float(np.percentile([o[1] for o in inc_outs], 50)),
                    "includes": "sbo_append_observations (rank-k update of L, L^-1, alpha) + sbo_step_incremental "
                                "(refresh / drift policy on) + mask D2H; CUDA events, this rank"}
-    if name == "C5" or primary:     # end of the chain against a full refresh of the same observation set (same kernels, fp64 / fp32)
-        mu_i, s2_i = ctx.mu(), ctx.sigma2()
-        ctx.step(p.beta, p.f_min, mask_out=mask_host)
-        mu_f, s2_f = ctx.mu(), ctx.sigma2()
-        dm = float(np.abs(mu_i - mu_f).max() / max(1.0, np.abs(mu_f).max())); ds = float(np.abs(s2_i - s2_f).max() / p.sigma_f ** 2)
-        incremental["end_parity"] = {"vs": "full refresh (refit not needed: same factor) of the same observations on the GPU",
-                                     "mu_rel_max": h.max_over_ranks(dm), "s2_abs_max_over_sf2": h.max_over_ranks(ds)}
+    # end of the chain against a full refresh of the same observation set (same kernels, fp64 / fp32), every workload
+    mu_i, s2_i = ctx.mu(), ctx.sigma2()
+    ctx.step(p.beta, p.f_min, mask_out=mask_host)
+    mu_f, s2_f = ctx.mu(), ctx.sigma2()
+    dm = float(np.abs(mu_i - mu_f).max() / max(1.0, np.abs(mu_f).max())); ds = float(np.abs(s2_i - s2_f).max() / p.sigma_f ** 2)
+    incremental["end_parity"] = {"vs": "full refresh (refit not needed: same factor) of the same observations on the GPU",
+                                 "mu_rel_max": h.max_over_ranks(dm), "s2_abs_max_over_sf2": h.max_over_ranks(ds)}
+    del mu_i, s2_i, mu_f, s2_f
     # the same loop with SBO_OPT_MASK_DELTA: only the 64 KiB mask segments in which a byte changed travel to the host
     # (the warm-up step is the one full copy that makes mask_host the mirror of the device mask)
     ctx.set_option("mask_delta", 1)
