@@ -67,3 +67,52 @@ def test_skip_bound_is_conservative():
         s2c = hp.sigma_f ** 2 - (Vc ** 2).sum(axis=1)
         bound = 2.0 * p.n * np.sqrt(hp.sigma_f ** 2 / hp.noise_var) * 2.0 ** -b * hp.sigma_f ** 2
         assert np.abs(s2c - s2).max() <= bound
+
+
+def test_dmma_tile_staging_recurrence():
+    """Staging of posterior_thin2d_dmma_kernel (posterior_thin.cu): along a tile edge of 128 cells with pitch h, from three
+    exp per (observation, factor) -- e(0), g = exp(-2 d0 h / 2l^2), G_0 = exp(-(32 d0 h + 256 h^2) / 2l^2) -- the anchors
+    e(c) = e(0) g^c T[c] (c < 16, g^c from g, g^2, g^4, g^8) and eight recurrence steps e(c + 16 (i + 1)) = e(c + 16 i) G_i,
+    G_(i+1) = G_i exp(-512 h^2 / 2l^2) with G_0 scaled by R[c] = exp(-32 c h^2 / 2l^2) reproduce exp(-(d0 + c h)^2 / 2l^2)
+    to a few tens of roundings, for observations on either side of the edge and at the reach of the block-sparse walk."""
+    length = 0.4
+    inv2l2 = 1.0 / (2.0 * length * length)
+    worst = 0.0
+    for h in (4.0 * length / 128.0, 0.0078 * length, -0.011 * length):      # the host's bound 128 |h| <= 4 l, C5's pitch, a negative pitch
+        T = np.exp(-(np.arange(16.0) ** 2) * h * h * inv2l2)
+        R = np.exp(-32.0 * np.arange(16.0) * h * h * inv2l2)
+        q16 = np.exp(-512.0 * h * h * inv2l2)
+        for d0 in (-9.0 * length, -1.3 * length, 0.0, 0.37 * length, 8.5 * length, -13.0):
+            e0 = np.exp(-d0 * d0 * inv2l2)
+            g1 = np.exp(-2.0 * d0 * h * inv2l2)
+            g16 = np.exp(-(32.0 * d0 * h + 256.0 * h * h) * inv2l2)
+            pw = [g1, g1 * g1, (g1 * g1) ** 2, ((g1 * g1) ** 2) ** 2]
+            got = np.zeros(128)
+            for c in range(16):
+                e = e0 * T[c]
+                for b in range(4):
+                    if c >> b & 1:
+                        e *= pw[b]
+                gg = g16 * R[c]
+                for i in range(8):
+                    got[c + 16 * i] = e
+                    e *= gg
+                    gg *= q16
+            ref = np.exp(-((d0 + np.arange(128.0) * h) ** 2) * inv2l2)
+            live = ref > 1e-280                                                 # (an underflowing anchor zeroes its segment)
+            worst = max(worst, float(np.abs(got[live] / ref[live] - 1.0).max()))
+    assert worst < 2e-13, worst
+
+
+def test_pplanes_chunk_test_is_implied_by_the_item_mask():
+    """pplanes_kernel (posterior_tc_inc.cuh) leaves out the chunks whose box is farther than the cut-off in y alone from a slab
+    of rows; build_item_mask keeps a chunk for an item of that slab when dx^2 + dy^2 <= bits + 0.5 in fp32 with the same dy.
+    Whatever an item reads was therefore written: fl(dx^2 + dy^2) >= dy^2 for dx^2 >= 0, in round-to-nearest fp32."""
+    rng = np.random.default_rng(7)
+    dx = rng.uniform(0.0, 9.0, 200000).astype(np.float32)
+    dy = rng.uniform(0.0, 9.0, 200000).astype(np.float32)
+    bits = np.float32(36.0) + np.float32(0.5)
+    item_keeps = (dx * dx + dy * dy) <= bits             # numpy float32 arithmetic rounds each operation to nearest, like __fmul_rn / __fadd_rn
+    plane_written = (dy * dy) <= bits
+    assert not np.any(item_keeps & ~plane_written)
+    assert np.all((dx * dx + dy * dy) >= dy * dy)
