@@ -354,7 +354,7 @@ posterior_thin2d_f64_kernel(ThinParams p, double* __restrict__ mu_out, double* _
 //   G_(i+1) = G_i * exp(-512 h^2 / 2l^2);
 // 128 threads compute (e(0), g, g^2, g^4, g^8, G_0 without R) per (observation, factor) into shared memory, then every
 // thread forms its anchors with <= 6 multiplications (g^c from the bits of c; T, R from two 16-entry tables) and runs
-// eight recurrence steps: ~30 roundings per staged value, 3e-15 relative.  An anchor that underflows sits >= 34
+// eight recurrence steps: 3e-14 relative within the reach of the walk (tests/test_identities.py; the exponentials themselves carry |x| ulp).  An anchor that underflows sits >= 34
 // length-scales from every cell of the edge (the host requires 128 h <= 4 l); its ratios are zeroed with it so that a huge
 // ratio cannot meet the zero.
 constexpr int kD2Threads = 512;
