@@ -89,24 +89,36 @@ pplanes_kernel(const double* __restrict__ xy, const double* __restrict__ Linv, i
     const float dy = fmaxf(fmaxf(b.z - yhi, ylo - b.w), 0.f);
     if (__fmul_rn(dy, dy) > skip_bits + 0.5f) return;
   }
-  // one thread = one observation: its y and its entries of the new rows of L^-1 are read once for the CTA's grid rows
+  // one thread = one observation: its y and its entries of the new rows of L^-1 are read once for the CTA's grid rows.
+  // The row factor follows a recurrence along the grid rows (pitch ry, dy(g + 1) = dy(g) - ry):
+  //   e(g + 1) = e(g) s(g),  s(g) = exp((2 dy(g) ry - ry^2) / 2l^2),  s(g + 1) = s(g) exp(-2 ry^2 / 2l^2),
+  // anchored with two fp64 exp at every GLOBAL grid row that is a multiple of 16 -- so the value of a row does not depend
+  // on where a band of rows starts (row-band shards and P bands give the same bits) -- instead of one exp per row:
+  // <= 15 steps, ~40 roundings, far below the 2^-22 of the fp16 pair it is rounded to.
   const int kp = 1 << lq;
   const double yj = j < n ? xy[2 * (size_t)j + 1] : 0.0;
   double lq_[16];
 #pragma unroll
   for (int q = 0; q < 16; ++q) lq_[q] = (q < k && q < kp && j < n) ? Linv[(size_t)(row_lo + q) * ld + j] : 0.0;
+  const double q2 = exp(-2.0 * ry * ry * inv2l2);
+  double e = 0.0, st = 0.0;
+  auto anchor = [&](int grow) {
+    const double dy = yj - cell_coord(y0, ry, grow);
+    e = exp(-dy * dy * inv2l2) * scale;
+    st = e != 0.0 ? exp((2.0 * dy * ry - ry * ry) * inv2l2) : 0.0;   // (a huge ratio must not meet an underflowed anchor)
+  };
+  const int gr0 = row0 + lr_base + lb0;
+  anchor(gr0 & ~15);
+  for (int g = gr0 & ~15; g < gr0; ++g) { e *= st; st *= q2; }
 #pragma unroll 2
   for (int r = 0; r < kPplaneRows; ++r) {
     const int lb = lb0 + r, lr = lr_base + lb;
-    double e = 0.0;
-    if (j < n && lr < rows_local) {
-      const double dy = yj - cell_coord(y0, ry, row0 + lr);
-      e = exp(-dy * dy * inv2l2) * scale;
-    }
+    if (r > 0 && ((gr0 + r) & 15) == 0) anchor(gr0 + r);
+    const double er = (j < n && lr < rows_local) ? e : 0.0;
 #pragma unroll
     for (int q = 0; q < 16; ++q) {
       if (q < kp) {
-        const double x = (q < k && e != 0.0) ? e * lq_[q] : 0.0;
+        const double x = (q < k && er != 0.0) ? er * lq_[q] : 0.0;
         const __half hi = __float2half_rn((float)x);
         const __half lo = __float2half_rn((float)(x - (double)__half2float(hi)));
         const size_t rho = (size_t)lb * kp + q;
@@ -114,6 +126,8 @@ pplanes_kernel(const double* __restrict__ xy, const double* __restrict__ Linv, i
         planes[((size_t)rp + rho) * ld + j] = lo;
       }
     }
+    e *= st;
+    st *= q2;
   }
 }
 

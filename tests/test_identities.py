@@ -116,3 +116,38 @@ def test_pplanes_chunk_test_is_implied_by_the_item_mask():
     plane_written = (dy * dy) <= bits
     assert not np.any(item_keeps & ~plane_written)
     assert np.all((dx * dx + dy * dy) >= dy * dy)
+
+
+def test_pplanes_row_recurrence():
+    """pplanes_kernel (posterior_tc_inc.cuh): the row factor exp(-(y_j - y(g))^2 / 2l^2) along consecutive grid rows g by
+    e(g + 1) = e(g) s(g), s(g + 1) = s(g) exp(-2 ry^2 / 2l^2), re-anchored with two exp at every global row that is a
+    multiple of 16; a band that starts anywhere reproduces the same values, bit for bit, as one that starts at row 0."""
+    length, y0 = 0.4, 0.25
+    inv2l2 = 1.0 / (2.0 * length * length)
+
+    def rows(gr0, count, yj, ry):
+        out = np.zeros(count)
+        q2 = np.exp(-2.0 * ry * ry * inv2l2)
+
+        def anchor(g):
+            dy = yj - (y0 + g * ry)
+            e = np.exp(-dy * dy * inv2l2)
+            return e, (np.exp((2.0 * dy * ry - ry * ry) * inv2l2) if e != 0.0 else 0.0)
+        e, st = anchor(gr0 & ~15)
+        for _ in range(gr0 & ~15, gr0):
+            e, st = e * st, st * q2
+        for r in range(count):
+            if r > 0 and (gr0 + r) & 15 == 0:
+                e, st = anchor(gr0 + r)
+            out[r] = e
+            e, st = e * st, st * q2
+        return out
+
+    for ry in (0.0022, 0.05, -0.013):
+        for yj in (0.3, 7.9, -2.0):
+            full = rows(0, 96, yj, ry)
+            ref = np.exp(-((yj - (y0 + np.arange(96.0) * ry)) ** 2) * inv2l2)
+            live = ref > 1e-250
+            assert np.abs(full[live] / ref[live] - 1.0).max() < 5e-13
+            for start in (5, 16, 37):
+                assert np.array_equal(rows(start, 48, yj, ry), full[start:start + 48])
