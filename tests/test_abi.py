@@ -90,3 +90,16 @@ def test_plan_row_bands_is_a_partition_and_balances_work(pkg):
     small = S.make_problem("C2", n=300, W=256, H=100)   # dense walk: equal rows
     c2, _ = plan_row_bands(small, 4)
     assert c2 == [0, 25, 50, 75, 100]
+
+
+def test_plan_row_bands_cuts_are_the_measured_ones(pkg):
+    """The cuts the multi-GPU measurements of round 2 were taken with (profiles/bench_c4_{2,4,8}gpu_r02g.json,
+    bench_default_2gpu_r02t.json: identical checksums, 98.8 % at 8 GPUs): a change of the planner that moves them is a
+    change of what was measured."""
+    from safe_bayesian_optimization_b200 import synthetic as S
+    from safe_bayesian_optimization_b200.optimizer import plan_row_bands
+    p = S.make_problem("C4")
+    assert plan_row_bands(p, 2)[0] == [0, 2778, 8192]
+    assert plan_row_bands(p, 8)[0] == [0, 842, 1483, 2102, 2778, 3548, 4471, 5675, 8192]
+    assert plan_row_bands(S.make_problem("C3"), 8)[0] == [0, 468, 860, 1216, 1563, 1940, 2393, 2990, 4096]
+    assert plan_row_bands(S.make_problem("C5"), 2)[0] == [0, 1510, 4096]
